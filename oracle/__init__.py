@@ -1,0 +1,416 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+ctypes bindings of ``oracle/liboracle.so`` (the CPU restatement of Radler's minor
+loops; see ``oracle/oracle.h``). Importable only from ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl reference``
+leg. The product package never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+
+
+def build(force: bool = False) -> str:
+    """Compile liboracle.so (and oracle/_ref when /root/reference exists)."""
+    if force or not os.path.exists(_LIB_PATH):
+        subprocess.run(["make", "-C", _HERE, "-B" if force else "-s", "liboracle.so"], check=True)
+    return _LIB_PATH
+
+
+class _Cube(C.Structure):
+    _fields_ = [("width", C.c_uint64), ("height", C.c_uint64), ("n_channels", C.c_uint64),
+                ("n_pol", C.c_uint64), ("weights", C.POINTER(C.c_float)),
+                ("pol_linked", C.POINTER(C.c_uint8)), ("pol_norm", C.c_float),
+                ("squared_joins", C.c_int32)]
+
+
+class _Settings(C.Structure):
+    _fields_ = [("threshold", C.c_float), ("major_iteration_threshold", C.c_float),
+                ("minor_loop_gain", C.c_float), ("major_loop_gain", C.c_float),
+                ("clean_border_ratio", C.c_float), ("divergence_limit", C.c_float),
+                ("max_iterations", C.c_uint64), ("iteration_number", C.c_uint64),
+                ("allow_negative", C.c_int32), ("stop_on_negative", C.c_int32),
+                ("clean_mask", C.POINTER(C.c_uint8)), ("rms_factor", C.POINTER(C.c_float)),
+                ("spectral_mode", C.c_int32), ("n_terms", C.c_uint64),
+                ("frequencies", C.POINTER(C.c_double)), ("fit_weights", C.POINTER(C.c_float)),
+                ("record_trace", C.c_int32)]
+
+
+class _Result(C.Structure):
+    _fields_ = [("has_starting_peak", C.c_int32), ("starting_peak_value", C.c_float),
+                ("final_peak_value", C.c_float), ("another_iteration_required", C.c_int32),
+                ("is_diverging", C.c_int32), ("iteration_number", C.c_uint64),
+                ("n_trace", C.c_uint64), ("n_selected", C.c_uint64)]
+
+
+class _MsConfig(C.Structure):
+    _fields_ = [("fast_sub_minor_loop", C.c_int32), ("sub_minor_loop_gain", C.c_double),
+                ("scale_bias", C.c_double), ("max_scales", C.c_uint64),
+                ("convolution_padding", C.c_double), ("scale_list", C.POINTER(C.c_double)),
+                ("n_scale_list", C.c_uint64), ("shape", C.c_int32), ("beam_size", C.c_double),
+                ("pixel_scale_x", C.c_double), ("pixel_scale_y", C.c_double)]
+
+
+class _ScaleInfo(C.Structure):
+    _fields_ = [("scale", C.c_float), ("psf_peak", C.c_float), ("kernel_peak", C.c_float),
+                ("bias_factor", C.c_float), ("gain", C.c_float),
+                ("max_normalized_image_value", C.c_float),
+                ("max_unnormalized_image_value", C.c_float), ("rms", C.c_float),
+                ("max_x", C.c_uint64), ("max_y", C.c_uint64), ("is_active", C.c_int32),
+                ("n_components_cleaned", C.c_uint64), ("total_flux_cleaned", C.c_float)]
+
+
+TRACE_DTYPE = np.dtype([("iteration", "<u4"), ("scale", "<u4"), ("x", "<u4"), ("y", "<u4"),
+                        ("value", "<f4")])
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB_PATH)
+        L.orc_create_generic.restype = C.c_void_p
+        L.orc_create_generic.argtypes = [C.c_int32]
+        L.orc_create_multiscale.restype = C.c_void_p
+        L.orc_create_multiscale.argtypes = [C.POINTER(_MsConfig)]
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_last_error.restype = C.c_char_p
+        L.orc_last_error.argtypes = [C.c_void_p]
+        L.orc_execute.restype = C.c_int32
+        L.orc_execute.argtypes = [C.c_void_p, C.POINTER(_Cube), C.POINTER(_Settings), C.c_void_p,
+                                  C.c_void_p, C.c_void_p, C.POINTER(_Result)]
+        L.orc_get_trace.restype = C.c_uint64
+        L.orc_get_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        L.orc_ms_set_automask_mode.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        L.orc_ms_scale_count.restype = C.c_uint64
+        L.orc_ms_scale_count.argtypes = [C.c_void_p]
+        L.orc_ms_minor_iterations.restype = C.c_uint64
+        L.orc_ms_minor_iterations.argtypes = [C.c_void_p]
+        L.orc_ms_scale_info.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(_ScaleInfo)]
+        L.orc_ms_scale_mask.restype = C.c_int32
+        L.orc_ms_scale_mask.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.orc_set_threads.argtypes = [C.c_uint64]
+        L.orc_get_threads.restype = C.c_uint64
+        L.orc_find_peak.restype = C.c_int32
+        L.orc_find_peak.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_uint64,
+                                    C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
+                                    C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                    C.POINTER(C.c_float)]
+        L.orc_subtract_image.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64,
+                                         C.c_uint64, C.c_uint64, C.c_float]
+        L.orc_partial_subtract_image.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p,
+                                                 C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
+                                                 C.c_float, C.c_uint64, C.c_uint64]
+        L.orc_integrate.argtypes = [C.POINTER(_Cube), C.c_void_p, C.c_int32, C.c_void_p]
+        L.orc_integrated_psf.argtypes = [C.POINTER(_Cube), C.c_void_p, C.c_void_p]
+        L.orc_spectral_fit.argtypes = [C.c_int32, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
+                                       C.c_void_p, C.c_void_p]
+        L.orc_polynomial_projection.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
+                                                C.c_void_p]
+        L.orc_convolve.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64]
+        L.orc_prepare_convolution_kernel.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64,
+                                                     C.c_uint64]
+        L.orc_prepare_small_convolution_kernel.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64,
+                                                           C.c_void_p, C.c_uint64]
+        L.orc_fft1d.argtypes = [C.c_void_p, C.c_uint64, C.c_int32]
+        L.orc_trim.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64,
+                               C.c_uint64]
+        L.orc_untrim.argtypes = L.orc_trim.argtypes
+        L.orc_good_fft_size.restype = C.c_uint64
+        L.orc_good_fft_size.argtypes = [C.c_uint64]
+        L.orc_convolution_size.restype = C.c_uint64
+        L.orc_convolution_size.argtypes = [C.c_double, C.c_uint64, C.c_double]
+        L.orc_make_shape_function.restype = C.c_uint64
+        L.orc_make_shape_function.argtypes = [C.c_float, C.c_uint64, C.c_int32, C.c_void_p]
+        L.orc_ms_transform.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_float,
+                                       C.c_int32]
+        L.orc_add_shape_component.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_float,
+                                              C.c_uint64, C.c_uint64, C.c_float, C.c_int32]
+        _lib = L
+    return _lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+@dataclass
+class Cube:
+    """Layout metadata of an ImageSet: images ordered [channel][pol]."""
+    width: int
+    height: int
+    n_channels: int = 1
+    n_pol: int = 1
+    weights: np.ndarray | None = None
+    pol_linked: np.ndarray | None = None
+    pol_norm: float = 1.0
+    squared_joins: bool = False
+    _keep: list = field(default_factory=list, repr=False)
+
+    def c(self) -> _Cube:
+        w = None if self.weights is None else _f32(self.weights)
+        p = None if self.pol_linked is None else np.ascontiguousarray(self.pol_linked, np.uint8)
+        self._keep = [w, p]
+        return _Cube(self.width, self.height, self.n_channels, self.n_pol,
+                     None if w is None else w.ctypes.data_as(C.POINTER(C.c_float)),
+                     None if p is None else p.ctypes.data_as(C.POINTER(C.c_uint8)),
+                     self.pol_norm, int(self.squared_joins))
+
+
+@dataclass
+class Settings:
+    """Mirror of DeconvolutionAlgorithm's settings (deconvolution_algorithm.h:189-202)."""
+    threshold: float = 0.0
+    major_iteration_threshold: float = 0.0
+    minor_loop_gain: float = 0.1
+    major_loop_gain: float = 1.0
+    clean_border_ratio: float = 0.05
+    divergence_limit: float = 4.0
+    max_iterations: int = 500
+    iteration_number: int = 0
+    allow_negative: bool = True
+    stop_on_negative: bool = False
+    clean_mask: np.ndarray | None = None
+    rms_factor: np.ndarray | None = None
+    spectral_mode: int = 0
+    n_terms: int = 0
+    frequencies: np.ndarray | None = None
+    fit_weights: np.ndarray | None = None
+    record_trace: bool = False
+
+
+@dataclass
+class Result:
+    starting_peak_value: float | None
+    final_peak_value: float
+    another_iteration_required: bool
+    is_diverging: bool
+    iteration_number: int
+    trace: np.ndarray
+    n_selected: int = 0
+
+
+class Algorithm:
+    def __init__(self, handle):
+        self._h = handle
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_destroy(self._h)
+            self._h = None
+
+    def execute(self, cube: Cube, s: Settings, residual, model, psfs) -> Result:
+        """Runs ExecuteMajorIteration; residual/model ([C,H,W] float32) are updated in place."""
+        assert residual.dtype == np.float32 and residual.flags.c_contiguous
+        assert model.dtype == np.float32 and model.flags.c_contiguous
+        psfs = _f32(psfs)
+        mask = None if s.clean_mask is None else np.ascontiguousarray(s.clean_mask, np.uint8)
+        rms = None if s.rms_factor is None else _f32(s.rms_factor)
+        fr = None if s.frequencies is None else np.ascontiguousarray(s.frequencies, np.float64)
+        fw = None if s.fit_weights is None else _f32(s.fit_weights)
+        cs = _Settings(s.threshold, s.major_iteration_threshold, s.minor_loop_gain,
+                       s.major_loop_gain, s.clean_border_ratio, s.divergence_limit,
+                       s.max_iterations, s.iteration_number, int(s.allow_negative),
+                       int(s.stop_on_negative),
+                       None if mask is None else mask.ctypes.data_as(C.POINTER(C.c_uint8)),
+                       None if rms is None else rms.ctypes.data_as(C.POINTER(C.c_float)),
+                       s.spectral_mode, s.n_terms,
+                       None if fr is None else fr.ctypes.data_as(C.POINTER(C.c_double)),
+                       None if fw is None else fw.ctypes.data_as(C.POINTER(C.c_float)),
+                       int(s.record_trace))
+        cc = cube.c()
+        out = _Result()
+        rc = lib().orc_execute(self._h, C.byref(cc), C.byref(cs), _ptr(residual), _ptr(model),
+                               _ptr(psfs), C.byref(out))
+        if rc != 0:
+            raise RuntimeError(lib().orc_last_error(self._h).decode())
+        trace = np.zeros(out.n_trace, TRACE_DTYPE)
+        if out.n_trace:
+            lib().orc_get_trace(self._h, _ptr(trace), out.n_trace)
+        return Result(out.starting_peak_value if out.has_starting_peak else None,
+                      out.final_peak_value, bool(out.another_iteration_required),
+                      bool(out.is_diverging), out.iteration_number, trace, out.n_selected)
+
+
+class GenericClean(Algorithm):
+    def __init__(self, use_sub_minor_optimization: bool = True):
+        super().__init__(lib().orc_create_generic(int(use_sub_minor_optimization)))
+
+
+class MultiScale(Algorithm):
+    def __init__(self, beam_size=0.0, pixel_scale=1.0, fast_sub_minor_loop=True,
+                 sub_minor_loop_gain=0.2, scale_bias=0.6, max_scales=0, convolution_padding=1.1,
+                 scale_list=None, shape=0):
+        sl = None if not scale_list else np.ascontiguousarray(scale_list, np.float64)
+        cfg = _MsConfig(int(fast_sub_minor_loop), sub_minor_loop_gain, scale_bias, max_scales,
+                        convolution_padding,
+                        None if sl is None else sl.ctypes.data_as(C.POINTER(C.c_double)),
+                        0 if sl is None else len(sl), shape, beam_size, pixel_scale, pixel_scale)
+        super().__init__(lib().orc_create_multiscale(C.byref(cfg)))
+
+    def set_automask_mode(self, track: bool, use: bool):
+        lib().orc_ms_set_automask_mode(self._h, int(track), int(use))
+
+    def scale_infos(self):
+        out = []
+        for i in range(lib().orc_ms_scale_count(self._h)):
+            s = _ScaleInfo()
+            lib().orc_ms_scale_info(self._h, i, C.byref(s))
+            out.append({k: getattr(s, k) for k, _ in _ScaleInfo._fields_})
+        return out
+
+    def minor_iterations(self) -> int:
+        return lib().orc_ms_minor_iterations(self._h)
+
+    def scale_mask(self, i, width, height):
+        m = np.zeros((height, width), np.uint8)
+        return m if lib().orc_ms_scale_mask(self._h, i, _ptr(m)) else None
+
+
+# ---- leaf functions ----------------------------------------------------------------
+def set_threads(n: int):
+    lib().orc_set_threads(n)
+
+
+def find_peak(image, allow_negative=True, start_y=0, end_y=None, h_border=0, v_border=0,
+              mask=None):
+    image = _f32(image)
+    h, w = image.shape
+    if end_y is None:
+        end_y = h
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    x, y, v = C.c_uint64(), C.c_uint64(), C.c_float()
+    found = lib().orc_find_peak(_ptr(image), w, h, int(allow_negative), start_y, end_y, h_border,
+                                v_border, _ptr(m), C.byref(x), C.byref(y), C.byref(v))
+    return (v.value if found else None), x.value, y.value
+
+
+def subtract_image(image, psf, x, y, factor):
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    psf = _f32(psf)
+    h, w = image.shape
+    lib().orc_subtract_image(_ptr(image), _ptr(psf), w, h, x, y, factor)
+
+
+def partial_subtract_image(image, psf, x, y, factor, start_y, end_y):
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    psf = _f32(psf)
+    lib().orc_partial_subtract_image(_ptr(image), image.shape[1], image.shape[0], _ptr(psf),
+                                     psf.shape[1], psf.shape[0], x, y, factor, start_y, end_y)
+
+
+def integrate(cube: Cube, images, square=False):
+    images = _f32(images)
+    dest = np.zeros((cube.height, cube.width), np.float32)
+    cc = cube.c()
+    lib().orc_integrate(C.byref(cc), _ptr(images), int(square), _ptr(dest))
+    return dest
+
+
+def integrated_psf(cube: Cube, psfs):
+    psfs = _f32(psfs)
+    dest = np.zeros((cube.height, cube.width), np.float32)
+    cc = cube.c()
+    lib().orc_integrated_psf(C.byref(cc), _ptr(psfs), _ptr(dest))
+    return dest
+
+
+def spectral_fit(values, freqs, weights, n_terms, mode=1, n_pol=1):
+    values = _f32(values).copy()
+    freqs = np.ascontiguousarray(freqs, np.float64)
+    weights = _f32(weights)
+    lib().orc_spectral_fit(mode, n_terms, len(freqs), n_pol, _ptr(freqs), _ptr(weights),
+                           _ptr(values))
+    return values
+
+
+def polynomial_projection(freqs, weights, n_terms):
+    freqs = np.ascontiguousarray(freqs, np.float64)
+    weights = _f32(weights)
+    out = np.zeros((len(freqs), len(freqs)), np.float64)
+    lib().orc_polynomial_projection(n_terms, len(freqs), _ptr(freqs), _ptr(weights), _ptr(out))
+    return out
+
+
+def convolve(image, kernel):
+    image = _f32(image).copy()
+    kernel = _f32(kernel)
+    h, w = image.shape
+    lib().orc_convolve(_ptr(image), _ptr(kernel), w, h)
+    return image
+
+
+def prepare_convolution_kernel(src):
+    src = _f32(src)
+    dst = np.zeros_like(src)
+    lib().orc_prepare_convolution_kernel(_ptr(dst), _ptr(src), src.shape[1], src.shape[0])
+    return dst
+
+
+def prepare_small_convolution_kernel(kernel, w, h):
+    kernel = _f32(kernel)
+    dst = np.zeros((h, w), np.float32)
+    lib().orc_prepare_small_convolution_kernel(_ptr(dst), w, h, _ptr(kernel), kernel.shape[0])
+    return dst
+
+
+def fft1d(z, inverse=False):
+    z = np.ascontiguousarray(z, np.complex64).copy()
+    lib().orc_fft1d(_ptr(z), len(z), int(inverse))
+    return z
+
+
+def trim(src, dw, dh):
+    src = _f32(src)
+    dst = np.zeros((dh, dw), np.float32)
+    lib().orc_trim(_ptr(dst), dw, dh, _ptr(src), src.shape[1], src.shape[0])
+    return dst
+
+
+def untrim(src, dw, dh):
+    src = _f32(src)
+    dst = np.zeros((dh, dw), np.float32)
+    lib().orc_untrim(_ptr(dst), dw, dh, _ptr(src), src.shape[1], src.shape[0])
+    return dst
+
+
+def good_fft_size(n):
+    return lib().orc_good_fft_size(n)
+
+
+def convolution_size(scale, n, padding):
+    return lib().orc_convolution_size(scale, n, padding)
+
+
+def make_shape_function(scale, max_n, shape=0):
+    n = lib().orc_make_shape_function(scale, max_n, shape, None)
+    out = np.zeros((n, n), np.float32)
+    lib().orc_make_shape_function(scale, max_n, shape, _ptr(out))
+    return out
+
+
+def ms_transform(images, scale, shape=0):
+    images = _f32(images).copy()
+    n, h, w = images.shape
+    lib().orc_ms_transform(_ptr(images), n, w, h, scale, shape)
+    return images
+
+
+def add_shape_component(image, scale, x, y, gain, shape=0):
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    lib().orc_add_shape_component(_ptr(image), image.shape[1], image.shape[0], scale, x, y, gain,
+                                  shape)
