@@ -1,0 +1,220 @@
+/* radler_b200.h — C ABI of the B200-native Radler minor-loop library.
+ *
+ * Drop-in boundary: the reference's plugin interface
+ *   radler::algorithms::DeconvolutionAlgorithm
+ *   (cpp/algorithms/deconvolution_algorithm.h:60-210; virtuals
+ *    ExecuteMajorIteration :69-71 and Clone :73)
+ * The reference has no C ABI of its own; the closest precedent is the flat-array
+ * plugin of PythonDeconvolution (cpp/algorithms/python_deconvolution.cc:171-275).
+ * Every entry point below names the reference interface it replaces. All
+ * pointers are plain; no C++/torch types cross this boundary. Status codes
+ * replace exceptions; rdl_last_error() returns the message a C++ shim re-throws
+ * as std::runtime_error.
+ *
+ * There is NO CPU fallback: every compute entry point fails with
+ * RDL_ERR_NO_DEVICE when no CUDA device (sm_100) is usable.
+ */
+#ifndef RADLER_B200_H_
+#define RADLER_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rdl_handle rdl_handle;
+
+typedef enum {
+  RDL_OK = 0,
+  RDL_ERR_INVALID_ARGUMENT = 1, /* std::runtime_error in the reference (dimension mismatch ...) */
+  RDL_ERR_NO_DEVICE = 2,
+  RDL_ERR_CUDA = 3,
+  RDL_ERR_UNSUPPORTED = 4, /* settings the reference rejects or this build does not cover */
+  RDL_ERR_OUT_OF_MEMORY = 5
+} rdl_status;
+
+/* radler::AlgorithmType (cpp/settings.h) subset on the hot path */
+typedef enum { RDL_GENERIC_CLEAN = 0, RDL_MULTISCALE = 1, RDL_IUWT = 2 } rdl_algorithm;
+/* radler::MultiscaleShape (cpp/settings.h) */
+typedef enum { RDL_SHAPE_TAPERED_QUADRATIC = 0, RDL_SHAPE_GAUSSIAN = 1 } rdl_multiscale_shape;
+/* schaapcommon::fitters::SpectralFittingMode subset */
+typedef enum { RDL_FIT_NONE = 0, RDL_FIT_POLYNOMIAL = 1 } rdl_spectral_mode;
+typedef enum { RDL_MEM_HOST = 0, RDL_MEM_DEVICE = 1 } rdl_memory_space;
+
+/* Construction-time configuration: the constructor arguments of GenericClean
+ * (generic_clean.h: use_sub_minor_optimization), MultiScaleAlgorithm
+ * (multiscale_algorithm.cc:153-163: Settings::Multiscale, beam size, pixel
+ * scales, track_components) and IuwtDeconvolution. */
+typedef struct {
+  int32_t algorithm;                  /* rdl_algorithm */
+  int32_t device;                     /* CUDA device ordinal (new knob, not in the reference) */
+  int32_t use_sub_minor_optimization; /* Settings::Generic, settings.h:527-532 */
+  /* Settings::Multiscale, settings.h:465-524 */
+  int32_t ms_fast_sub_minor_loop;
+  double ms_sub_minor_loop_gain;
+  double ms_scale_bias;
+  uint64_t ms_max_scales;
+  double ms_convolution_padding;
+  const double* ms_scale_list;
+  uint64_t ms_n_scale_list;
+  int32_t ms_shape; /* rdl_multiscale_shape */
+  double beam_size;
+  double pixel_scale_x, pixel_scale_y;
+  int32_t track_components;
+} rdl_config;
+
+/* Fills the reference's defaults (settings.h; deconvolution_algorithm.h:189-202). */
+void rdl_config_default(rdl_config* cfg);
+
+/* Describes an ImageSet (cpp/image_set.h:19-381): images ordered
+ * [deconvolution channel][polarization], all width x height fp32 row-major. */
+typedef struct {
+  uint64_t width, height;
+  uint64_t n_channels;           /* NDeconvolutionChannels() == PsfCount() */
+  uint64_t n_pol;                /* images per channel */
+  const float* channel_weights;  /* ImageSet::weights_ [n_channels]; NULL = all 1 */
+  const uint8_t* pol_linked;     /* [n_pol] 1 if in linked_polarizations (or the set is empty); NULL = all */
+  float pol_norm;                /* polarization_normalization_factor_ (image_set.h:286-313) */
+  int32_t squared_joins;         /* Settings::squared_joins */
+  int32_t memory_space;          /* rdl_memory_space of residual/model/psf pointers */
+} rdl_cube_desc;
+
+/* DeconvolutionResult (deconvolution_algorithm.h:31-58) */
+typedef struct {
+  int32_t has_starting_peak; /* OptionalNumber<float>::has_value */
+  float starting_peak_value;
+  float final_peak_value;
+  int32_t another_iteration_required;
+  int32_t is_diverging;
+  uint64_t iteration_number; /* IterationNumber() after the call */
+} rdl_result;
+
+/* One recorded component, for parity checks of peak sequences. */
+typedef struct {
+  uint32_t iteration;
+  uint32_t scale_index;
+  uint32_t x, y;
+  float value;
+} rdl_trace_entry;
+
+/* MultiScaleAlgorithm::ScaleInfo (multiscale_algorithm.h:58-77) */
+typedef struct {
+  float scale, psf_peak, kernel_peak, bias_factor, gain;
+  float max_normalized_image_value, max_unnormalized_image_value, rms;
+  uint64_t max_x, max_y;
+  int32_t is_active;
+  uint64_t n_components_cleaned;
+  float total_flux_cleaned;
+} rdl_scale_info;
+
+/* ---- lifetime: constructors / Clone() / destructor ------------------------- */
+rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out);
+/* DeconvolutionAlgorithm::Clone (deconvolution_algorithm.h:73): deep copy incl. state */
+rdl_status rdl_clone(const rdl_handle* h, rdl_handle** out);
+void rdl_destroy(rdl_handle* h);
+/* message of the last failing call on this handle (never NULL) */
+const char* rdl_last_error(const rdl_handle* h);
+
+/* ---- setters mirroring DeconvolutionAlgorithm (deconvolution_algorithm.h:75-166) */
+rdl_status rdl_set_max_iterations(rdl_handle* h, uint64_t n);             /* SetMaxIterations */
+rdl_status rdl_set_threshold(rdl_handle* h, float v);                     /* SetThreshold */
+rdl_status rdl_set_major_iteration_threshold(rdl_handle* h, float v);     /* SetMajorIterationThreshold */
+rdl_status rdl_set_minor_loop_gain(rdl_handle* h, float v);               /* SetMinorLoopGain */
+rdl_status rdl_set_major_loop_gain(rdl_handle* h, float v);               /* SetMajorLoopGain */
+rdl_status rdl_set_allow_negative_components(rdl_handle* h, int32_t v);   /* SetAllowNegativeComponents */
+rdl_status rdl_set_stop_on_negative_components(rdl_handle* h, int32_t v); /* SetStopOnNegativeComponents */
+rdl_status rdl_set_clean_border_ratio(rdl_handle* h, float v);            /* SetCleanBorderRatio */
+rdl_status rdl_set_divergence_limit(rdl_handle* h, float v);              /* SetDivergenceLimit */
+rdl_status rdl_set_iteration_number(rdl_handle* h, uint64_t n);           /* SetIterationNumber */
+/* SetCleanMask: non-owning const bool* in the reference; here the mask (width*height
+ * bytes, host memory) is copied to the device at the call. NULL clears it. */
+rdl_status rdl_set_clean_mask(rdl_handle* h, const uint8_t* mask, uint64_t width, uint64_t height);
+/* SetRmsFactorImage (moved-in aocommon::Image); NULL clears it. Host memory. */
+rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t width, uint64_t height);
+/* SetSpectralFitter(unique_ptr<SpectralFitter>, n_polarizations)
+ * (deconvolution_algorithm.h:137-142; fitter built in radler.cc:318-331). */
+rdl_status rdl_set_spectral_fitter(rdl_handle* h, int32_t mode, uint64_t n_terms,
+                                   const double* frequencies, const float* weights,
+                                   uint64_t n_channels, uint64_t n_polarizations);
+/* MultiScaleAlgorithm::SetAutoMaskMode (multiscale_algorithm.h:41-45) */
+rdl_status rdl_set_auto_mask_mode(rdl_handle* h, int32_t track_per_scale_masks,
+                                  int32_t use_per_scale_masks);
+/* record up to `capacity` components of the next calls (0 disables) */
+rdl_status rdl_set_trace_capacity(rdl_handle* h, uint64_t capacity);
+
+/* ---- getters ----------------------------------------------------------------- */
+uint64_t rdl_iteration_number(const rdl_handle* h);             /* IterationNumber */
+uint64_t rdl_scale_count(const rdl_handle* h);                  /* ScaleCount */
+rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* out); /* ScaleSize & co */
+/* GetScaleMask(i): copies width*height bytes to host memory */
+rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out);
+uint64_t rdl_trace_size(const rdl_handle* h);
+uint64_t rdl_trace_get(const rdl_handle* h, rdl_trace_entry* out, uint64_t capacity);
+/* number of pixels the last sub-minor run selected (diagnostic) */
+uint64_t rdl_last_selected_count(const rdl_handle* h);
+/* outer minor-loop passes of the last multiscale call (diagnostic) */
+uint64_t rdl_minor_iteration_count(const rdl_handle* h);
+/* number of kernels this handle has launched so far (bench.py "gpu_launches") */
+uint64_t rdl_kernel_launch_count(const rdl_handle* h);
+
+/* ---- the hot path: DeconvolutionAlgorithm::ExecuteMajorIteration ------------
+ * (deconvolution_algorithm.h:69-71). residual[i], model[i] (i < n_channels*n_pol)
+ * are updated in place; psfs[c] (c < n_channels) are read-only, same size as the
+ * images. With RDL_MEM_HOST the images are staged to HBM and copied back inside
+ * the call; with RDL_MEM_DEVICE they are used where they are. `stream` is a
+ * cudaStream_t (NULL = the handle's own stream). */
+rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* cube,
+                                       float* const* residual, float* const* model,
+                                       const float* const* psfs, void* stream, rdl_result* out);
+
+/* ---- kernel-level entry points (device pointers; used by tests and the roofline
+ * harness, and what a host-side caller can compose itself) ------------------------ */
+
+/* peak_finder::Find / FindWithMask (cpp/math/peak_finder.h:80-127) fused with
+ * ImageSet::GetLinearIntegrated (mode 0) / GetSquareIntegrated (mode 1)
+ * (cpp/image_set.h:131-155) and the optional RMS-factor multiply
+ * (generic_clean.cc:255-277). images: device pointers. found/x/y/value: host outputs. */
+rdl_status rdl_find_peak(rdl_handle* h, const rdl_cube_desc* cube, const float* const* images,
+                         int32_t integration_mode, int32_t allow_negative, uint64_t start_y,
+                         uint64_t end_y, uint64_t horizontal_border, uint64_t vertical_border,
+                         const uint8_t* device_mask, const float* device_rms_factor,
+                         void* stream, int32_t* found, uint64_t* x, uint64_t* y, float* value);
+
+/* ThreadedDeconvolutionTools::SubtractImage for all images of a cube in one launch
+ * (threaded_deconvolution_tools.cc:18-28 -> simple_clean.cc:61-96):
+ * images[i] -= psfs[i / n_pol] shifted to (x, y), times factors[i]. Device pointers;
+ * factors is a host array of n_channels*n_pol floats. */
+rdl_status rdl_subtract_image(rdl_handle* h, const rdl_cube_desc* cube, float* const* images,
+                              const float* const* psfs, uint64_t x, uint64_t y,
+                              const float* factors, void* stream);
+
+/* ImageSet::GetLinearIntegrated / GetSquareIntegrated materialised (device pointers). */
+rdl_status rdl_integrate(rdl_handle* h, const rdl_cube_desc* cube, const float* const* images,
+                         int32_t integration_mode, float* device_dest, void* stream);
+
+/* schaapcommon::math::Convolve (called at multiscale_transforms.cc:21,
+ * subminor_loop.cc:210): in-place circular convolution of n_images device images
+ * (width x height) with one device kernel image prepared by PrepareConvolutionKernel /
+ * PrepareSmallConvolutionKernel. */
+rdl_status rdl_convolve(rdl_handle* h, float* const* images, uint64_t n_images,
+                        const float* device_kernel, uint64_t width, uint64_t height, void* stream);
+
+/* MultiScaleTransforms::Transform (multiscale_transforms.cc:11-23). */
+rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_t n_images,
+                                    uint64_t width, uint64_t height, float scale, int32_t shape,
+                                    void* stream);
+
+/* utils::CalculateGoodFFTSize / GetConvolutionSize (cpp/utils/fft_size_calculations.h:15-50) */
+uint64_t rdl_good_fft_size(uint64_t minimum_size);
+uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);
+
+/* library / device introspection */
+const char* rdl_version(void);
+int32_t rdl_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADLER_B200_H_ */

@@ -1,0 +1,508 @@
+// extern "C" boundary (include/radler_b200.h). Exceptions never cross it: they are
+// turned into status codes + rdl_last_error().
+#include <cmath>
+#include <cstring>
+#include <new>
+
+#include "fft.cuh"
+#include "handle.h"
+#include "multiscale.cuh"
+
+using namespace rdl;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <typename F>
+rdl_status Guard(rdl_handle* h, F&& f) {
+  try {
+    f();
+    return RDL_OK;
+  } catch (const CudaError& e) {
+    if (h) h->error = e.what();
+    cudaGetLastError();
+    return std::strstr(e.what(), "cudaMalloc") ? RDL_ERR_OUT_OF_MEMORY : RDL_ERR_CUDA;
+  } catch (const std::invalid_argument& e) {
+    if (h) h->error = e.what();
+    return RDL_ERR_INVALID_ARGUMENT;
+  } catch (const std::domain_error& e) {
+    if (h) h->error = e.what();
+    return RDL_ERR_UNSUPPORTED;
+  } catch (const std::bad_alloc&) {
+    if (h) h->error = "host allocation failed";
+    return RDL_ERR_OUT_OF_MEMORY;
+  } catch (const std::exception& e) {
+    if (h) h->error = e.what();
+    return RDL_ERR_INVALID_ARGUMENT;
+  }
+}
+
+bool DeviceUsable(int device, std::string& why) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    why = "no CUDA device available (this library has no CPU fallback)";
+    return false;
+  }
+  if (device < 0 || device >= n) {
+    why = "device ordinal out of range";
+    return false;
+  }
+  cudaDeviceProp prop{};
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+    cudaGetLastError();
+    why = "cudaGetDeviceProperties failed";
+    return false;
+  }
+  if (prop.major != 10) {
+    why = std::string("device '") + prop.name + "' is not sm_100 (kernels are built for sm_100a only)";
+    return false;
+  }
+  return true;
+}
+
+void CheckCube(const rdl_cube_desc* c) {
+  if (!c) throw std::invalid_argument("cube descriptor is null");
+  if (c->width == 0 || c->height == 0) throw std::invalid_argument("empty image");
+  if (c->n_channels == 0 || c->n_pol == 0) throw std::invalid_argument("cube has no images");
+  if (c->n_channels * c->n_pol > size_t(kMaxImages))
+    throw std::domain_error("more than 64 images per cube are not supported");
+  if (c->width * c->height >= (1ull << 32))
+    throw std::domain_error("images of 2^32 pixels or more are not supported");
+}
+
+void FillCubeMeta(DeviceCube& cube, const rdl_cube_desc* c) {
+  cube.width = c->width;
+  cube.height = c->height;
+  cube.n_channels = c->n_channels;
+  cube.n_pol = c->n_pol;
+  cube.n_images = c->n_channels * c->n_pol;
+  cube.weights.assign(c->n_channels, 1.0f);
+  if (c->channel_weights) cube.weights.assign(c->channel_weights, c->channel_weights + c->n_channels);
+  cube.pol_linked.assign(c->n_pol, 1);
+  if (c->pol_linked) cube.pol_linked.assign(c->pol_linked, c->pol_linked + c->n_pol);
+  cube.pol_norm = c->pol_norm;
+  cube.squared_joins = c->squared_joins != 0;
+}
+
+bool Aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+void SetVec(DeviceCube& cube) {
+  bool ok = cube.width % 4 == 0;
+  for (size_t i = 0; ok && i != cube.n_images; ++i)
+    ok = Aligned16(cube.residual.p[i]) && (!cube.model.p[i] || Aligned16(cube.model.p[i]));
+  for (size_t i = 0; ok && i != cube.n_channels; ++i)
+    ok = !cube.psf.p[i] || Aligned16(cube.psf.p[i]);
+  cube.vec = ok ? 4 : 1;
+}
+
+cudaStream_t StreamOf(rdl_handle* h, void* stream) {
+  return stream ? static_cast<cudaStream_t>(stream) : h->own_stream;
+}
+
+}  // namespace
+
+extern "C" {
+
+void rdl_config_default(rdl_config* cfg) {
+  std::memset(cfg, 0, sizeof(*cfg));
+  cfg->algorithm = RDL_GENERIC_CLEAN;
+  cfg->device = 0;
+  cfg->use_sub_minor_optimization = 1;
+  cfg->ms_fast_sub_minor_loop = 1;
+  cfg->ms_sub_minor_loop_gain = 0.2;
+  cfg->ms_scale_bias = 0.6;
+  cfg->ms_max_scales = 0;
+  cfg->ms_convolution_padding = 1.1;
+  cfg->ms_shape = RDL_SHAPE_TAPERED_QUADRATIC;
+  cfg->beam_size = 0.0;
+  cfg->pixel_scale_x = cfg->pixel_scale_y = 1.0;
+  cfg->track_components = 0;
+}
+
+rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out) {
+  if (!cfg || !out) return RDL_ERR_INVALID_ARGUMENT;
+  *out = nullptr;
+  std::string why;
+  if (!DeviceUsable(cfg->device, why)) {
+    g_create_error = why;
+    return RDL_ERR_NO_DEVICE;
+  }
+  if (cfg->algorithm != RDL_GENERIC_CLEAN && cfg->algorithm != RDL_MULTISCALE) {
+    g_create_error = "algorithm not supported by this build";
+    return RDL_ERR_UNSUPPORTED;
+  }
+  rdl_handle* h = new (std::nothrow) rdl_handle;
+  if (!h) return RDL_ERR_OUT_OF_MEMORY;
+  h->config = *cfg;
+  if (cfg->ms_scale_list && cfg->ms_n_scale_list)
+    h->ms_scale_list.assign(cfg->ms_scale_list, cfg->ms_scale_list + cfg->ms_n_scale_list);
+  h->config.ms_scale_list = nullptr;
+  h->device = cfg->device;
+  const rdl_status st = Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    RDL_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  });
+  if (st != RDL_OK) {
+    g_create_error = h->error;
+    delete h;
+    return st;
+  }
+  *out = h;
+  return RDL_OK;
+}
+
+rdl_status rdl_clone(const rdl_handle* src, rdl_handle** out) {
+  if (!src || !out) return RDL_ERR_INVALID_ARGUMENT;
+  rdl_config cfg = src->config;
+  cfg.ms_scale_list = src->ms_scale_list.data();
+  cfg.ms_n_scale_list = src->ms_scale_list.size();
+  rdl_status st = rdl_create(&cfg, out);
+  if (st != RDL_OK) return st;
+  rdl_handle* h = *out;
+  st = Guard(h, [&] {
+    h->settings = src->settings;
+    h->iteration_number = src->iteration_number;
+    h->track_per_scale_masks = src->track_per_scale_masks;
+    h->use_per_scale_masks = src->use_per_scale_masks;
+    h->trace_capacity = src->trace_capacity;
+    if (!src->mask_host.empty()) {
+      st = rdl_set_clean_mask(h, src->mask_host.data(), src->mask_w, src->mask_h);
+      if (st != RDL_OK) throw std::runtime_error(h->error);
+    }
+    if (!src->rms_host.empty()) {
+      st = rdl_set_rms_factor_image(h, src->rms_host.data(), src->rms_w, src->rms_h);
+      if (st != RDL_OK) throw std::runtime_error(h->error);
+    }
+    if (src->fit_mode != RDL_FIT_NONE) {
+      st = rdl_set_spectral_fitter(h, src->fit_mode, src->fit_terms, src->fit_freqs.data(),
+                                   src->fit_weights.data(), src->fit_freqs.size(), src->fit_n_pol);
+      if (st != RDL_OK) throw std::runtime_error(h->error);
+    } else {
+      h->fit_n_pol = src->fit_n_pol;
+    }
+    if (src->ms) h->ms = CloneMultiScaleState(*src->ms, h->own_stream);
+  });
+  if (st != RDL_OK) {
+    rdl_destroy(h);
+    *out = nullptr;
+  }
+  return st;
+}
+
+void rdl_destroy(rdl_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  h->ms.reset();
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+const char* rdl_last_error(const rdl_handle* h) {
+  return h ? h->error.c_str() : g_create_error.c_str();
+}
+
+#define RDL_SETTER(name, expr)            \
+  rdl_status name {                       \
+    if (!h) return RDL_ERR_INVALID_ARGUMENT; \
+    expr;                                 \
+    return RDL_OK;                        \
+  }
+RDL_SETTER(rdl_set_max_iterations(rdl_handle* h, uint64_t n), h->settings.max_iterations = n)
+RDL_SETTER(rdl_set_threshold(rdl_handle* h, float v), h->settings.threshold = v)
+RDL_SETTER(rdl_set_major_iteration_threshold(rdl_handle* h, float v),
+           h->settings.major_iteration_threshold = v)
+RDL_SETTER(rdl_set_minor_loop_gain(rdl_handle* h, float v), h->settings.minor_loop_gain = v)
+RDL_SETTER(rdl_set_major_loop_gain(rdl_handle* h, float v), h->settings.major_loop_gain = v)
+RDL_SETTER(rdl_set_allow_negative_components(rdl_handle* h, int32_t v),
+           h->settings.allow_negative_components = v != 0)
+RDL_SETTER(rdl_set_stop_on_negative_components(rdl_handle* h, int32_t v),
+           h->settings.stop_on_negative_component = v != 0)
+RDL_SETTER(rdl_set_clean_border_ratio(rdl_handle* h, float v), h->settings.clean_border_ratio = v)
+RDL_SETTER(rdl_set_divergence_limit(rdl_handle* h, float v), h->settings.divergence_limit = v)
+RDL_SETTER(rdl_set_iteration_number(rdl_handle* h, uint64_t n), h->iteration_number = n)
+RDL_SETTER(rdl_set_trace_capacity(rdl_handle* h, uint64_t n), h->trace_capacity = n)
+RDL_SETTER(rdl_set_auto_mask_mode(rdl_handle* h, int32_t track, int32_t use),
+           (h->track_per_scale_masks = track != 0, h->use_per_scale_masks = use != 0))
+#undef RDL_SETTER
+
+rdl_status rdl_set_clean_mask(rdl_handle* h, const uint8_t* mask, uint64_t width, uint64_t height) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    if (!mask) {
+      h->mask.Free();
+      h->mask_host.clear();
+      h->mask_w = h->mask_h = 0;
+      return;
+    }
+    h->mask_host.assign(mask, mask + width * height);
+    h->mask.Resize(width * height);
+    RDL_CUDA(cudaMemcpy(h->mask.get(), mask, width * height, cudaMemcpyHostToDevice));
+    h->mask_w = width;
+    h->mask_h = height;
+  });
+}
+
+rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t width,
+                                    uint64_t height) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    if (!image) {
+      h->rms.Free();
+      h->rms_host.clear();
+      h->rms_w = h->rms_h = 0;
+      return;
+    }
+    h->rms_host.assign(image, image + width * height);
+    h->rms.Resize(width * height);
+    RDL_CUDA(cudaMemcpy(h->rms.get(), image, width * height * sizeof(float),
+                        cudaMemcpyHostToDevice));
+    h->rms_w = width;
+    h->rms_h = height;
+  });
+}
+
+rdl_status rdl_set_spectral_fitter(rdl_handle* h, int32_t mode, uint64_t n_terms,
+                                   const double* frequencies, const float* weights,
+                                   uint64_t n_channels, uint64_t n_polarizations) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    if (mode != RDL_FIT_NONE && mode != RDL_FIT_POLYNOMIAL)
+      throw std::domain_error("only kNoFitting and kPolynomial spectral fitting are supported");
+    if (n_polarizations == 0) throw std::invalid_argument("n_polarizations must be >= 1");
+    h->fit_mode = mode;
+    h->fit_terms = n_terms;
+    h->fit_n_pol = n_polarizations;
+    h->fit_freqs.clear();
+    h->fit_weights.clear();
+    h->projection_host.clear();
+    if (mode == RDL_FIT_NONE) return;
+    if (!frequencies || n_channels == 0 || n_channels > size_t(kMaxImages))
+      throw std::invalid_argument("spectral fitter needs 1..64 channel frequencies");
+    h->fit_freqs.assign(frequencies, frequencies + n_channels);
+    h->fit_weights.assign(n_channels, 1.0f);
+    if (weights) h->fit_weights.assign(weights, weights + n_channels);
+    h->projection_host = PolynomialProjection(n_terms, h->fit_freqs, h->fit_weights);
+    RDL_CUDA(cudaSetDevice(h->device));
+    h->projection.Resize(h->projection_host.size());
+    RDL_CUDA(cudaMemcpy(h->projection.get(), h->projection_host.data(),
+                        h->projection_host.size() * sizeof(double), cudaMemcpyHostToDevice));
+  });
+}
+
+uint64_t rdl_iteration_number(const rdl_handle* h) { return h ? h->iteration_number : 0; }
+uint64_t rdl_trace_size(const rdl_handle* h) { return h ? h->trace_host.size() : 0; }
+uint64_t rdl_trace_get(const rdl_handle* h, rdl_trace_entry* out, uint64_t capacity) {
+  if (!h || !out) return 0;
+  const uint64_t n = std::min<uint64_t>(capacity, h->trace_host.size());
+  static_assert(sizeof(rdl_trace_entry) == sizeof(TraceEntry), "trace layout");
+  std::memcpy(out, h->trace_host.data(), n * sizeof(TraceEntry));
+  return n;
+}
+uint64_t rdl_last_selected_count(const rdl_handle* h) { return h ? h->last_selected : 0; }
+uint64_t rdl_minor_iteration_count(const rdl_handle* h) { return h ? h->minor_iterations : 0; }
+uint64_t rdl_kernel_launch_count(const rdl_handle* h) { return h ? h->launches : 0; }
+
+uint64_t rdl_scale_count(const rdl_handle* h) { return h && h->ms ? MultiScaleScaleCount(*h->ms) : 0; }
+rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* out) {
+  if (!h || !out || !h->ms || i >= MultiScaleScaleCount(*h->ms)) return RDL_ERR_INVALID_ARGUMENT;
+  *out = MultiScaleScaleInfo(*h->ms, i);
+  return RDL_OK;
+}
+rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out) {
+  if (!h || !out || !h->ms) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(const_cast<rdl_handle*>(h), [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    MultiScaleCopyScaleMask(*h->ms, i, out);
+  });
+}
+
+rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
+                                       float* const* residual, float* const* model,
+                                       const float* const* psfs, void* stream_v, rdl_result* out) {
+  if (!h || !out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    CheckCube(c);
+    if (!residual || !model || !psfs) throw std::invalid_argument("null image table");
+    if (h->mask.get() && (h->mask_w != c->width || h->mask_h != c->height))
+      throw std::invalid_argument("clean mask dimensions do not match the image");
+    if (h->rms.get() && (h->rms_w != c->width || h->rms_h != c->height))
+      throw std::invalid_argument("Error in RMS factor image dimensions!");
+    if (h->fit_mode == RDL_FIT_POLYNOMIAL &&
+        (h->fit_freqs.size() != c->n_channels || h->fit_n_pol != c->n_pol))
+      throw std::invalid_argument("spectral fitter channel/polarisation count does not match the cube");
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    DeviceCube cube;
+    FillCubeMeta(cube, c);
+    const size_t n = cube.Pixels(), bytes = n * sizeof(float);
+    const bool host = c->memory_space == RDL_MEM_HOST;
+    if (host) {
+      h->stage_residual.Reserve(cube.n_images * n);
+      h->stage_model.Reserve(cube.n_images * n);
+      h->stage_psf.Reserve(cube.n_channels * n);
+      for (size_t i = 0; i != cube.n_images; ++i) {
+        cube.residual.p[i] = h->stage_residual.get() + i * n;
+        cube.model.p[i] = h->stage_model.get() + i * n;
+        RDL_CUDA(cudaMemcpyAsync(cube.residual.p[i], residual[i], bytes, cudaMemcpyHostToDevice, stream));
+        RDL_CUDA(cudaMemcpyAsync(cube.model.p[i], model[i], bytes, cudaMemcpyHostToDevice, stream));
+      }
+      for (size_t i = 0; i != cube.n_channels; ++i) {
+        float* dst = h->stage_psf.get() + i * n;
+        RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], bytes, cudaMemcpyHostToDevice, stream));
+        cube.psf.p[i] = dst;
+      }
+    } else {
+      for (size_t i = 0; i != cube.n_images; ++i) {
+        cube.residual.p[i] = residual[i];
+        cube.model.p[i] = model[i];
+      }
+      for (size_t i = 0; i != cube.n_channels; ++i) cube.psf.p[i] = psfs[i];
+    }
+    SetVec(cube);
+    rdl_result r{};
+    if (h->config.algorithm == RDL_GENERIC_CLEAN)
+      r = RunGenericClean(*h, cube, stream);
+    else
+      r = RunMultiScale(*h, cube, stream);
+    if (host) {
+      for (size_t i = 0; i != cube.n_images; ++i) {
+        RDL_CUDA(cudaMemcpyAsync(residual[i], cube.residual.p[i], bytes, cudaMemcpyDeviceToHost, stream));
+        RDL_CUDA(cudaMemcpyAsync(model[i], cube.model.p[i], bytes, cudaMemcpyDeviceToHost, stream));
+      }
+    }
+    RDL_CUDA(cudaStreamSynchronize(stream));
+    *out = r;
+  });
+}
+
+rdl_status rdl_find_peak(rdl_handle* h, const rdl_cube_desc* c, const float* const* images,
+                         int32_t integration_mode, int32_t allow_negative, uint64_t start_y,
+                         uint64_t end_y, uint64_t horizontal_border, uint64_t vertical_border,
+                         const uint8_t* device_mask, const float* device_rms_factor,
+                         void* stream_v, int32_t* found, uint64_t* x, uint64_t* y, float* value) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    CheckCube(c);
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    DeviceCube cube;
+    FillCubeMeta(cube, c);
+    ConstPtrTable t{};
+    for (size_t i = 0; i != cube.n_images; ++i) {
+      t.p[i] = images[i];
+      cube.residual.p[i] = const_cast<float*>(images[i]);
+    }
+    SetVec(cube);
+    const IntegSpec spec = integration_mode == 0 ? MakeLinearSpec(cube) : MakeSquareSpec(cube);
+    const PeakWindow w = MakePeakWindow(cube.width, cube.height, start_y, end_y, horizontal_border,
+                                        vertical_border, device_mask, device_rms_factor,
+                                        allow_negative != 0);
+    h->key.Reserve(1);
+    LaunchFindPeak(spec, t, int(cube.width), int(cube.height), w, h->key.get(), cube.vec, stream);
+    ++h->launches;
+    unsigned long long key = 0;
+    RDL_CUDA(cudaMemcpyAsync(&key, h->key.get(), sizeof(key), cudaMemcpyDeviceToHost, stream));
+    RDL_CUDA(cudaStreamSynchronize(stream));
+    float v = 0.0f;
+    uint32_t index = 0;
+    const bool has = DecodePeakKey(key, v, index);
+    if (found) *found = has;
+    if (x) *x = has ? index % cube.width : cube.width;
+    if (y) *y = has ? index / cube.width : cube.height;
+    if (value) *value = has ? v : 0.0f;
+  });
+}
+
+rdl_status rdl_subtract_image(rdl_handle* h, const rdl_cube_desc* c, float* const* images,
+                              const float* const* psfs, uint64_t x, uint64_t y,
+                              const float* factors, void* stream_v) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    CheckCube(c);
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    const size_t n_images = c->n_channels * c->n_pol;
+    PtrTable img{};
+    ConstPtrTable psf{};
+    for (size_t i = 0; i != n_images; ++i) {
+      img.p[i] = images[i];
+      psf.p[i] = psfs[i / c->n_pol];
+    }
+    LaunchSubtract(img, psf, int(n_images), int(c->width), int(c->height), int(x), int(y), factors,
+                   stream);
+    ++h->launches;
+    RDL_CUDA(cudaGetLastError());
+  });
+}
+
+rdl_status rdl_integrate(rdl_handle* h, const rdl_cube_desc* c, const float* const* images,
+                         int32_t integration_mode, float* device_dest, void* stream_v) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    CheckCube(c);
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    DeviceCube cube;
+    FillCubeMeta(cube, c);
+    ConstPtrTable t{};
+    for (size_t i = 0; i != cube.n_images; ++i) {
+      t.p[i] = images[i];
+      cube.residual.p[i] = const_cast<float*>(images[i]);
+    }
+    SetVec(cube);
+    const int vec = cube.vec == 4 && Aligned16(device_dest) ? 4 : 1;
+    const IntegSpec spec = integration_mode == 0 ? MakeLinearSpec(cube) : MakeSquareSpec(cube);
+    LaunchIntegrate(spec, t, cube.Pixels(), device_dest, vec, stream);
+    ++h->launches;
+    RDL_CUDA(cudaGetLastError());
+  });
+}
+
+rdl_status rdl_convolve(rdl_handle* h, float* const* images, uint64_t n_images,
+                        const float* device_kernel, uint64_t width, uint64_t height,
+                        void* stream_v) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    FftConvolver& conv = GetConvolver(*h, width, height);
+    conv.SetKernel(device_kernel, stream);
+    for (uint64_t i = 0; i != n_images; ++i) conv.Convolve(images[i], images[i], stream);
+    h->launches += conv.TakeLaunchCount();
+    RDL_CUDA(cudaGetLastError());
+  });
+}
+
+rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_t n_images,
+                                    uint64_t width, uint64_t height, float scale, int32_t shape,
+                                    void* stream_v) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    MultiScaleTransform(*h, images, n_images, width, height, scale, shape, stream);
+    RDL_CUDA(cudaGetLastError());
+  });
+}
+
+uint64_t rdl_good_fft_size(uint64_t minimum_size) { return CalculateGoodFFTSize(minimum_size); }
+uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding) {
+  return GetConvolutionSize(convolution_scale, original_size, padding);
+}
+
+const char* rdl_version(void) { return "radler_b200 0.1 (sm_100a)"; }
+
+int32_t rdl_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+}  // extern "C"

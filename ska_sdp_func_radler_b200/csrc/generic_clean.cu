@@ -1,0 +1,120 @@
+// GenericClean::ExecuteMajorIteration on the device (generic_clean.cc:56-253).
+// Path B (use_sub_minor_optimization = false): the FindPeak -> fit -> SubtractImage ->
+// re-integrate loop runs as a chain of fused HogbomStepKernel launches; the host only
+// polls the device-side control block once per batch of launches.
+// Path A (sub-minor optimisation) lives in subminor.cu.
+#include <algorithm>
+#include <cmath>
+
+#include "handle.h"
+#include "subminor.cuh"
+
+namespace rdl {
+
+namespace {
+
+struct PinnedState {
+  CleanState* p = nullptr;
+  PinnedState() { RDL_CUDA(cudaMallocHost(&p, sizeof(CleanState))); }
+  ~PinnedState() { cudaFreeHost(p); }
+};
+
+rdl_result FinishResult(const rdl_handle& h, const CleanState& s, uint64_t iteration_at_start) {
+  // generic_clean.cc:75-88, 208-252
+  rdl_result r{};
+  r.has_starting_peak = s.has_start;
+  r.starting_peak_value = s.has_start ? s.start_value : 0.0f;
+  r.final_peak_value = r.starting_peak_value;
+  r.iteration_number = s.iteration;
+  if (s.done == 2 || s.done == 3) return r;  // no peak / no iterations left
+  if (s.diverging) {
+    if (s.has_peak) r.final_peak_value = s.max_value;
+    r.another_iteration_required = 0;
+    r.is_diverging = 1;
+  } else if (s.has_peak) {
+    const float v = s.max_value;
+    const bool final_threshold_reached = std::fabs(v) <= h.settings.threshold || v == 0.0f;
+    const bool negative_reached = v < 0.0f && h.settings.stop_on_negative_component;
+    const bool mgain_reached = std::fabs(v) <= s.major_iter_threshold;
+    const bool did_work = (s.iteration - iteration_at_start) != 0;
+    r.another_iteration_required =
+        mgain_reached && did_work && !negative_reached && !final_threshold_reached;
+    r.final_peak_value = v;
+  } else {
+    r.another_iteration_required = 0;
+  }
+  return r;
+}
+
+}  // namespace
+
+rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream) {
+  if (h.settings.stop_on_negative_component) h.settings.allow_negative_components = true;
+  const size_t width = cube.width, height = cube.height;
+  const uint64_t iteration_at_start = h.iteration_number;
+
+  if (h.config.use_sub_minor_optimization) return RunGenericCleanSubMinor(h, cube, stream);
+
+  HogbomParams p{};
+  p.img = cube.residual;
+  p.model = cube.model;
+  for (size_t i = 0; i != cube.n_images; ++i) p.psf.p[i] = cube.psf.p[cube.PsfIndex(i)];
+  p.first_spec = MakeLinearSpec(cube);
+  p.step_spec = MakeSquareSpec(cube);
+  p.simple_first = IsSimpleSpec(p.first_spec, cube.n_images);
+  p.simple_step = IsSimpleSpec(p.step_spec, cube.n_images);
+  // peak_finder.h:99-107: borders = round(size * ratio)
+  const size_t hb = size_t(std::round(width * h.settings.clean_border_ratio));
+  const size_t vb = size_t(std::round(height * h.settings.clean_border_ratio));
+  p.window = MakePeakWindow(width, height, 0, height, hb, vb, h.mask.get(), h.rms.get(),
+                            h.settings.allow_negative_components);
+  p.n_images = int(cube.n_images);
+  p.width = int(width);
+  p.height = int(height);
+  p.threshold = h.settings.threshold;
+  p.major_iteration_threshold = h.settings.major_iteration_threshold;
+  p.gain = h.settings.minor_loop_gain;
+  p.mgain = h.settings.major_loop_gain;
+  p.divergence_limit = h.settings.divergence_limit;
+  p.stop_on_negative = h.settings.stop_on_negative_component;
+  p.max_iterations = h.settings.max_iterations;
+  p.projection = h.fit_mode == RDL_FIT_POLYNOMIAL ? h.projection.get() : nullptr;
+  p.n_fit = int(h.fit_freqs.size());
+  p.n_pol = int(cube.n_pol);
+  h.trace_dev.Reserve(std::max<uint64_t>(h.trace_capacity, 1));
+  p.trace = h.trace_dev.get();
+  p.trace_capacity = h.trace_capacity;
+
+  h.state.Reserve(1);
+  PinnedState host;
+  *host.p = CleanState{};
+  host.p->iteration = h.iteration_number;
+  RDL_CUDA(cudaMemcpyAsync(h.state.get(), host.p, sizeof(CleanState), cudaMemcpyHostToDevice,
+                           stream));
+  LaunchHogbomStep(p, h.state.get(), true, cube.vec, stream);
+  ++h.launches;
+
+  // Batch size: about a millisecond of device work between polls.
+  const double bytes_per_iteration = 12.0 * double(cube.n_images) * double(cube.Pixels());
+  const double t_iteration = std::max(bytes_per_iteration / 6.0e12, 3.0e-6);
+  const int batch = int(std::clamp(1.0e-3 / t_iteration, 8.0, 256.0));
+  for (;;) {
+    RDL_CUDA(cudaMemcpyAsync(host.p, h.state.get(), sizeof(CleanState), cudaMemcpyDeviceToHost,
+                             stream));
+    RDL_CUDA(cudaStreamSynchronize(stream));
+    if (host.p->done) break;
+    for (int b = 0; b != batch; ++b) LaunchHogbomStep(p, h.state.get(), false, cube.vec, stream);
+    h.launches += batch;
+    RDL_CUDA(cudaGetLastError());
+  }
+  const CleanState s = *host.p;
+  h.iteration_number = s.iteration;
+  h.trace_host.resize(s.n_trace);
+  if (s.n_trace)
+    RDL_CUDA(cudaMemcpyAsync(h.trace_host.data(), h.trace_dev.get(),
+                             s.n_trace * sizeof(TraceEntry), cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+  return FinishResult(h, s, iteration_at_start);
+}
+
+}  // namespace rdl

@@ -1,0 +1,158 @@
+// Host-side state of one algorithm instance (the analogue of a
+// radler::algorithms::DeconvolutionAlgorithm object, deconvolution_algorithm.h:60-210).
+#ifndef RDL_HANDLE_H_
+#define RDL_HANDLE_H_
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/radler_b200.h"
+#include "clean_kernels.cuh"
+#include "common.cuh"
+
+namespace rdl {
+
+// RAII device allocation.
+template <typename T>
+class DeviceBuffer {
+ public:
+  DeviceBuffer() = default;
+  explicit DeviceBuffer(size_t n) { Resize(n); }
+  DeviceBuffer(const DeviceBuffer&) = delete;
+  DeviceBuffer& operator=(const DeviceBuffer&) = delete;
+  DeviceBuffer(DeviceBuffer&& o) noexcept : ptr_(o.ptr_), n_(o.n_) { o.ptr_ = nullptr; o.n_ = 0; }
+  DeviceBuffer& operator=(DeviceBuffer&& o) noexcept {
+    if (this != &o) {
+      Free();
+      ptr_ = o.ptr_;
+      n_ = o.n_;
+      o.ptr_ = nullptr;
+      o.n_ = 0;
+    }
+    return *this;
+  }
+  ~DeviceBuffer() { Free(); }
+  void Resize(size_t n) {
+    if (n == n_) return;
+    Free();
+    if (n) {
+      cudaError_t e = cudaMalloc(&ptr_, n * sizeof(T));
+      if (e != cudaSuccess) {
+        ptr_ = nullptr;
+        throw CudaError(std::string("cudaMalloc(") + std::to_string(n * sizeof(T)) +
+                        " bytes): " + cudaGetErrorString(e));
+      }
+    }
+    n_ = n;
+  }
+  // Grow-only variant for scratch space.
+  void Reserve(size_t n) {
+    if (n > n_) Resize(n);
+  }
+  void Free() {
+    if (ptr_) cudaFree(ptr_);
+    ptr_ = nullptr;
+    n_ = 0;
+  }
+  T* get() const { return ptr_; }
+  size_t size() const { return n_; }
+  bool empty() const { return n_ == 0; }
+
+ private:
+  T* ptr_ = nullptr;
+  size_t n_ = 0;
+};
+
+// The cube an ExecuteMajorIteration call works on, resident in HBM.
+struct DeviceCube {
+  size_t width = 0, height = 0, n_channels = 0, n_pol = 0, n_images = 0;
+  std::vector<float> weights;
+  std::vector<uint8_t> pol_linked;
+  float pol_norm = 1.0f;
+  bool squared_joins = false;
+  PtrTable residual{}, model{};
+  ConstPtrTable psf{};  // per channel
+  int vec = 1;          // 4 when width % 4 == 0 and all pointers are 16-byte aligned
+  size_t PsfIndex(size_t image) const { return image / n_pol; }
+  size_t Pixels() const { return width * height; }
+};
+
+// Builds the integration recipes of image_set.cc for a cube.
+IntegSpec MakeLinearSpec(const DeviceCube& cube);  // GetLinearIntegrated
+IntegSpec MakeSquareSpec(const DeviceCube& cube);  // GetSquareIntegrated
+IntegSpec MakeIntegratedPsfSpec(const DeviceCube& cube);  // GetIntegratedPsf, over channels
+bool IsSimpleSpec(const IntegSpec& spec, size_t n_images);
+
+// Polynomial projection matrix (spectral fit restated).
+std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
+                                         const std::vector<float>& weights);
+
+struct Settings {  // deconvolution_algorithm.h:189-202
+  float threshold = 0.0f;
+  float major_iteration_threshold = 0.0f;
+  float minor_loop_gain = 0.1f;
+  float major_loop_gain = 1.0f;
+  float clean_border_ratio = 0.05f;
+  uint64_t max_iterations = 500;
+  float divergence_limit = 4.0f;
+  bool allow_negative_components = true;
+  bool stop_on_negative_component = false;
+};
+
+class MultiScaleState;
+
+}  // namespace rdl
+
+struct rdl_handle {
+  rdl_config config{};
+  std::vector<double> ms_scale_list;
+  rdl::Settings settings;
+  uint64_t iteration_number = 0;
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  std::string error;
+  uint64_t launches = 0;
+
+  // clean mask / rms factor image (device copies) + host copies for Clone()
+  rdl::DeviceBuffer<uint8_t> mask;
+  std::vector<uint8_t> mask_host;
+  size_t mask_w = 0, mask_h = 0;
+  rdl::DeviceBuffer<float> rms;
+  std::vector<float> rms_host;
+  size_t rms_w = 0, rms_h = 0;
+
+  // spectral fitter
+  int32_t fit_mode = RDL_FIT_NONE;
+  uint64_t fit_terms = 0, fit_n_pol = 1;
+  std::vector<double> fit_freqs;
+  std::vector<float> fit_weights;
+  std::vector<double> projection_host;
+  rdl::DeviceBuffer<double> projection;
+
+  // auto-mask mode (multiscale)
+  bool track_per_scale_masks = false, use_per_scale_masks = false;
+
+  // trace
+  uint64_t trace_capacity = 0;
+  rdl::DeviceBuffer<rdl::TraceEntry> trace_dev;
+  std::vector<rdl::TraceEntry> trace_host;
+
+  // loop control block + scratch
+  rdl::DeviceBuffer<rdl::CleanState> state;
+  rdl::DeviceBuffer<unsigned long long> key;
+  uint64_t last_selected = 0;
+  uint64_t minor_iterations = 0;
+
+  // staging for RDL_MEM_HOST calls
+  rdl::DeviceBuffer<float> stage_residual, stage_model, stage_psf;
+
+  std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
+};
+
+namespace rdl {
+rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream);
+rdl_result RunMultiScale(rdl_handle& h, DeviceCube& cube, cudaStream_t stream);
+}  // namespace rdl
+
+#endif

@@ -1,0 +1,18 @@
+// MultiScaleAlgorithm on the device (algorithms/multiscale_algorithm.{h,cc}).
+#ifndef RDL_MULTISCALE_CUH_
+#define RDL_MULTISCALE_CUH_
+
+#include <memory>
+
+#include "handle.h"
+
+namespace rdl {
+std::shared_ptr<MultiScaleState> CloneMultiScaleState(const MultiScaleState& src,
+                                                      cudaStream_t stream);
+uint64_t MultiScaleScaleCount(const MultiScaleState& s);
+rdl_scale_info MultiScaleScaleInfo(const MultiScaleState& s, uint64_t i);
+void MultiScaleCopyScaleMask(const MultiScaleState& s, uint64_t i, uint8_t* out_host);
+void MultiScaleTransform(rdl_handle& h, float* const* images, uint64_t n_images, uint64_t width,
+                         uint64_t height, float scale, int32_t shape, cudaStream_t stream);
+}  // namespace rdl
+#endif
