@@ -18,11 +18,82 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 
+_REF_PATH = os.path.join(_HERE, "_ref", "libradler_ref.so")
+_REFERENCE_ROOT = "/root/reference"
+
+
 def build(force: bool = False) -> str:
     """Compile liboracle.so (and oracle/_ref when /root/reference exists)."""
     if force or not os.path.exists(_LIB_PATH):
         subprocess.run(["make", "-C", _HERE, "-B" if force else "-s", "liboracle.so"], check=True)
+    if os.path.isdir(os.path.join(_REFERENCE_ROOT, "cpp")) and (force or not os.path.exists(_REF_PATH)):
+        subprocess.run(["make", "-C", _HERE, "-s", "ref"], check=True)
     return _LIB_PATH
+
+
+_ref = None
+
+
+def ref_lib():
+    """oracle/_ref/libradler_ref.so: the reference's own peak_finder.cc, simple_clean.cc and
+    dijkstra_splitter.cc compiled where they lie. None when it was never built (it is
+    prebuilt in the dev container and travels to the GPU box as a built file)."""
+    global _ref
+    if _ref is None:
+        if not os.path.exists(_REF_PATH):
+            if not os.path.isdir(os.path.join(_REFERENCE_ROOT, "cpp")):
+                return None
+            build()
+        L = C.CDLL(_REF_PATH)
+        u64, vp = C.c_uint64, C.c_void_p
+        L.ref_find_peak.restype = C.c_int32
+        L.ref_find_peak.argtypes = [C.c_int32, vp, u64, u64, C.c_int32, u64, u64, u64, u64, vp,
+                                    C.POINTER(u64), C.POINTER(u64), C.POINTER(C.c_float)]
+        L.ref_subtract_image.argtypes = [vp, vp, u64, u64, u64, u64, C.c_float]
+        L.ref_partial_subtract_image.argtypes = [vp, u64, u64, vp, u64, u64, u64, u64, C.c_float,
+                                                 u64, u64]
+        L.ref_good_fft_size.restype = u64
+        L.ref_good_fft_size.argtypes = [u64]
+        L.ref_convolution_size.restype = u64
+        L.ref_convolution_size.argtypes = [C.c_double, u64, C.c_double]
+        for n in ["ref_divide_vertically", "ref_divide_horizontally"]:
+            getattr(L, n).argtypes = [vp, vp, u64, u64, u64, u64]
+        for n in ["ref_add_vertical_divider", "ref_add_horizontal_divider"]:
+            getattr(L, n).argtypes = [vp, vp, vp, u64, u64, u64, u64]
+        for n in ["ref_flood_vertical_area", "ref_flood_horizontal_area"]:
+            getattr(L, n).argtypes = [vp, u64, u64, u64, vp, C.POINTER(u64), C.POINTER(u64)]
+        L.ref_get_bounding_mask.argtypes = [vp, u64, u64, u64, u64, vp, vp] + [C.POINTER(u64)] * 4
+        _ref = L
+    return _ref
+
+
+def ref_find_peak(image, variant=1, allow_negative=True, start_y=0, end_y=None, h_border=0,
+                  v_border=0, mask=None):
+    """Reference peak_finder: variant 0 Simple, 1 Avx, 2 FindWithMask."""
+    image = np.ascontiguousarray(image, np.float32)
+    h, w = image.shape
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    x, y, v = C.c_uint64(), C.c_uint64(), C.c_float()
+    found = ref_lib().ref_find_peak(variant, image.ctypes.data, w, h, int(allow_negative), start_y,
+                                    h if end_y is None else end_y, h_border, v_border,
+                                    None if m is None else m.ctypes.data, C.byref(x), C.byref(y),
+                                    C.byref(v))
+    return (v.value if found else None), x.value, y.value
+
+
+def ref_partial_subtract_image(image, psf, x, y, factor, start_y, end_y):
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    psf = np.ascontiguousarray(psf, np.float32)
+    ref_lib().ref_partial_subtract_image(image.ctypes.data, image.shape[1], image.shape[0],
+                                         psf.ctypes.data, psf.shape[1], psf.shape[0], x, y, factor,
+                                         start_y, end_y)
+
+
+def ref_subtract_image(image, psf, x, y, factor):
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    psf = np.ascontiguousarray(psf, np.float32)
+    ref_lib().ref_subtract_image(image.ctypes.data, psf.ctypes.data, image.shape[1],
+                                 image.shape[0], x, y, factor)
 
 
 class _Cube(C.Structure):
@@ -304,6 +375,16 @@ def subtract_image(image, psf, x, y, factor):
     psf = _f32(psf)
     h, w = image.shape
     lib().orc_subtract_image(_ptr(image), _ptr(psf), w, h, x, y, factor)
+
+
+def subtract_image_whole(image, psf, x, y, factor):
+    """simple_clean::SubtractImage (simple_clean.cc:17-59), incl. the dropped odd column."""
+    assert image.dtype == np.float32 and image.flags.c_contiguous
+    psf = _f32(psf)
+    h, w = image.shape
+    f = lib().orc_subtract_image_whole
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_float]
+    f(_ptr(image), _ptr(psf), w, h, x, y, factor)
 
 
 def partial_subtract_image(image, psf, x, y, factor, start_y, end_y):

@@ -232,6 +232,12 @@ void orc_subtract_image(float* image, const float* psf, uint64_t w, uint64_t h, 
   ThreadedSubtractImage(image, p, x, y, factor);
 }
 
+// simple_clean::SubtractImage (non-partial; drops the odd last column, quirk A7)
+void orc_subtract_image_whole(float* image, const float* psf, uint64_t w, uint64_t h, uint64_t x,
+                              uint64_t y, float factor) {
+  SubtractImageWhole(image, psf, w, h, x, y, factor);
+}
+
 void orc_partial_subtract_image(float* image, uint64_t iw, uint64_t ih, const float* psf,
                                 uint64_t pw, uint64_t ph, uint64_t x, uint64_t y, float factor,
                                 uint64_t start_y, uint64_t end_y) {

@@ -1,0 +1,106 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.
+// extern "C" wrappers around the reference's OWN leaf sources, compiled where they lie
+// under /root/reference (see Makefile target `ref`): cpp/math/peak_finder.cc,
+// cpp/algorithms/simple_clean.cc, cpp/math/dijkstra_splitter.cc and the header-only
+// cpp/utils/fft_size_calculations.h. The rest of the reference cannot be built here
+// (aocommon / schaapcommon submodules are empty, FFTW/Boost/GSL/casacore are absent).
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "algorithms/simple_clean.h"
+#include "math/dijkstra_splitter.h"
+#include "math/peak_finder.h"
+#include "utils/fft_size_calculations.h"
+
+using namespace radler;
+
+extern "C" {
+
+// variant: 0 = Simple, 1 = Avx (what Find dispatches to on an AVX build), 2 = FindWithMask
+int ref_find_peak(int variant, const float* image, uint64_t w, uint64_t h, int allow_negative,
+                  uint64_t start_y, uint64_t end_y, uint64_t hb, uint64_t vb,
+                  const uint8_t* mask, uint64_t* x, uint64_t* y, float* value) {
+  size_t px = 0, py = 0;
+  aocommon::OptionalNumber<float> r;
+  if (variant == 2)
+    r = math::peak_finder::FindWithMask(image, w, h, px, py, allow_negative != 0, start_y, end_y,
+                                        reinterpret_cast<const bool*>(mask), size_t(hb),
+                                        size_t(vb));
+  else if (variant == 1)
+    r = math::peak_finder::Avx(image, w, h, px, py, allow_negative != 0, start_y, end_y, hb, vb);
+  else
+    r = math::peak_finder::Simple(image, w, h, px, py, allow_negative != 0, start_y, end_y, hb,
+                                  vb);
+  *x = px;
+  *y = py;
+  *value = r.ValueOr(0.0f);
+  return r.HasValue() ? 1 : 0;
+}
+
+void ref_subtract_image(float* image, const float* psf, uint64_t w, uint64_t h, uint64_t x,
+                        uint64_t y, float factor) {
+  algorithms::simple_clean::SubtractImage(image, psf, w, h, x, y, factor);
+}
+
+void ref_partial_subtract_image(float* image, uint64_t iw, uint64_t ih, const float* psf,
+                                uint64_t pw, uint64_t ph, uint64_t x, uint64_t y, float factor,
+                                uint64_t start_y, uint64_t end_y) {
+  if (iw == pw && ih == ph)
+    algorithms::simple_clean::PartialSubtractImage(image, psf, iw, ih, x, y, factor, start_y,
+                                                   end_y);
+  else
+    algorithms::simple_clean::PartialSubtractImage(image, iw, ih, psf, pw, ph, x, y, factor,
+                                                   start_y, end_y);
+}
+
+uint64_t ref_good_fft_size(uint64_t n) { return utils::CalculateGoodFFTSize(n); }
+uint64_t ref_convolution_size(double scale, uint64_t n, double padding) {
+  return utils::GetConvolutionSize(scale, n, padding);
+}
+
+void ref_divide_vertically(const float* image, float* output, uint64_t w, uint64_t h,
+                           uint64_t x1, uint64_t x2) {
+  math::DijkstraSplitter(w, h).DivideVertically(image, output, x1, x2);
+}
+void ref_divide_horizontally(const float* image, float* output, uint64_t w, uint64_t h,
+                             uint64_t y1, uint64_t y2) {
+  math::DijkstraSplitter(w, h).DivideHorizontally(image, output, y1, y2);
+}
+void ref_add_vertical_divider(const float* image, float* scratch, float* output, uint64_t w,
+                              uint64_t h, uint64_t x1, uint64_t x2) {
+  math::DijkstraSplitter(w, h).AddVerticalDivider(image, scratch, output, x1, x2);
+}
+void ref_add_horizontal_divider(const float* image, float* scratch, float* output, uint64_t w,
+                                uint64_t h, uint64_t y1, uint64_t y2) {
+  math::DijkstraSplitter(w, h).AddHorizontalDivider(image, scratch, output, y1, y2);
+}
+void ref_flood_vertical_area(const float* subdivision, uint64_t w, uint64_t h, uint64_t sub_x,
+                             uint8_t* mask, uint64_t* x, uint64_t* subwidth) {
+  size_t ox = 0, ow = 0;
+  math::DijkstraSplitter(w, h).FloodVerticalArea(subdivision, sub_x,
+                                                 reinterpret_cast<bool*>(mask), ox, ow);
+  *x = ox;
+  *subwidth = ow;
+}
+void ref_flood_horizontal_area(const float* subdivision, uint64_t w, uint64_t h, uint64_t sub_y,
+                               uint8_t* mask, uint64_t* y, uint64_t* subheight) {
+  size_t oy = 0, oh = 0;
+  math::DijkstraSplitter(w, h).FloodHorizontalArea(subdivision, sub_y,
+                                                   reinterpret_cast<bool*>(mask), oy, oh);
+  *y = oy;
+  *subheight = oh;
+}
+void ref_get_bounding_mask(const uint8_t* vertical_mask, uint64_t w, uint64_t h, uint64_t vx,
+                           uint64_t vw, const uint8_t* horizontal_mask, uint8_t* mask,
+                           uint64_t* sub_x, uint64_t* sub_y, uint64_t* sub_w, uint64_t* sub_h) {
+  size_t x = 0, y = 0, sw = 0, sh = 0;
+  math::DijkstraSplitter(w, h).GetBoundingMask(reinterpret_cast<const bool*>(vertical_mask), vx,
+                                               vw, reinterpret_cast<const bool*>(horizontal_mask),
+                                               reinterpret_cast<bool*>(mask), x, y, sw, sh);
+  *sub_x = x;
+  *sub_y = y;
+  *sub_w = sw;
+  *sub_h = sh;
+}
+}

@@ -1,0 +1,438 @@
+"""radler_b200 — host-side Python view of ``libradler_b200.so`` (include/radler_b200.h).
+
+The product is the C++/CUDA library; this module is a thin ctypes layer that mirrors the
+reference's algorithm interface (``DeconvolutionAlgorithm::ExecuteMajorIteration`` and
+its setters, cpp/algorithms/deconvolution_algorithm.h:60-210) so tests and ``bench.py``
+call the hot path exactly as a host program would: plain pointers and sizes, no torch
+types in any signature. torch is used only to own device memory when the caller wants
+HBM-resident cubes (``RDL_MEM_DEVICE``).
+
+There is NO CPU fallback and nothing here imports ``oracle/``: if the CUDA library is
+missing, or no sm_100 device is present, construction fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libradler_b200.so")
+
+RDL_OK, RDL_ERR_INVALID_ARGUMENT, RDL_ERR_NO_DEVICE, RDL_ERR_CUDA, RDL_ERR_UNSUPPORTED, \
+    RDL_ERR_OUT_OF_MEMORY = range(6)
+GENERIC_CLEAN, MULTISCALE, IUWT = 0, 1, 2
+SHAPE_TAPERED_QUADRATIC, SHAPE_GAUSSIAN = 0, 1
+FIT_NONE, FIT_POLYNOMIAL = 0, 1
+MEM_HOST, MEM_DEVICE = 0, 1
+
+
+class RadlerError(RuntimeError):
+    """std::runtime_error of the reference, carried over the C ABI as status + message."""
+
+    def __init__(self, status: int, message: str):
+        super().__init__(f"[rdl status {status}] {message}")
+        self.status = status
+
+
+class _Config(C.Structure):
+    _fields_ = [("algorithm", C.c_int32), ("device", C.c_int32),
+                ("use_sub_minor_optimization", C.c_int32), ("ms_fast_sub_minor_loop", C.c_int32),
+                ("ms_sub_minor_loop_gain", C.c_double), ("ms_scale_bias", C.c_double),
+                ("ms_max_scales", C.c_uint64), ("ms_convolution_padding", C.c_double),
+                ("ms_scale_list", C.POINTER(C.c_double)), ("ms_n_scale_list", C.c_uint64),
+                ("ms_shape", C.c_int32), ("beam_size", C.c_double),
+                ("pixel_scale_x", C.c_double), ("pixel_scale_y", C.c_double),
+                ("track_components", C.c_int32)]
+
+
+class _CubeDesc(C.Structure):
+    _fields_ = [("width", C.c_uint64), ("height", C.c_uint64), ("n_channels", C.c_uint64),
+                ("n_pol", C.c_uint64), ("channel_weights", C.POINTER(C.c_float)),
+                ("pol_linked", C.POINTER(C.c_uint8)), ("pol_norm", C.c_float),
+                ("squared_joins", C.c_int32), ("memory_space", C.c_int32)]
+
+
+class _Result(C.Structure):
+    _fields_ = [("has_starting_peak", C.c_int32), ("starting_peak_value", C.c_float),
+                ("final_peak_value", C.c_float), ("another_iteration_required", C.c_int32),
+                ("is_diverging", C.c_int32), ("iteration_number", C.c_uint64)]
+
+
+class _ScaleInfo(C.Structure):
+    _fields_ = [("scale", C.c_float), ("psf_peak", C.c_float), ("kernel_peak", C.c_float),
+                ("bias_factor", C.c_float), ("gain", C.c_float),
+                ("max_normalized_image_value", C.c_float),
+                ("max_unnormalized_image_value", C.c_float), ("rms", C.c_float),
+                ("max_x", C.c_uint64), ("max_y", C.c_uint64), ("is_active", C.c_int32),
+                ("n_components_cleaned", C.c_uint64), ("total_flux_cleaned", C.c_float)]
+
+
+TRACE_DTYPE = np.dtype([("iteration", "<u4"), ("scale", "<u4"), ("x", "<u4"), ("y", "<u4"),
+                        ("value", "<f4")])
+
+# every symbol include/radler_b200.h declares (checked by tests/test_abi.py)
+EXPORTED_SYMBOLS = [
+    "rdl_config_default", "rdl_create", "rdl_clone", "rdl_destroy", "rdl_last_error",
+    "rdl_set_max_iterations", "rdl_set_threshold", "rdl_set_major_iteration_threshold",
+    "rdl_set_minor_loop_gain", "rdl_set_major_loop_gain", "rdl_set_allow_negative_components",
+    "rdl_set_stop_on_negative_components", "rdl_set_clean_border_ratio",
+    "rdl_set_divergence_limit", "rdl_set_iteration_number", "rdl_set_clean_mask",
+    "rdl_set_rms_factor_image", "rdl_set_spectral_fitter", "rdl_set_auto_mask_mode",
+    "rdl_set_trace_capacity", "rdl_iteration_number", "rdl_scale_count", "rdl_scale_info_get",
+    "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
+    "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
+    "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
+    "rdl_multiscale_transform", "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
+    "rdl_device_count",
+]
+
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compiles libradler_b200.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "-j8"] +
+                       (["-B"] if force else []), check=True)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with "
+                          "`make -C ska_sdp_func_radler_b200/csrc` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, u64, i32, f32 = C.c_void_p, C.c_uint64, C.c_int32, C.c_float
+    L.rdl_config_default.argtypes = [C.POINTER(_Config)]
+    L.rdl_create.argtypes = [C.POINTER(_Config), C.POINTER(vp)]
+    L.rdl_clone.argtypes = [vp, C.POINTER(vp)]
+    L.rdl_destroy.argtypes = [vp]
+    L.rdl_destroy.restype = None
+    L.rdl_last_error.argtypes = [vp]
+    L.rdl_last_error.restype = C.c_char_p
+    for name, t in [("rdl_set_max_iterations", u64), ("rdl_set_threshold", f32),
+                    ("rdl_set_major_iteration_threshold", f32), ("rdl_set_minor_loop_gain", f32),
+                    ("rdl_set_major_loop_gain", f32), ("rdl_set_allow_negative_components", i32),
+                    ("rdl_set_stop_on_negative_components", i32),
+                    ("rdl_set_clean_border_ratio", f32), ("rdl_set_divergence_limit", f32),
+                    ("rdl_set_iteration_number", u64), ("rdl_set_trace_capacity", u64)]:
+        getattr(L, name).argtypes = [vp, t]
+    L.rdl_set_clean_mask.argtypes = [vp, vp, u64, u64]
+    L.rdl_set_rms_factor_image.argtypes = [vp, vp, u64, u64]
+    L.rdl_set_spectral_fitter.argtypes = [vp, i32, u64, vp, vp, u64, u64]
+    L.rdl_set_auto_mask_mode.argtypes = [vp, i32, i32]
+    for name in ["rdl_iteration_number", "rdl_scale_count", "rdl_trace_size",
+                 "rdl_last_selected_count", "rdl_minor_iteration_count",
+                 "rdl_kernel_launch_count"]:
+        getattr(L, name).argtypes = [vp]
+        getattr(L, name).restype = u64
+    L.rdl_scale_info_get.argtypes = [vp, u64, C.POINTER(_ScaleInfo)]
+    L.rdl_scale_mask_get.argtypes = [vp, u64, vp]
+    L.rdl_trace_get.argtypes = [vp, vp, u64]
+    L.rdl_trace_get.restype = u64
+    L.rdl_execute_major_iteration.argtypes = [vp, C.POINTER(_CubeDesc), vp, vp, vp, vp,
+                                              C.POINTER(_Result)]
+    L.rdl_find_peak.argtypes = [vp, C.POINTER(_CubeDesc), vp, i32, i32, u64, u64, u64, u64, vp,
+                                vp, vp, C.POINTER(i32), C.POINTER(u64), C.POINTER(u64),
+                                C.POINTER(f32)]
+    L.rdl_subtract_image.argtypes = [vp, C.POINTER(_CubeDesc), vp, vp, u64, u64, vp, vp]
+    L.rdl_integrate.argtypes = [vp, C.POINTER(_CubeDesc), vp, i32, vp, vp]
+    L.rdl_convolve.argtypes = [vp, vp, u64, vp, u64, u64, vp]
+    L.rdl_multiscale_transform.argtypes = [vp, vp, u64, u64, u64, f32, i32, vp]
+    L.rdl_good_fft_size.argtypes = [u64]
+    L.rdl_good_fft_size.restype = u64
+    L.rdl_convolution_size.argtypes = [C.c_double, u64, C.c_double]
+    L.rdl_convolution_size.restype = u64
+    L.rdl_version.restype = C.c_char_p
+    L.rdl_device_count.restype = i32
+    _lib = L
+    return L
+
+
+@dataclass
+class Cube:
+    """ImageSet layout (cpp/image_set.h:19-381): images ordered [channel][polarization]."""
+    width: int
+    height: int
+    n_channels: int = 1
+    n_pol: int = 1
+    weights: np.ndarray | None = None
+    pol_linked: np.ndarray | None = None
+    pol_norm: float = 1.0
+    squared_joins: bool = False
+    _keep: list = field(default_factory=list, repr=False)
+
+    @property
+    def n_images(self) -> int:
+        return self.n_channels * self.n_pol
+
+    def desc(self, memory_space: int) -> _CubeDesc:
+        w = None if self.weights is None else np.ascontiguousarray(self.weights, np.float32)
+        p = None if self.pol_linked is None else np.ascontiguousarray(self.pol_linked, np.uint8)
+        self._keep = [w, p]
+        return _CubeDesc(self.width, self.height, self.n_channels, self.n_pol,
+                         None if w is None else w.ctypes.data_as(C.POINTER(C.c_float)),
+                         None if p is None else p.ctypes.data_as(C.POINTER(C.c_uint8)),
+                         self.pol_norm, int(self.squared_joins), memory_space)
+
+
+@dataclass
+class Result:
+    """DeconvolutionResult (deconvolution_algorithm.h:31-58)."""
+    starting_peak_value: float | None
+    final_peak_value: float
+    another_iteration_required: bool
+    is_diverging: bool
+    iteration_number: int
+
+
+def _is_torch(a) -> bool:
+    return type(a).__module__.startswith("torch")
+
+
+def _plane_pointers(a, n: int, plane_elems: int):
+    """Pointer table (void*[n]) of the n image planes of `a` + its memory space."""
+    if _is_torch(a):
+        if not a.is_cuda:
+            raise ValueError("torch tensors passed to radler_b200 must live on a CUDA device")
+        if not a.is_contiguous() or a.dtype.itemsize != 4 or not a.dtype.is_floating_point:
+            raise ValueError("expected a contiguous float32 tensor")
+        if a.numel() != n * plane_elems:
+            raise ValueError(f"expected {n} planes of {plane_elems} pixels")
+        base, space = a.data_ptr(), MEM_DEVICE
+    else:
+        if a.dtype != np.float32 or not a.flags.c_contiguous:
+            raise ValueError("expected a C-contiguous float32 array")
+        if a.size != n * plane_elems:
+            raise ValueError(f"expected {n} planes of {plane_elems} pixels")
+        base, space = a.ctypes.data, MEM_HOST
+    table = (C.c_void_p * n)(*[base + i * plane_elems * 4 for i in range(n)])
+    return table, space
+
+
+class DeconvolutionAlgorithm:
+    """Mirror of radler::algorithms::DeconvolutionAlgorithm over the C ABI."""
+
+    def __init__(self, algorithm: int = GENERIC_CLEAN, *, device: int = 0,
+                 use_sub_minor_optimization: bool = True, fast_sub_minor_loop: bool = True,
+                 sub_minor_loop_gain: float = 0.2, scale_bias: float = 0.6, max_scales: int = 0,
+                 convolution_padding: float = 1.1, scale_list=None, shape: int = 0,
+                 beam_size: float = 0.0, pixel_scale: float = 1.0, track_components: bool = False,
+                 _handle=None):
+        L = lib()
+        self._h = None
+        if _handle is not None:
+            self._h = _handle
+            return
+        cfg = _Config()
+        L.rdl_config_default(C.byref(cfg))
+        cfg.algorithm, cfg.device = algorithm, device
+        cfg.use_sub_minor_optimization = int(use_sub_minor_optimization)
+        cfg.ms_fast_sub_minor_loop = int(fast_sub_minor_loop)
+        cfg.ms_sub_minor_loop_gain = sub_minor_loop_gain
+        cfg.ms_scale_bias = scale_bias
+        cfg.ms_max_scales = max_scales
+        cfg.ms_convolution_padding = convolution_padding
+        sl = None if not scale_list else np.ascontiguousarray(scale_list, np.float64)
+        if sl is not None:
+            cfg.ms_scale_list = sl.ctypes.data_as(C.POINTER(C.c_double))
+            cfg.ms_n_scale_list = len(sl)
+        cfg.ms_shape = shape
+        cfg.beam_size = beam_size
+        cfg.pixel_scale_x = cfg.pixel_scale_y = pixel_scale
+        cfg.track_components = int(track_components)
+        h = C.c_void_p()
+        st = L.rdl_create(C.byref(cfg), C.byref(h))
+        if st != RDL_OK:
+            raise RadlerError(st, L.rdl_last_error(None).decode())
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().rdl_destroy(self._h)
+            self._h = None
+
+    def _check(self, st: int):
+        if st != RDL_OK:
+            raise RadlerError(st, lib().rdl_last_error(self._h).decode())
+
+    def clone(self) -> "DeconvolutionAlgorithm":
+        h = C.c_void_p()
+        self._check(lib().rdl_clone(self._h, C.byref(h)))
+        return DeconvolutionAlgorithm(_handle=h)
+
+    # -- setters (deconvolution_algorithm.h:75-166) ---------------------------------
+    def set_max_iterations(self, n): self._check(lib().rdl_set_max_iterations(self._h, n))
+    def set_threshold(self, v): self._check(lib().rdl_set_threshold(self._h, v))
+    def set_major_iteration_threshold(self, v):
+        self._check(lib().rdl_set_major_iteration_threshold(self._h, v))
+    def set_minor_loop_gain(self, v): self._check(lib().rdl_set_minor_loop_gain(self._h, v))
+    def set_major_loop_gain(self, v): self._check(lib().rdl_set_major_loop_gain(self._h, v))
+    def set_allow_negative_components(self, v):
+        self._check(lib().rdl_set_allow_negative_components(self._h, int(v)))
+    def set_stop_on_negative_components(self, v):
+        self._check(lib().rdl_set_stop_on_negative_components(self._h, int(v)))
+    def set_clean_border_ratio(self, v): self._check(lib().rdl_set_clean_border_ratio(self._h, v))
+    def set_divergence_limit(self, v): self._check(lib().rdl_set_divergence_limit(self._h, v))
+    def set_iteration_number(self, n): self._check(lib().rdl_set_iteration_number(self._h, n))
+    def set_trace_capacity(self, n): self._check(lib().rdl_set_trace_capacity(self._h, n))
+
+    def set_clean_mask(self, mask):
+        if mask is None:
+            self._check(lib().rdl_set_clean_mask(self._h, None, 0, 0))
+            return
+        m = np.ascontiguousarray(mask, np.uint8)
+        self._check(lib().rdl_set_clean_mask(self._h, m.ctypes.data, m.shape[1], m.shape[0]))
+
+    def set_rms_factor_image(self, image):
+        if image is None:
+            self._check(lib().rdl_set_rms_factor_image(self._h, None, 0, 0))
+            return
+        a = np.ascontiguousarray(image, np.float32)
+        self._check(lib().rdl_set_rms_factor_image(self._h, a.ctypes.data, a.shape[1], a.shape[0]))
+
+    def set_spectral_fitter(self, mode, n_terms=0, frequencies=None, weights=None, n_pol=1):
+        fr = None if frequencies is None else np.ascontiguousarray(frequencies, np.float64)
+        w = None if weights is None else np.ascontiguousarray(weights, np.float32)
+        self._check(lib().rdl_set_spectral_fitter(
+            self._h, mode, n_terms, None if fr is None else fr.ctypes.data,
+            None if w is None else w.ctypes.data, 0 if fr is None else len(fr), n_pol))
+
+    def set_auto_mask_mode(self, track: bool, use: bool):
+        self._check(lib().rdl_set_auto_mask_mode(self._h, int(track), int(use)))
+
+    def apply(self, **settings):
+        """Convenience: apply(threshold=..., minor_loop_gain=...) -> the setters above."""
+        for k, v in settings.items():
+            getattr(self, "set_" + k)(v)
+        return self
+
+    # -- getters ----------------------------------------------------------------------
+    @property
+    def iteration_number(self) -> int: return lib().rdl_iteration_number(self._h)
+    @property
+    def last_selected_count(self) -> int: return lib().rdl_last_selected_count(self._h)
+    @property
+    def minor_iteration_count(self) -> int: return lib().rdl_minor_iteration_count(self._h)
+    @property
+    def kernel_launch_count(self) -> int: return lib().rdl_kernel_launch_count(self._h)
+    @property
+    def scale_count(self) -> int: return lib().rdl_scale_count(self._h)
+
+    def scale_infos(self):
+        out = []
+        for i in range(self.scale_count):
+            s = _ScaleInfo()
+            self._check(lib().rdl_scale_info_get(self._h, i, C.byref(s)))
+            out.append({k: getattr(s, k) for k, _ in _ScaleInfo._fields_})
+        return out
+
+    def scale_mask(self, i, width, height):
+        m = np.zeros((height, width), np.uint8)
+        self._check(lib().rdl_scale_mask_get(self._h, i, m.ctypes.data))
+        return m
+
+    def trace(self) -> np.ndarray:
+        n = lib().rdl_trace_size(self._h)
+        t = np.zeros(n, TRACE_DTYPE)
+        if n:
+            lib().rdl_trace_get(self._h, t.ctypes.data, n)
+        return t
+
+    # -- the hot path -------------------------------------------------------------------
+    def execute_major_iteration(self, cube: Cube, residual, model, psfs, stream=None) -> Result:
+        """ExecuteMajorIteration (deconvolution_algorithm.h:69-71). residual/model
+        ([n_images,H,W]) are updated in place; psfs is [n_channels,H,W]. All three are
+        either numpy arrays (host memory, staged inside the call) or CUDA torch tensors."""
+        n = cube.width * cube.height
+        rt, s0 = _plane_pointers(residual, cube.n_images, n)
+        mt, s1 = _plane_pointers(model, cube.n_images, n)
+        pt, s2 = _plane_pointers(psfs, cube.n_channels, n)
+        if not (s0 == s1 == s2):
+            raise ValueError("residual, model and psfs must live in the same memory space")
+        d = cube.desc(s0)
+        out = _Result()
+        self._check(lib().rdl_execute_major_iteration(self._h, C.byref(d), rt, mt, pt, stream,
+                                                      C.byref(out)))
+        return Result(out.starting_peak_value if out.has_starting_peak else None,
+                      out.final_peak_value, bool(out.another_iteration_required),
+                      bool(out.is_diverging), out.iteration_number)
+
+    # -- kernel-level entry points (device tensors) -----------------------------------
+    def find_peak(self, cube: Cube, images, *, square=False, allow_negative=True, start_y=0,
+                  end_y=None, h_border=0, v_border=0, mask=None, rms_factor=None, stream=None):
+        t, space = _plane_pointers(images, cube.n_images, cube.width * cube.height)
+        assert space == MEM_DEVICE
+        d = cube.desc(space)
+        found, x, y, v = C.c_int32(), C.c_uint64(), C.c_uint64(), C.c_float()
+        self._check(lib().rdl_find_peak(
+            self._h, C.byref(d), t, int(square), int(allow_negative), start_y,
+            cube.height if end_y is None else end_y, h_border, v_border,
+            None if mask is None else mask.data_ptr(),
+            None if rms_factor is None else rms_factor.data_ptr(), stream, C.byref(found),
+            C.byref(x), C.byref(y), C.byref(v)))
+        return (v.value if found.value else None), x.value, y.value
+
+    def subtract_image(self, cube: Cube, images, psfs, x, y, factors, stream=None):
+        t, space = _plane_pointers(images, cube.n_images, cube.width * cube.height)
+        p, _ = _plane_pointers(psfs, cube.n_channels, cube.width * cube.height)
+        assert space == MEM_DEVICE
+        d = cube.desc(space)
+        f = np.ascontiguousarray(factors, np.float32)
+        assert f.size == cube.n_images
+        self._check(lib().rdl_subtract_image(self._h, C.byref(d), t, p, x, y, f.ctypes.data,
+                                             stream))
+
+    def integrate(self, cube: Cube, images, dest, *, square=False, stream=None):
+        t, space = _plane_pointers(images, cube.n_images, cube.width * cube.height)
+        assert space == MEM_DEVICE
+        d = cube.desc(space)
+        self._check(lib().rdl_integrate(self._h, C.byref(d), t, int(square), dest.data_ptr(),
+                                        stream))
+
+    def convolve(self, images, kernel, stream=None):
+        """schaapcommon::math::Convolve on [n,H,W] device images with a prepared kernel."""
+        n, h, w = images.shape
+        t, space = _plane_pointers(images, n, h * w)
+        assert space == MEM_DEVICE
+        self._check(lib().rdl_convolve(self._h, t, n, kernel.data_ptr(), w, h, stream))
+
+    def multiscale_transform(self, images, scale, shape=0, stream=None):
+        n, h, w = images.shape
+        t, space = _plane_pointers(images, n, h * w)
+        assert space == MEM_DEVICE
+        self._check(lib().rdl_multiscale_transform(self._h, t, n, w, h, scale, shape, stream))
+
+
+def GenericClean(use_sub_minor_optimization: bool = True, **kw) -> DeconvolutionAlgorithm:
+    """GenericClean (cpp/algorithms/generic_clean.h)."""
+    return DeconvolutionAlgorithm(GENERIC_CLEAN,
+                                  use_sub_minor_optimization=use_sub_minor_optimization, **kw)
+
+
+def MultiScaleAlgorithm(beam_size: float, pixel_scale: float = 1.0, **kw) -> DeconvolutionAlgorithm:
+    """MultiScaleAlgorithm (cpp/algorithms/multiscale_algorithm.h)."""
+    return DeconvolutionAlgorithm(MULTISCALE, beam_size=beam_size, pixel_scale=pixel_scale, **kw)
+
+
+def good_fft_size(n: int) -> int:
+    return lib().rdl_good_fft_size(n)
+
+
+def convolution_size(scale: float, n: int, padding: float) -> int:
+    return lib().rdl_convolution_size(scale, n, padding)
+
+
+def version() -> str:
+    return lib().rdl_version().decode()
+
+
+def device_count() -> int:
+    return lib().rdl_device_count()
