@@ -1,5 +1,6 @@
 // extern "C" boundary (include/radler_b200.h). Exceptions never cross it: they are
 // turned into status codes + rdl_last_error().
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -140,6 +141,9 @@ rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out) {
     h->ms_scale_list.assign(cfg->ms_scale_list, cfg->ms_scale_list + cfg->ms_n_scale_list);
   h->config.ms_scale_list = nullptr;
   h->device = cfg->device;
+  // MultiScaleAlgorithm ctor (multiscale_algorithm.cc:153-163)
+  h->beam_size_in_pixels = cfg->beam_size / std::max(cfg->pixel_scale_x, cfg->pixel_scale_y);
+  if (!(h->beam_size_in_pixels > 0.0)) h->beam_size_in_pixels = 1.0;
   const rdl_status st = Guard(h, [&] {
     RDL_CUDA(cudaSetDevice(h->device));
     RDL_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));

@@ -1,0 +1,734 @@
+// Hand-written FFT convolution engine for sm_100a — the device-side restatement of
+// schaapcommon::math::Convolve / PrepareConvolutionKernel / PrepareSmallConvolutionKernel as
+// Radler calls them (multiscale_transforms.cc:11-23, subminor_loop.cc:195-218).
+//
+//   out = irfft2( rfft2(in) * rfft2(kernel) ) / (W*H)          (circular, in place)
+//
+// Three HBM passes per convolution, every 1-D transform done entirely in shared memory:
+//   RowForwardKernel   real rows -> half spectrum   (R2C through a length-W/2 complex FFT)
+//   ColumnKernel       column FFT, * kernel spectrum, inverse column FFT   (one pass)
+//   RowInverseKernel   half spectrum -> real rows, fused with the caller's epilogue
+//                      (store / residual -= result / model += result) and with the
+//                      reference's Untrim/Trim (centred zero-pad and crop).
+// The 1-D transforms are in-place decimation-in-frequency forward and decimation-in-time
+// inverse passes (radix 8/4/2/3/5/7, generic prime radix <= 127), so no bit-reversal pass is
+// ever needed: the column spectra stay in digit-reversed order (the kernel spectrum is
+// produced by the same forward pass), only the row split step looks frequencies up through a
+// small permutation table. Algorithmic HBM traffic: 28 bytes per padded pixel.
+// Results are not bit-comparable with FFTW or the CPU checker; parity is by tolerance.
+#include "fft.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <map>
+#include <vector>
+
+namespace rdl {
+
+size_t CalculateGoodFFTSize(size_t minimum_size) {  // fft_size_calculations.h:15-29
+  size_t best = 2 * minimum_size;
+  for (size_t f2 = 2; f2 < best; f2 *= 2)
+    for (size_t f23 = f2; f23 < best; f23 *= 3)
+      for (size_t f235 = f23; f235 < best; f235 *= 5)
+        for (size_t f2357 = f235; f2357 < best; f2357 *= 7)
+          if (f2357 >= minimum_size) best = f2357;
+  return best;
+}
+
+size_t GetConvolutionSize(double scale, size_t original_size, double padding) {  // :39-50
+  return CalculateGoodFFTSize(size_t(std::ceil(padding * (scale * 1.5 + double(original_size)))));
+}
+
+namespace {
+
+constexpr int kMaxStages = 24;
+constexpr int kMaxGenericRadix = 127;
+constexpr size_t kMaxSmemBytes = 227 * 1024;
+
+struct Plan {
+  int n;
+  int n_stages;
+  int radix[kMaxStages];
+  int len[kMaxStages];  // block length the stage works on (n, n/r0, n/(r0 r1), ...)
+  const float2* tw;     // exp(-2 pi i t / n), t in [0, n)
+};
+
+// One padding slot per 32 complex values keeps the strided late stages off the same banks.
+__host__ __device__ __forceinline__ int Pad(int i) { return i + (i >> 5); }
+inline int PaddedLength(int n) { return (Pad(n - 1) + 1) | 1; }
+
+__device__ __forceinline__ float2 operator+(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 operator-(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 operator*(float s, float2 a) { return make_float2(s * a.x, s * a.y); }
+__device__ __forceinline__ float2 CMul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ float2 Conj(float2 a) { return make_float2(a.x, -a.y); }
+// forward: * (-i); inverse: * (+i)
+template <bool INV>
+__device__ __forceinline__ float2 MulI(float2 a) {
+  return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+}
+
+template <int R, bool INV>
+struct Dft;
+
+template <bool INV>
+struct Dft<2, INV> {
+  __device__ __forceinline__ static void Run(float2 (&v)[2]) {
+    const float2 t = v[0];
+    v[0] = t + v[1];
+    v[1] = t - v[1];
+  }
+};
+
+template <bool INV>
+struct Dft<4, INV> {
+  __device__ __forceinline__ static void Run(float2 (&v)[4]) {
+    const float2 t0 = v[0] + v[2], t1 = v[0] - v[2], t2 = v[1] + v[3];
+    const float2 t3 = MulI<INV>(v[1] - v[3]);
+    v[0] = t0 + t2;
+    v[1] = t1 + t3;
+    v[2] = t0 - t2;
+    v[3] = t1 - t3;
+  }
+};
+
+template <bool INV>
+struct Dft<8, INV> {
+  __device__ __forceinline__ static void Run(float2 (&v)[8]) {
+    float2 e[4] = {v[0], v[2], v[4], v[6]};
+    float2 o[4] = {v[1], v[3], v[5], v[7]};
+    Dft<4, INV>::Run(e);
+    Dft<4, INV>::Run(o);
+    constexpr float c = 0.70710678118654752440f;
+    const float2 o1 = INV ? make_float2(c * (o[1].x - o[1].y), c * (o[1].x + o[1].y))
+                          : make_float2(c * (o[1].x + o[1].y), c * (o[1].y - o[1].x));
+    const float2 o2 = MulI<INV>(o[2]);
+    const float2 o3 = INV ? make_float2(c * (-o[3].x - o[3].y), c * (o[3].x - o[3].y))
+                          : make_float2(c * (o[3].y - o[3].x), c * (-o[3].y - o[3].x));
+    v[0] = e[0] + o[0];
+    v[4] = e[0] - o[0];
+    v[1] = e[1] + o1;
+    v[5] = e[1] - o1;
+    v[2] = e[2] + o2;
+    v[6] = e[2] - o2;
+    v[3] = e[3] + o3;
+    v[7] = e[3] - o3;
+  }
+};
+
+template <int P>
+struct Trig;
+template <>
+struct Trig<3> {
+  __device__ __forceinline__ static float C(int t) { return t == 0 ? 1.0f : -0.5f; }
+  __device__ __forceinline__ static float S(int t) {
+    return t == 0 ? 0.0f : (t == 1 ? 0.86602540378443864676f : -0.86602540378443864676f);
+  }
+};
+template <>
+struct Trig<5> {
+  __device__ __forceinline__ static float C(int t) {
+    return t == 0 ? 1.0f : ((t == 1 || t == 4) ? 0.30901699437494742410f : -0.80901699437494742410f);
+  }
+  __device__ __forceinline__ static float S(int t) {
+    return t == 0 ? 0.0f
+                  : (t == 1 ? 0.95105651629515357212f
+                            : (t == 2 ? 0.58778525229247312917f
+                                      : (t == 3 ? -0.58778525229247312917f
+                                                : -0.95105651629515357212f)));
+  }
+};
+template <>
+struct Trig<7> {
+  __device__ __forceinline__ static float C(int t) {
+    return t == 0 ? 1.0f
+                  : ((t == 1 || t == 6) ? 0.62348980185873353053f
+                                        : ((t == 2 || t == 5) ? -0.22252093395631440429f
+                                                              : -0.90096886790241912624f));
+  }
+  __device__ __forceinline__ static float S(int t) {
+    const float s1 = 0.78183148246802980871f, s2 = 0.97492791218182360702f,
+                s3 = 0.43388373911755812048f;
+    return t == 0 ? 0.0f
+                  : (t == 1 ? s1 : (t == 2 ? s2 : (t == 3 ? s3 : (t == 4 ? -s3 : (t == 5 ? -s2 : -s1)))));
+  }
+};
+
+template <int P, bool INV>
+struct DftOdd {
+  __device__ __forceinline__ static void Run(float2 (&v)[P]) {
+    constexpr int H = (P - 1) / 2;
+    float2 a[H], b[H];
+#pragma unroll
+    for (int m = 1; m <= H; ++m) {
+      a[m - 1] = v[m] + v[P - m];
+      b[m - 1] = v[m] - v[P - m];
+    }
+    const float2 x0 = v[0];
+    float2 sum = x0;
+#pragma unroll
+    for (int m = 0; m < H; ++m) sum = sum + a[m];
+#pragma unroll
+    for (int q = 1; q <= H; ++q) {
+      float2 c = x0, s = make_float2(0.0f, 0.0f);
+#pragma unroll
+      for (int m = 1; m <= H; ++m) {
+        const int t = (q * m) % P;
+        c = c + Trig<P>::C(t) * a[m - 1];
+        s = s + Trig<P>::S(t) * b[m - 1];
+      }
+      // forward: X_q = c - i s, X_{P-q} = c + i s; inverse: swapped
+      const float2 lo = make_float2(c.x + s.y, c.y - s.x), hi = make_float2(c.x - s.y, c.y + s.x);
+      v[q] = INV ? hi : lo;
+      v[P - q] = INV ? lo : hi;
+    }
+    v[0] = sum;
+  }
+};
+template <bool INV>
+struct Dft<3, INV> : DftOdd<3, INV> {};
+template <bool INV>
+struct Dft<5, INV> : DftOdd<5, INV> {};
+template <bool INV>
+struct Dft<7, INV> : DftOdd<7, INV> {};
+
+// One in-place radix-R pass over n_seq sequences of length n held in shared memory.
+// DIF (forward): r-point DFT then twiddle; DIT (inverse): conjugate twiddle then inverse DFT.
+template <int R, bool INV>
+__device__ __forceinline__ void Stage(float2* s, int n_seq, int seq_stride, int n, int L,
+                                      const float2* __restrict__ tw) {
+  const int m = L / R;
+  const int tw_step = n / L;
+  const int n_bf = n / R;
+  for (int t = threadIdx.x; t < n_bf; t += blockDim.x) {
+    const int b = t / m, j = t - b * m;
+    const int base = b * L + j;
+    float2 w[R];
+    if (m > 1) {
+      // every power straight from the double-rounded table: chaining products of w^j costs
+      // about 4x in accuracy, which the reference's 2e-6 point-source test does not allow
+#pragma unroll
+      for (int q = 1; q < R; ++q) {
+        w[q] = __ldg(tw + j * q * tw_step);
+        if (INV) w[q].y = -w[q].y;
+      }
+    }
+    for (int c = 0; c < n_seq; ++c) {
+      float2* p = s + c * seq_stride;
+      float2 v[R];
+#pragma unroll
+      for (int q = 0; q < R; ++q) v[q] = p[Pad(base + q * m)];
+      if (INV && m > 1) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = CMul(v[q], w[q]);
+      }
+      Dft<R, INV>::Run(v);
+      if (!INV && m > 1) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) v[q] = CMul(v[q], w[q]);
+      }
+#pragma unroll
+      for (int q = 0; q < R; ++q) p[Pad(base + q * m)] = v[q];
+    }
+  }
+}
+
+// Any prime radix p <= kMaxGenericRadix by direct O(p^2) evaluation (local-memory staging).
+// Only reached for the non-smooth padded sizes of GenericClean path A
+// (generic_clean.cc:63-66: even(ceil(1.1f*N)), e.g. 1128 = 2^3 * 3 * 47).
+template <bool INV>
+__device__ void GenericStage(float2* s, int n_seq, int seq_stride, int n, int L, int p,
+                             const float2* __restrict__ tw) {
+  const int m = L / p;
+  const int tw_step = n / L;
+  const int root_step = n / p;
+  const int n_bf = n / p;
+  for (int t = threadIdx.x; t < n_bf; t += blockDim.x) {
+    const int b = t / m, j = t - b * m;
+    const int base = b * L + j;
+    for (int c = 0; c < n_seq; ++c) {
+      float2* ptr = s + c * seq_stride;
+      float2 x[kMaxGenericRadix];
+      for (int q = 0; q < p; ++q) {
+        float2 v = ptr[Pad(base + q * m)];
+        if (INV && m > 1) v = CMul(v, Conj(__ldg(tw + j * q * tw_step)));
+        x[q] = v;
+      }
+      for (int q = 0; q < p; ++q) {
+        float2 acc = x[0];
+        int idx = 0;
+        for (int k = 1; k < p; ++k) {
+          idx += q;
+          if (idx >= p) idx -= p;
+          float2 r = __ldg(tw + idx * root_step);
+          if (INV) r.y = -r.y;
+          acc = acc + CMul(x[k], r);
+        }
+        if (!INV && m > 1) acc = CMul(acc, __ldg(tw + j * q * tw_step));
+        ptr[Pad(base + q * m)] = acc;
+      }
+    }
+  }
+}
+
+template <bool INV>
+__device__ __forceinline__ void RunStage(float2* s, int n_seq, int seq_stride, const Plan& plan,
+                                         int st) {
+  const int n = plan.n, L = plan.len[st];
+  switch (plan.radix[st]) {
+    case 8: Stage<8, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    case 4: Stage<4, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    case 2: Stage<2, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    case 3: Stage<3, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    case 5: Stage<5, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    case 7: Stage<7, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
+    default: GenericStage<INV>(s, n_seq, seq_stride, n, L, plan.radix[st], plan.tw); break;
+  }
+}
+
+// Forward: natural order in, digit-reversed out. Inverse: digit-reversed in, natural out.
+// Both leave the block synchronised.
+template <bool INV>
+__device__ __forceinline__ void RunFft(float2* s, int n_seq, int seq_stride, const Plan& plan) {
+  if (!INV) {
+    for (int st = 0; st < plan.n_stages; ++st) {
+      RunStage<false>(s, n_seq, seq_stride, plan, st);
+      __syncthreads();
+    }
+  } else {
+    for (int st = plan.n_stages - 1; st >= 0; --st) {
+      RunStage<true>(s, n_seq, seq_stride, plan, st);
+      __syncthreads();
+    }
+  }
+}
+
+struct RowParams {
+  // real image side
+  const float* src;  // forward: source image (sw x sh)
+  float* dst;        // inverse: destination image (sw x sh)
+  int sw, sh;
+  int ox, oy;        // position of the image inside the W x H frame (Untrim / Trim offsets)
+  int W, H;
+  float2* spec;      // [H][pitch] half spectrum, 2n = W
+  int pitch;
+  Plan plan;         // n = W / 2
+  const uint32_t* perm;     // perm[k] = slot of frequency k after the forward pass
+  const float2* split_tw;   // exp(-2 pi i k / W), k in [0, n]
+  int rows_per_cta;
+  int seq_stride;
+  int mode;          // inverse epilogue: 0 store, 1 dst -= v, 2 dst += v
+};
+
+__global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant__ RowParams p) {
+  extern __shared__ float2 smem[];
+  const int n = p.plan.n;
+  const int row0 = blockIdx.x * p.rows_per_cta;
+  const int n_seq = min(p.rows_per_cta, p.sh - row0);
+  for (int c = 0; c < n_seq; ++c) {
+    float* s = reinterpret_cast<float*>(smem + c * p.seq_stride);
+    const float* src = p.src + size_t(row0 + c) * p.sw;
+    for (int x = threadIdx.x; x < p.W; x += blockDim.x) {
+      const int xs = x - p.ox;
+      const float v = (xs >= 0 && xs < p.sw) ? __ldg(src + xs) : 0.0f;
+      s[2 * Pad(x >> 1) + (x & 1)] = v;
+    }
+  }
+  __syncthreads();
+  RunFft<false>(smem, n_seq, p.seq_stride, p.plan);
+  // split: 2 X[k] = (Z[k] + conj Z[n-k]) - i w^k (Z[k] - conj Z[n-k]),  k = 0..n
+  for (int c = 0; c < n_seq; ++c) {
+    const float2* s = smem + c * p.seq_stride;
+    float2* out = p.spec + size_t(p.oy + row0 + c) * p.pitch;
+    for (int k = threadIdx.x; k <= n; k += blockDim.x) {
+      const int ka = k == n ? 0 : k, kb = k == 0 ? 0 : n - k;
+      const float2 a = s[Pad(__ldg(p.perm + ka))], b = s[Pad(__ldg(p.perm + kb))];
+      const float2 sum = make_float2(a.x + b.x, a.y - b.y);
+      const float2 dif = make_float2(a.x - b.x, a.y + b.y);
+      const float2 t = CMul(__ldg(p.split_tw + k), dif);
+      out[k] = make_float2(sum.x + t.y, sum.y - t.x);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant__ RowParams p) {
+  extern __shared__ float2 smem[];
+  const int n = p.plan.n;
+  const int row0 = blockIdx.x * p.rows_per_cta;
+  const int n_seq = min(p.rows_per_cta, p.sh - row0);
+  // inverse split: 2 Z[k] = (Y[k] + conj Y[n-k]) + i conj(w^k) (Y[k] - conj Y[n-k]),  k = 0..n-1
+  for (int c = 0; c < n_seq; ++c) {
+    float2* s = smem + c * p.seq_stride;
+    const float2* in = p.spec + size_t(p.oy + row0 + c) * p.pitch;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      const float2 a = in[k], b = in[n - k];
+      const float2 sum = make_float2(a.x + b.x, a.y - b.y);
+      const float2 dif = make_float2(a.x - b.x, a.y + b.y);
+      const float2 t = CMul(Conj(__ldg(p.split_tw + k)), dif);
+      s[Pad(__ldg(p.perm + k))] = make_float2(sum.x - t.y, sum.y + t.x);
+    }
+  }
+  __syncthreads();
+  RunFft<true>(smem, n_seq, p.seq_stride, p.plan);
+  for (int c = 0; c < n_seq; ++c) {
+    const float* s = reinterpret_cast<const float*>(smem + c * p.seq_stride);
+    float* dst = p.dst + size_t(row0 + c) * p.sw;
+    for (int xs = threadIdx.x; xs < p.sw; xs += blockDim.x) {
+      const int x = xs + p.ox;
+      const float v = s[2 * Pad(x >> 1) + (x & 1)];
+      if (p.mode == 0)
+        dst[xs] = v;
+      else if (p.mode == 1)
+        dst[xs] = dst[xs] - v;
+      else
+        dst[xs] = dst[xs] + v;
+    }
+  }
+}
+
+struct ColParams {
+  float2* spec;          // work spectrum, transformed in place
+  const float2* kspec;   // kernel spectrum to multiply with (convolve mode)
+  float2* kspec_out;     // forward-only mode: where the scaled spectrum goes
+  int pitch, n_cols, H;
+  int y0, y1;            // rows of `spec` that hold data (others are zero by construction)
+  int out_y0, out_y1;    // rows the inverse row pass will read
+  int cols_per_cta, seq_stride;
+  float scale;
+  Plan plan;             // n = H
+};
+
+template <bool CONVOLVE>
+__global__ void __launch_bounds__(512, 1) ColumnKernel(const __grid_constant__ ColParams p) {
+  extern __shared__ float2 smem[];
+  const int H = p.H, cx = p.cols_per_cta;
+  const int c0 = blockIdx.x * cx;
+  const int n_seq = min(cx, p.n_cols - c0);
+  const int rows_in = p.y1 - p.y0;
+  for (int i = threadIdx.x; i < rows_in * cx; i += blockDim.x) {
+    const int r = i / cx, c = i - r * cx;
+    if (c < n_seq) smem[c * p.seq_stride + Pad(p.y0 + r)] = p.spec[size_t(p.y0 + r) * p.pitch + c0 + c];
+  }
+  if (rows_in < H) {
+    const int rows_zero = H - rows_in;
+    for (int i = threadIdx.x; i < rows_zero * cx; i += blockDim.x) {
+      const int r = i / cx, c = i - r * cx;
+      const int y = r < p.y0 ? r : r + rows_in;
+      if (c < n_seq) smem[c * p.seq_stride + Pad(y)] = make_float2(0.0f, 0.0f);
+    }
+  }
+  __syncthreads();
+  RunFft<false>(smem, n_seq, p.seq_stride, p.plan);
+  if (!CONVOLVE) {
+    for (int i = threadIdx.x; i < H * cx; i += blockDim.x) {
+      const int r = i / cx, c = i - r * cx;
+      if (c < n_seq) p.kspec_out[size_t(r) * p.pitch + c0 + c] = p.scale * smem[c * p.seq_stride + Pad(r)];
+    }
+    return;
+  }
+  for (int i = threadIdx.x; i < H * cx; i += blockDim.x) {
+    const int r = i / cx, c = i - r * cx;
+    if (c < n_seq) {
+      float2* v = smem + c * p.seq_stride + Pad(r);
+      *v = CMul(*v, __ldg(p.kspec + size_t(r) * p.pitch + c0 + c));
+    }
+  }
+  __syncthreads();
+  RunFft<true>(smem, n_seq, p.seq_stride, p.plan);
+  const int rows_out = p.out_y1 - p.out_y0;
+  for (int i = threadIdx.x; i < rows_out * cx; i += blockDim.x) {
+    const int r = i / cx, c = i - r * cx;
+    if (c < n_seq) p.spec[size_t(p.out_y0 + r) * p.pitch + c0 + c] = smem[c * p.seq_stride + Pad(p.out_y0 + r)];
+  }
+}
+
+// dst (w x h) = PrepareSmallConvolutionKernel(k, n): an n x n kernel wrapped around the origin
+__global__ void WrapSmallKernelKernel(float* dst, int w, int h, const float* k, int n) {
+  const int half = n / 2;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n * n; i += gridDim.x * blockDim.x) {
+    const int ky = i / n, kx = i - ky * n;
+    const int y = (ky + h - half) % h, x = (kx + w - half) % w;
+    dst[size_t(y) * w + x] = k[i];
+  }
+}
+
+// dst (w x h) = PrepareConvolutionKernel(Untrim(psf, pw x ph -> w x h)): centred zero-pad, then
+// the circular shift that moves (w/2, h/2) to the origin (subminor_loop.cc:199-202).
+__global__ void PreparePsfKernelKernel(float* dst, int w, int h, const float* psf, int pw, int ph) {
+  const int sx = (w - pw) / 2, sy = (h - ph) / 2;
+  const size_t total = size_t(w) * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const int y = int(i / w), x = int(i - size_t(y) * w);
+    const int yy = (y + h / 2) % h - sy, xx = (x + w / 2) % w - sx;
+    dst[i] = (yy >= 0 && yy < ph && xx >= 0 && xx < pw) ? __ldg(psf + size_t(yy) * pw + xx) : 0.0f;
+  }
+}
+
+struct HostPlan {
+  Plan plan{};
+  DeviceBuffer<float2> tw;
+  std::vector<int> radices;
+
+  void Build(int n) {
+    if (n < 1) throw std::invalid_argument("FFT length must be positive");
+    std::vector<int> generic, pow2, odd;
+    int rest = n;
+    while (rest % 8 == 0) { pow2.push_back(8); rest /= 8; }
+    while (rest % 4 == 0) { pow2.push_back(4); rest /= 4; }
+    while (rest % 2 == 0) { pow2.push_back(2); rest /= 2; }
+    for (int p : {7, 5, 3})
+      while (rest % p == 0) { odd.push_back(p); rest /= p; }
+    for (int p = 11; rest > 1; p += 2) {
+      if (p * p > rest) p = rest;
+      while (rest % p == 0) {
+        if (p > kMaxGenericRadix)
+          throw std::domain_error("FFT length " + std::to_string(n) + " has the prime factor " +
+                                  std::to_string(p) + " > " + std::to_string(kMaxGenericRadix) +
+                                  ", which this build does not support");
+        generic.push_back(p);
+        rest /= p;
+      }
+    }
+    // generic primes first (largest strides), powers of two next, small odd radices last:
+    // the late, short-stride stages then have odd strides and stay off the same banks.
+    radices = generic;
+    radices.insert(radices.end(), pow2.begin(), pow2.end());
+    radices.insert(radices.end(), odd.begin(), odd.end());
+    if (radices.empty()) radices.push_back(1);
+    if (int(radices.size()) > kMaxStages) throw std::domain_error("FFT plan has too many stages");
+    plan.n = n;
+    plan.n_stages = 0;
+    int len = n;
+    for (int r : radices) {
+      if (r == 1) continue;
+      plan.radix[plan.n_stages] = r;
+      plan.len[plan.n_stages] = len;
+      len /= r;
+      ++plan.n_stages;
+    }
+    std::vector<float2> t(n);
+    for (int i = 0; i < n; ++i) {
+      const double a = -2.0 * M_PI * double(i) / double(n);
+      t[i] = make_float2(float(std::cos(a)), float(std::sin(a)));
+    }
+    tw.Resize(n);
+    RDL_CUDA(cudaMemcpy(tw.get(), t.data(), n * sizeof(float2), cudaMemcpyHostToDevice));
+    plan.tw = tw.get();
+  }
+
+  // slot of frequency k after the forward (DIF) pass
+  uint32_t Slot(uint32_t k) const {
+    uint32_t pos = 0;
+    int len = plan.n;
+    for (int st = 0; st < plan.n_stages; ++st) {
+      const int r = plan.radix[st], m = len / r;
+      pos += (k % r) * m;
+      k /= r;
+      len = m;
+    }
+    return pos;
+  }
+};
+
+}  // namespace
+
+struct FftConvolver::Impl {
+  int W, H, n, pitch;
+  HostPlan row, col;
+  DeviceBuffer<uint32_t> perm;
+  DeviceBuffer<float2> split_tw;
+  DeviceBuffer<float2> work, kernel_spectrum;
+  DeviceBuffer<float> kernel_image;
+  int rows_per_cta = 1, row_threads = 256, row_stride = 0;
+  int cols_per_cta = 1, col_threads = 256, col_stride = 0;
+  size_t row_smem = 0, col_smem = 0;
+};
+
+FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width_(width), height_(height) {
+  Impl& d = *impl_;
+  try {
+    if (width < 2 || height < 1 || width % 2 != 0)
+      throw std::domain_error("FFT convolution needs an even image width (got " +
+                              std::to_string(width) + " x " + std::to_string(height) + ")");
+    d.W = int(width);
+    d.H = int(height);
+    d.n = d.W / 2;
+    d.pitch = (d.n + 1 + 3) & ~3;
+    d.row.Build(d.n);
+    d.col.Build(d.H);
+    std::vector<uint32_t> perm(d.n);
+    for (int k = 0; k < d.n; ++k) perm[k] = d.row.Slot(uint32_t(k));
+    d.perm.Resize(d.n);
+    RDL_CUDA(cudaMemcpy(d.perm.get(), perm.data(), d.n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    std::vector<float2> st(d.n + 1);
+    for (int k = 0; k <= d.n; ++k) {
+      const double a = -2.0 * M_PI * double(k) / double(d.W);
+      st[k] = make_float2(float(std::cos(a)), float(std::sin(a)));
+    }
+    d.split_tw.Resize(d.n + 1);
+    RDL_CUDA(cudaMemcpy(d.split_tw.get(), st.data(), (d.n + 1) * sizeof(float2), cudaMemcpyHostToDevice));
+
+    d.row_stride = PaddedLength(d.n);
+    const size_t row_bytes = size_t(d.row_stride) * sizeof(float2);
+    if (row_bytes > kMaxSmemBytes) throw std::domain_error("image row does not fit in shared memory");
+    d.rows_per_cta = int(std::clamp<size_t>(size_t(56 * 1024) / row_bytes, 1, 8));
+    d.row_smem = row_bytes * d.rows_per_cta;
+    d.row_threads = d.n * d.rows_per_cta >= 4096 ? 256 : 128;
+
+    d.col_stride = PaddedLength(d.H);
+    const size_t col_bytes = size_t(d.col_stride) * sizeof(float2);
+    if (col_bytes > kMaxSmemBytes) throw std::domain_error("image column does not fit in shared memory");
+    d.cols_per_cta = 4 * col_bytes <= kMaxSmemBytes ? 4 : (2 * col_bytes <= kMaxSmemBytes ? 2 : 1);
+    d.col_smem = col_bytes * d.cols_per_cta;
+    const int work_items = d.H * d.cols_per_cta;
+    d.col_threads = (work_items >= 4096 ? 512 : (work_items >= 1024 ? 256 : 64));
+
+    RDL_CUDA(cudaFuncSetAttribute(RowForwardKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(RowInverseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    d.work.Resize(size_t(d.H) * d.pitch);
+  } catch (...) {
+    delete impl_;
+    impl_ = nullptr;
+    throw;
+  }
+}
+
+FftConvolver::~FftConvolver() { delete impl_; }
+
+size_t FftConvolver::SpectrumSize() const { return size_t(impl_->H) * impl_->pitch; }
+
+void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (sw > size_t(d.W) || sh > size_t(d.H)) throw std::invalid_argument("source larger than the FFT frame");
+  RowParams p{};
+  p.src = src;
+  p.sw = int(sw);
+  p.sh = int(sh);
+  p.ox = (d.W - int(sw)) / 2;
+  p.oy = (d.H - int(sh)) / 2;
+  p.W = d.W;
+  p.H = d.H;
+  p.spec = d.work.get();
+  p.pitch = d.pitch;
+  p.plan = d.row.plan;
+  p.perm = d.perm.get();
+  p.split_tw = d.split_tw.get();
+  p.rows_per_cta = d.rows_per_cta;
+  p.seq_stride = d.row_stride;
+  const int grid = (int(sh) + d.rows_per_cta - 1) / d.rows_per_cta;
+  RowForwardKernel<<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  ++launches_;
+}
+
+void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectrum_out, cudaStream_t stream) {
+  Impl& d = *impl_;
+  ForwardRows(kernel_image, d.W, d.H, stream);
+  ColParams c{};
+  c.spec = d.work.get();
+  c.kspec_out = spectrum_out;
+  c.pitch = d.pitch;
+  c.n_cols = d.n + 1;
+  c.H = d.H;
+  c.y0 = 0;
+  c.y1 = d.H;
+  c.cols_per_cta = d.cols_per_cta;
+  c.seq_stride = d.col_stride;
+  c.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
+  c.plan = d.col.plan;
+  const int grid = (c.n_cols + d.cols_per_cta - 1) / d.cols_per_cta;
+  ColumnKernel<false><<<grid, d.col_threads, d.col_smem, stream>>>(c);
+  ++launches_;
+}
+
+void FftConvolver::MakeSmallKernelSpectrum(const float* small_kernel, size_t n, float2* spectrum_out,
+                                           cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (n > size_t(d.W) || n > size_t(d.H)) throw std::invalid_argument("convolution kernel larger than the image");
+  d.kernel_image.Reserve(size_t(d.W) * d.H);
+  RDL_CUDA(cudaMemsetAsync(d.kernel_image.get(), 0, size_t(d.W) * d.H * sizeof(float), stream));
+  const int total = int(n * n);
+  WrapSmallKernelKernel<<<std::min((total + 255) / 256, 1184), 256, 0, stream>>>(
+      d.kernel_image.get(), d.W, d.H, small_kernel, int(n));
+  ++launches_;
+  MakeKernelSpectrum(d.kernel_image.get(), spectrum_out, stream);
+}
+
+void FftConvolver::MakePsfKernelSpectrum(const float* psf, size_t pw, size_t ph, float2* spectrum_out,
+                                         cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (pw > size_t(d.W) || ph > size_t(d.H)) throw std::invalid_argument("PSF larger than the FFT frame");
+  d.kernel_image.Reserve(size_t(d.W) * d.H);
+  PreparePsfKernelKernel<<<1184, 256, 0, stream>>>(d.kernel_image.get(), d.W, d.H, psf, int(pw), int(ph));
+  ++launches_;
+  MakeKernelSpectrum(d.kernel_image.get(), spectrum_out, stream);
+}
+
+void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const float2* kernel_spectrum,
+                                float* dst, size_t dw, size_t dh, int mode, cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (dw > size_t(d.W) || dh > size_t(d.H)) throw std::invalid_argument("destination larger than the FFT frame");
+  ForwardRows(src, sw, sh, stream);
+  ColParams c{};
+  c.spec = d.work.get();
+  c.kspec = kernel_spectrum;
+  c.pitch = d.pitch;
+  c.n_cols = d.n + 1;
+  c.H = d.H;
+  c.y0 = (d.H - int(sh)) / 2;
+  c.y1 = c.y0 + int(sh);
+  c.out_y0 = (d.H - int(dh)) / 2;
+  c.out_y1 = c.out_y0 + int(dh);
+  c.cols_per_cta = d.cols_per_cta;
+  c.seq_stride = d.col_stride;
+  c.scale = 1.0f;
+  c.plan = d.col.plan;
+  const int cgrid = (c.n_cols + d.cols_per_cta - 1) / d.cols_per_cta;
+  ColumnKernel<true><<<cgrid, d.col_threads, d.col_smem, stream>>>(c);
+  ++launches_;
+  RowParams p{};
+  p.dst = dst;
+  p.sw = int(dw);
+  p.sh = int(dh);
+  p.ox = (d.W - int(dw)) / 2;
+  p.oy = c.out_y0;
+  p.W = d.W;
+  p.H = d.H;
+  p.spec = d.work.get();
+  p.pitch = d.pitch;
+  p.plan = d.row.plan;
+  p.perm = d.perm.get();
+  p.split_tw = d.split_tw.get();
+  p.rows_per_cta = d.rows_per_cta;
+  p.seq_stride = d.row_stride;
+  p.mode = mode;
+  const int grid = (int(dh) + d.rows_per_cta - 1) / d.rows_per_cta;
+  RowInverseKernel<<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  ++launches_;
+}
+
+void FftConvolver::SetKernel(const float* kernel, cudaStream_t stream) {
+  Impl& d = *impl_;
+  d.kernel_spectrum.Reserve(SpectrumSize());
+  MakeKernelSpectrum(kernel, d.kernel_spectrum.get(), stream);
+}
+
+void FftConvolver::Convolve(const float* in, float* out, cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (d.kernel_spectrum.empty()) throw std::invalid_argument("FftConvolver::Convolve without a kernel");
+  ConvolveWith(in, d.W, d.H, d.kernel_spectrum.get(), out, d.W, d.H, 0, stream);
+}
+
+FftConvolver& GetConvolver(rdl_handle& h, size_t width, size_t height) {
+  auto key = std::make_pair(width, height);
+  auto it = h.convolvers.find(key);
+  if (it == h.convolvers.end())
+    it = h.convolvers.emplace(key, std::make_shared<FftConvolver>(width, height)).first;
+  return *it->second;
+}
+
+}  // namespace rdl

@@ -25,6 +25,22 @@ class FftConvolver {
   void SetKernel(const float* kernel, cudaStream_t stream);
   // out = irfft2(rfft2(in) * kernel_spectrum) / (W*H); in may equal out.
   void Convolve(const float* in, float* out, cudaStream_t stream);
+
+  // -- building blocks used by the multiscale / sub-minor code --------------------------
+  // Number of float2 elements of one kernel spectrum of this frame size.
+  size_t SpectrumSize() const;
+  // spectrum_out = scaled half spectrum of a W x H kernel image (origin at pixel 0,0).
+  void MakeKernelSpectrum(const float* kernel_image, float2* spectrum_out, cudaStream_t stream);
+  // PrepareSmallConvolutionKernel (n x n kernel wrapped around the origin) + spectrum.
+  void MakeSmallKernelSpectrum(const float* small_kernel, size_t n, float2* spectrum_out,
+                               cudaStream_t stream);
+  // PrepareConvolutionKernel(Untrim(psf, pw x ph -> W x H)) + spectrum.
+  void MakePsfKernelSpectrum(const float* psf, size_t pw, size_t ph, float2* spectrum_out,
+                             cudaStream_t stream);
+  // Untrim(src, sw x sh) -> convolve -> Trim(dw x dh), fused epilogue:
+  // mode 0: dst = result, 1: dst -= result, 2: dst += result. src may equal dst.
+  void ConvolveWith(const float* src, size_t sw, size_t sh, const float2* kernel_spectrum,
+                    float* dst, size_t dw, size_t dh, int mode, cudaStream_t stream);
   uint64_t TakeLaunchCount() {
     const uint64_t n = launches_;
     launches_ = 0;
@@ -32,6 +48,7 @@ class FftConvolver {
   }
 
  private:
+  void ForwardRows(const float* src, size_t sw, size_t sh, cudaStream_t stream);
   struct Impl;
   Impl* impl_;
   size_t width_, height_;

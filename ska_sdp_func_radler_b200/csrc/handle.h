@@ -3,8 +3,10 @@
 #ifndef RDL_HANDLE_H_
 #define RDL_HANDLE_H_
 
+#include <map>
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/radler_b200.h"
@@ -101,6 +103,17 @@ struct Settings {  // deconvolution_algorithm.h:189-202
 };
 
 class MultiScaleState;
+class FftConvolver;
+
+// Device buffers of the sub-minor loop (grow-only, reused between runs).
+struct SubMinorBuffers {
+  DeviceBuffer<uint32_t> flags, block_counts, block_offsets, positions;
+  DeviceBuffer<float> residual, model, rms, candidates;
+  DeviceBuffer<unsigned char> state;
+  size_t n_selected = 0, capacity = 0, width = 0;
+  int n_images = 0;
+  uint64_t n_trace = 0;  // trace entries the last run produced
+};
 
 }  // namespace rdl
 
@@ -147,7 +160,14 @@ struct rdl_handle {
   // staging for RDL_MEM_HOST calls
   rdl::DeviceBuffer<float> stage_residual, stage_model, stage_psf;
 
+  rdl::SubMinorBuffers sub;
+  // FFT scratch: one W x H image, one kernel spectrum, one uploaded scale kernel
+  rdl::DeviceBuffer<float> fft_scratch, small_kernel;
+  rdl::DeviceBuffer<float2> fft_spectrum;
+  double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
+  // FFT engines by frame size (plans, twiddle tables, work spectrum); not cloned
+  std::map<std::pair<size_t, size_t>, std::shared_ptr<rdl::FftConvolver>> convolvers;
 };
 
 namespace rdl {
