@@ -255,8 +255,10 @@ class DeconvolutionAlgorithm:
         self._h = h
 
     def __del__(self):
-        if getattr(self, "_h", None):
-            lib().rdl_destroy(self._h)
+        # at interpreter shutdown module globals may already be gone
+        h, L = getattr(self, "_h", None), _lib
+        if h and L is not None:
+            L.rdl_destroy(h)
             self._h = None
 
     def _check(self, st: int):

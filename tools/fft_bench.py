@@ -8,7 +8,9 @@ import ska_sdp_func_radler_b200 as rdl
 
 sizes = [int(a) for a in sys.argv[1:]] or [4096, 4608, 8192, 9216, 9408]
 alg = rdl.GenericClean()
-stream = torch.cuda.current_stream().cuda_stream
+side = torch.cuda.Stream()  # a NULL stream would mean "the handle's own stream"
+torch.cuda.set_stream(side)
+stream = side.cuda_stream
 for n in sizes:
     n_img = 4
     imgs = torch.randn((n_img, n, n), device="cuda")
