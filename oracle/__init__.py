@@ -495,3 +495,171 @@ def add_shape_component(image, scale, x, y, gain, shape=0):
     assert image.dtype == np.float32 and image.flags.c_contiguous
     lib().orc_add_shape_component(_ptr(image), image.shape[1], image.shape[0], scale, x, y, gain,
                                   shape)
+
+
+# ---- oracle/_ref: the reference's OWN algorithm sources (oracle/ref_algo.cc) ------------
+class _RefConfig(C.Structure):
+    _fields_ = [("algorithm", C.c_int32), ("use_sub_minor_optimization", C.c_int32),
+                ("threshold", C.c_float), ("minor_loop_gain", C.c_float),
+                ("major_loop_gain", C.c_float), ("clean_border_ratio", C.c_float),
+                ("divergence_limit", C.c_float), ("max_iterations", C.c_uint64),
+                ("allow_negative", C.c_int32), ("stop_on_negative", C.c_int32),
+                ("ms_fast_sub_minor_loop", C.c_int32), ("ms_sub_minor_loop_gain", C.c_double),
+                ("ms_scale_bias", C.c_double), ("ms_max_scales", C.c_uint64),
+                ("ms_convolution_padding", C.c_double), ("ms_scale_list", C.POINTER(C.c_double)),
+                ("ms_n_scale_list", C.c_uint64), ("ms_shape", C.c_int32),
+                ("beam_size", C.c_double), ("pixel_scale", C.c_double),
+                ("track_components", C.c_int32), ("fit_mode", C.c_int32),
+                ("fit_terms", C.c_uint64), ("grid_width", C.c_uint64),
+                ("grid_height", C.c_uint64), ("thread_count", C.c_uint64),
+                ("squared_joins", C.c_int32)]
+
+
+class _RefResult(C.Structure):
+    _fields_ = [("has_start_peak", C.c_int32), ("start_peak", C.c_float), ("end_peak", C.c_float),
+                ("another_iteration_required", C.c_int32), ("iteration_number", C.c_uint64)]
+
+
+_refa_ready = False
+
+
+def _refa():
+    global _refa_ready
+    L = ref_lib()
+    if L is None:
+        return None
+    if not _refa_ready:
+        vp, u64 = C.c_void_p, C.c_uint64
+        L.refa_last_error.restype = C.c_char_p
+        L.refa_last_error.argtypes = [vp]
+        L.refa_create.restype = vp
+        L.refa_create.argtypes = [C.POINTER(_RefConfig), u64, u64, u64, u64, vp, vp, vp]
+        L.refa_destroy.argtypes = [vp]
+        L.refa_set_threshold.argtypes = [vp, C.c_double]
+        L.refa_set_minor_loop_gain.argtypes = [vp, C.c_double]
+        L.refa_set_auto_mask_mode.argtypes = [vp, C.c_int32, C.c_int32]
+        L.refa_set_clean_mask.argtypes = [vp, vp]
+        L.refa_set_rms_factor_image.argtypes = [vp, vp]
+        L.refa_set_iteration_number.argtypes = [vp, u64]
+        L.refa_set_max_iterations.argtypes = [vp, u64]
+        L.refa_set_major_iteration_threshold.argtypes = [vp, C.c_float]
+        L.refa_execute.argtypes = [vp, vp, vp, vp, u64, u64, u64, vp, vp, C.c_double,
+                                   C.POINTER(_RefResult)]
+        L.refa_iteration_number.restype = u64
+        L.refa_iteration_number.argtypes = [vp]
+        L.refa_scale_count.restype = u64
+        L.refa_scale_count.argtypes = [vp]
+        L.refa_scale_size.restype = C.c_float
+        L.refa_scale_size.argtypes = [vp, u64]
+        L.refa_scale_mask_count.restype = u64
+        L.refa_scale_mask_count.argtypes = [vp]
+        L.refa_scale_mask.argtypes = [vp, u64, vp]
+        _refa_ready = True
+    return L
+
+
+@dataclass
+class RefResult:
+    starting_peak_value: float | None
+    final_peak_value: float
+    another_iteration_required: bool
+    iteration_number: int
+
+
+# aocommon::PolarizationEnum order of oracle/ref_shim/aocommon/polarization.h
+POL = {"I": 0, "Q": 1, "U": 2, "V": 3, "RR": 4, "RL": 5, "LR": 6, "LL": 7, "XX": 8, "XY": 9,
+       "YX": 10, "YY": 11}
+
+
+class Reference:
+    """The reference's own GenericClean / MultiScaleAlgorithm / IuwtDeconvolution behind its
+    ParallelDeconvolution, driven like Radler::InitializeDeconvolutionAlgorithm + Perform do
+    (oracle/ref_algo.cc). algorithm: "generic", "multiscale" or "iuwt"."""
+
+    def __init__(self, algorithm, width, height, n_channels=1, pols=("I",), weights=None,
+                 frequencies=None, *, use_sub_minor_optimization=True, threshold=0.0,
+                 minor_loop_gain=0.1, major_loop_gain=1.0, clean_border_ratio=0.0,
+                 divergence_limit=4.0, max_iterations=500, allow_negative=True,
+                 stop_on_negative=False, fast_sub_minor_loop=True, sub_minor_loop_gain=0.2,
+                 scale_bias=0.6, max_scales=0, convolution_padding=1.1, scale_list=None, shape=0,
+                 beam_size=0.0, pixel_scale=1.0, track_components=False, fit_terms=0,
+                 grid=(1, 1), threads=0, squared_joins=False):
+        L = _refa()
+        if L is None:
+            raise RuntimeError("oracle/_ref/libradler_ref.so is not built")
+        sl = np.ascontiguousarray(scale_list if scale_list else [], np.float64)
+        cfg = _RefConfig(
+            {"generic": 0, "multiscale": 1, "iuwt": 2}[algorithm], int(use_sub_minor_optimization),
+            threshold, minor_loop_gain, major_loop_gain, clean_border_ratio, divergence_limit,
+            max_iterations, int(allow_negative), int(stop_on_negative), int(fast_sub_minor_loop),
+            sub_minor_loop_gain, scale_bias, max_scales, convolution_padding,
+            sl.ctypes.data_as(C.POINTER(C.c_double)), len(sl), shape, beam_size, pixel_scale,
+            int(track_components), 1 if fit_terms else 0, fit_terms, grid[0], grid[1],
+            threads or (os.cpu_count() or 1), int(squared_joins))
+        p = np.ascontiguousarray([POL[x] for x in pols], np.int32)
+        w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+        f = None if frequencies is None else np.ascontiguousarray(frequencies, np.float64)
+        self.width, self.height, self.n_channels, self.n_pol = width, height, n_channels, len(pols)
+        self._major_loop_gain = major_loop_gain
+        self._h = L.refa_create(C.byref(cfg), width, height, n_channels, len(pols), _ptr(p),
+                                _ptr(w), _ptr(f))
+        if not self._h:
+            raise RuntimeError(L.refa_last_error(None).decode())
+
+    def __del__(self):
+        if getattr(self, "_h", None) and _ref is not None:
+            _ref.refa_destroy(self._h)
+            self._h = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(_ref.refa_last_error(self._h).decode())
+
+    def set_threshold(self, v): self._check(_ref.refa_set_threshold(self._h, v))
+    def set_minor_loop_gain(self, v): self._check(_ref.refa_set_minor_loop_gain(self._h, v))
+    def set_major_loop_gain(self, v): self._major_loop_gain = v
+    def set_auto_mask_mode(self, track, use):
+        self._check(_ref.refa_set_auto_mask_mode(self._h, int(track), int(use)))
+    def set_iteration_number(self, n): self._check(_ref.refa_set_iteration_number(self._h, n))
+    def set_max_iterations(self, n): self._check(_ref.refa_set_max_iterations(self._h, n))
+    def set_major_iteration_threshold(self, v):
+        self._check(_ref.refa_set_major_iteration_threshold(self._h, v))
+
+    def set_clean_mask(self, mask):
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        self._check(_ref.refa_set_clean_mask(self._h, _ptr(m)))
+
+    def set_rms_factor_image(self, image):
+        a = None if image is None else _f32(image)
+        self._check(_ref.refa_set_rms_factor_image(self._h, _ptr(a)))
+
+    def execute(self, residual, model, psfs, psf_offsets=None) -> RefResult:
+        """residual/model [n_images,H,W] updated in place; psfs [n_channels,h,w] or
+        [n_dd,n_channels,h,w] with psf_offsets [(x,y)] for direction-dependent PSFs."""
+        assert residual.dtype == np.float32 and residual.flags.c_contiguous
+        assert model.dtype == np.float32 and model.flags.c_contiguous
+        psfs = _f32(psfs)
+        if psfs.ndim == 3:
+            psfs = psfs[None]
+        n_dd, _, ph, pw = psfs.shape
+        ox = oy = None
+        if psf_offsets is not None:
+            ox = np.ascontiguousarray([o[0] for o in psf_offsets], np.int64)
+            oy = np.ascontiguousarray([o[1] for o in psf_offsets], np.int64)
+        out = _RefResult()
+        self._check(_ref.refa_execute(self._h, _ptr(residual), _ptr(model), _ptr(psfs), n_dd, pw,
+                                      ph, _ptr(ox), _ptr(oy), self._major_loop_gain,
+                                      C.byref(out)))
+        return RefResult(out.start_peak if out.has_start_peak else None, out.end_peak,
+                         bool(out.another_iteration_required), out.iteration_number)
+
+    @property
+    def iteration_number(self): return _ref.refa_iteration_number(self._h)
+
+    def scale_sizes(self):
+        return [_ref.refa_scale_size(self._h, i) for i in range(_ref.refa_scale_count(self._h))]
+
+    def scale_mask(self, i):
+        m = np.zeros((self.height, self.width), np.uint8)
+        self._check(_ref.refa_scale_mask(self._h, i, _ptr(m)))
+        return m

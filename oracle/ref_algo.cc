@@ -1,0 +1,323 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.
+// extern "C" driver around the reference's OWN algorithm sources, compiled where they lie under
+// /root/reference/cpp (oracle/Makefile target `ref`): image_set.cc, work_table.cc,
+// algorithms/{deconvolution_algorithm, generic_clean, subminor_loop, threaded_deconvolution_tools,
+// multiscale_algorithm, multiscale/multiscale_transforms, iuwt_deconvolution_algorithm,
+// iuwt/*, parallel_deconvolution}.cc, math/{peak_finder, dijkstra_splitter}.cc, ...
+// The un-vendored third-party leaves (aocommon Image / loops / logger, schaapcommon Convolve /
+// SpectralFitter) are OUR stand-ins under ref_shim/ (see each header). The call sequence below
+// is the one Radler::InitializeDeconvolutionAlgorithm (radler.cc:333-395) and Radler::Perform
+// (radler.cc:241-273) make: build the algorithm, apply the settings, hand it to
+// ParallelDeconvolution, ExecuteMajorIteration on ImageSets.
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "algorithms/generic_clean.h"
+#include "algorithms/iuwt_deconvolution.h"
+#include "algorithms/multiscale_algorithm.h"
+#include "algorithms/parallel_deconvolution.h"
+#include "image_set.h"
+#include "settings.h"
+#include "work_table.h"
+
+using namespace radler;
+
+extern "C" {
+
+struct refa_config {
+  int32_t algorithm;  // 0 GenericClean, 1 MultiScaleAlgorithm, 2 IuwtDeconvolution
+  int32_t use_sub_minor_optimization;
+  float threshold, minor_loop_gain, major_loop_gain, clean_border_ratio, divergence_limit;
+  uint64_t max_iterations;
+  int32_t allow_negative, stop_on_negative;
+  int32_t ms_fast_sub_minor_loop;
+  double ms_sub_minor_loop_gain, ms_scale_bias;
+  uint64_t ms_max_scales;
+  double ms_convolution_padding;
+  const double* ms_scale_list;
+  uint64_t ms_n_scale_list;
+  int32_t ms_shape;
+  double beam_size, pixel_scale;
+  int32_t track_components;
+  int32_t fit_mode;  // 0 none, 1 polynomial
+  uint64_t fit_terms;
+  uint64_t grid_width, grid_height;
+  uint64_t thread_count;
+  int32_t squared_joins;
+};
+
+struct refa_result {
+  int32_t has_start_peak;
+  float start_peak, end_peak;
+  int32_t another_iteration_required;
+  uint64_t iteration_number;  // of the first algorithm (sum over facets in grid mode)
+};
+
+}  // extern "C"
+
+namespace {
+
+// Accessor that is never used: the driver fills ImageSets directly.
+class UnusedAccessor final : public aocommon::ImageAccessor {
+ public:
+  void Load(float*) const override { throw std::runtime_error("unused accessor"); }
+  void Store(const float*) override { throw std::runtime_error("unused accessor"); }
+};
+
+struct Handle {
+  Settings settings;
+  std::unique_ptr<WorkTable> table;
+  std::unique_ptr<algorithms::ParallelDeconvolution> parallel;
+  size_t width = 0, height = 0, n_channels = 0, n_pol = 0;
+  std::unique_ptr<bool[]> mask;
+  std::string error;
+};
+
+thread_local std::string g_error;
+
+template <typename F>
+int Guard(Handle* h, F&& f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& e) {
+    (h ? h->error : g_error) = e.what();
+    return 1;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* refa_last_error(const void* handle) {
+  return handle ? static_cast<const Handle*>(handle)->error.c_str() : g_error.c_str();
+}
+
+void* refa_create(const refa_config* c, uint64_t width, uint64_t height, uint64_t n_channels,
+                  uint64_t n_pol, const int32_t* polarizations, const double* channel_weights,
+                  const double* channel_frequencies) {
+  auto h = std::make_unique<Handle>();
+  const int rc = Guard(nullptr, [&] {
+    Settings& s = h->settings;
+    s.trimmed_image_width = width;
+    s.trimmed_image_height = height;
+    s.channels_out = n_channels;
+    s.pixel_scale.x = s.pixel_scale.y = c->pixel_scale;
+    s.thread_count = c->thread_count ? c->thread_count : 1;
+    s.absolute_threshold = c->threshold;
+    s.minor_loop_gain = c->minor_loop_gain;
+    s.major_loop_gain = c->major_loop_gain;
+    s.border_ratio = c->clean_border_ratio;
+    s.divergence_limit = c->divergence_limit;
+    s.minor_iteration_count = c->max_iterations;
+    s.allow_negative_components = c->allow_negative != 0;
+    s.stop_on_negative_components = c->stop_on_negative != 0;
+    s.squared_joins = c->squared_joins != 0;
+    s.save_source_list = c->track_components != 0;
+    s.generic.use_sub_minor_optimization = c->use_sub_minor_optimization != 0;
+    s.multiscale.fast_sub_minor_loop = c->ms_fast_sub_minor_loop != 0;
+    s.multiscale.sub_minor_loop_gain = c->ms_sub_minor_loop_gain;
+    s.multiscale.scale_bias = c->ms_scale_bias;
+    s.multiscale.max_scales = c->ms_max_scales;
+    s.multiscale.convolution_padding = c->ms_convolution_padding;
+    s.multiscale.scale_list.assign(c->ms_scale_list, c->ms_scale_list + c->ms_n_scale_list);
+    s.multiscale.shape =
+        c->ms_shape == 1 ? MultiscaleShape::kGaussianShape : MultiscaleShape::kTaperedQuadraticShape;
+    s.parallel.grid_width = c->grid_width ? c->grid_width : 1;
+    s.parallel.grid_height = c->grid_height ? c->grid_height : 1;
+    s.parallel.max_threads = s.thread_count;
+    s.spectral_fitting.mode = c->fit_mode == 1
+                                  ? schaapcommon::fitters::SpectralFittingMode::kPolynomial
+                                  : schaapcommon::fitters::SpectralFittingMode::kNoFitting;
+    s.spectral_fitting.terms = c->fit_terms;
+    s.algorithm_type = c->algorithm == 0   ? AlgorithmType::kGenericClean
+                       : c->algorithm == 1 ? AlgorithmType::kMultiscale
+                                           : AlgorithmType::kIuwt;
+    h->width = width;
+    h->height = height;
+    h->n_channels = n_channels;
+    h->n_pol = n_pol;
+
+    // one original channel per deconvolution channel; entries ordered [channel][pol]
+    h->table = std::make_unique<WorkTable>(std::vector<PsfOffset>{}, n_channels, n_channels);
+    for (size_t ch = 0; ch != n_channels; ++ch) {
+      for (size_t p = 0; p != n_pol; ++p) {
+        auto e = std::make_unique<WorkTableEntry>();
+        const double f = channel_frequencies ? channel_frequencies[ch] : 1.0e8 + 1.0e6 * ch;
+        e->band_start_frequency = f;
+        e->band_end_frequency = f;
+        e->polarization = polarizations ? aocommon::PolarizationEnum(polarizations[p])
+                                        : aocommon::PolarizationEnum::StokesI;
+        e->original_channel_index = ch;
+        e->image_weight = channel_weights ? channel_weights[ch] : 1.0;
+        e->model_accessor = std::make_unique<UnusedAccessor>();
+        e->residual_accessor = std::make_unique<UnusedAccessor>();
+        if (p == 0) e->psf_accessors.emplace_back(std::make_unique<UnusedAccessor>());
+        h->table->AddEntry(std::move(e));
+      }
+    }
+
+    // Radler::InitializeDeconvolutionAlgorithm, radler.cc:348-388
+    std::unique_ptr<algorithms::DeconvolutionAlgorithm> algorithm;
+    switch (s.algorithm_type) {
+      case AlgorithmType::kGenericClean:
+        algorithm =
+            std::make_unique<algorithms::GenericClean>(s.generic.use_sub_minor_optimization);
+        break;
+      case AlgorithmType::kMultiscale:
+        algorithm = std::make_unique<algorithms::MultiScaleAlgorithm>(
+            s.multiscale, c->beam_size, s.pixel_scale.x, s.pixel_scale.y, s.save_source_list);
+        break;
+      default:
+        algorithm = std::make_unique<algorithms::IuwtDeconvolution>();
+        break;
+    }
+    algorithm->SetMaxIterations(s.minor_iteration_count);
+    algorithm->SetThreshold(s.absolute_threshold);
+    algorithm->SetMinorLoopGain(s.minor_loop_gain);
+    algorithm->SetMajorLoopGain(s.major_loop_gain);
+    algorithm->SetCleanBorderRatio(s.border_ratio);
+    algorithm->SetDivergenceLimit(s.divergence_limit);
+    algorithm->SetAllowNegativeComponents(s.allow_negative_components);
+    algorithm->SetStopOnNegativeComponents(s.stop_on_negative_components);
+    // Radler::CreateSpectralFitter, radler.cc:318-331
+    std::vector<double> frequencies;
+    std::vector<float> weights;
+    if (s.spectral_fitting.mode != schaapcommon::fitters::SpectralFittingMode::kNoFitting)
+      ImageSet::CalculateDeconvolutionFrequencies(*h->table, frequencies, weights);
+    algorithm->SetSpectralFitter(
+        std::make_unique<schaapcommon::fitters::SpectralFitter>(
+            s.spectral_fitting.mode, s.spectral_fitting.terms, std::move(frequencies),
+            std::move(weights)),
+        n_pol);
+    h->parallel = std::make_unique<algorithms::ParallelDeconvolution>(h->settings);
+    h->parallel->SetAlgorithm(std::move(algorithm));
+  });
+  return rc == 0 ? h.release() : nullptr;
+}
+
+void refa_destroy(void* handle) { delete static_cast<Handle*>(handle); }
+
+int refa_set_threshold(void* handle, double v) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->SetThreshold(v); });
+}
+int refa_set_minor_loop_gain(void* handle, double v) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->SetMinorLoopGain(v); });
+}
+int refa_set_auto_mask_mode(void* handle, int32_t track, int32_t use) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->SetAutoMaskMode(track != 0, use != 0); });
+}
+int refa_set_clean_mask(void* handle, const uint8_t* mask) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] {
+    if (!mask) {
+      h->mask.reset();
+      h->parallel->SetCleanMask(nullptr);
+      return;
+    }
+    const size_t n = h->width * h->height;
+    h->mask.reset(new bool[n]);
+    for (size_t i = 0; i != n; ++i) h->mask[i] = mask[i] != 0;
+    h->parallel->SetCleanMask(h->mask.get());
+  });
+}
+int refa_set_rms_factor_image(void* handle, const float* image) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] {
+    aocommon::Image img;
+    if (image) {
+      img = aocommon::Image(h->width, h->height);
+      std::memcpy(img.Data(), image, h->width * h->height * sizeof(float));
+    }
+    h->parallel->SetRmsFactorImage(std::move(img));
+  });
+}
+int refa_set_iteration_number(void* handle, uint64_t n) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->FirstAlgorithm().SetIterationNumber(n); });
+}
+int refa_set_max_iterations(void* handle, uint64_t n) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->FirstAlgorithm().SetMaxIterations(n); });
+}
+int refa_set_major_iteration_threshold(void* handle, float v) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] { h->parallel->FirstAlgorithm().SetMajorIterationThreshold(v); });
+}
+
+// residual / model: n_channels*n_pol planes of width*height floats, updated in place.
+// psfs: n_dd * n_channels planes of psf_width*psf_height floats ([dd][channel]).
+int refa_execute(void* handle, float* residual, float* model, const float* psfs, uint64_t n_dd,
+                 uint64_t psf_width, uint64_t psf_height, const int64_t* psf_offset_x,
+                 const int64_t* psf_offset_y, double major_loop_gain, refa_result* out) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] {
+    const size_t n = h->width * h->height, n_images = h->n_channels * h->n_pol;
+    const std::set<aocommon::PolarizationEnum> linked;  // empty = all linked
+    ImageSet data(*h->table, h->settings.squared_joins, linked, h->width, h->height);
+    ImageSet mdl(*h->table, h->settings.squared_joins, linked, h->width, h->height);
+    for (size_t i = 0; i != n_images; ++i) {
+      std::memcpy(data.Data(i), residual + i * n, n * sizeof(float));
+      std::memcpy(mdl.Data(i), model + i * n, n * sizeof(float));
+    }
+    const size_t pn = psf_width * psf_height;
+    std::vector<std::vector<aocommon::Image>> psf_images(n_dd);
+    std::vector<PsfOffset> offsets;
+    for (size_t d = 0; d != n_dd; ++d) {
+      for (size_t c = 0; c != h->n_channels; ++c) {
+        aocommon::Image img(psf_width, psf_height);
+        std::memcpy(img.Data(), psfs + (d * h->n_channels + c) * pn, pn * sizeof(float));
+        psf_images[d].push_back(std::move(img));
+      }
+      if (psf_offset_x && psf_offset_y) offsets.emplace_back(psf_offset_x[d], psf_offset_y[d]);
+    }
+    const algorithms::ParallelDeconvolutionResult r =
+        h->parallel->ExecuteMajorIteration(data, mdl, psf_images, offsets, major_loop_gain);
+    for (size_t i = 0; i != n_images; ++i) {
+      std::memcpy(residual + i * n, data.Data(i), n * sizeof(float));
+      std::memcpy(model + i * n, mdl.Data(i), n * sizeof(float));
+    }
+    out->has_start_peak = r.start_peak.HasValue();
+    out->start_peak = r.start_peak.ValueOr(0.0f);
+    out->end_peak = r.end_peak.ValueOr(0.0f);
+    out->another_iteration_required = r.another_iteration_required;
+    out->iteration_number = h->parallel->FirstAlgorithm().IterationNumber();
+  });
+}
+
+uint64_t refa_iteration_number(void* handle) {
+  return static_cast<Handle*>(handle)->parallel->FirstAlgorithm().IterationNumber();
+}
+
+uint64_t refa_scale_count(void* handle) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (h->settings.algorithm_type != AlgorithmType::kMultiscale) return 0;
+  return static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm()).ScaleCount();
+}
+float refa_scale_size(void* handle, uint64_t i) {
+  Handle* h = static_cast<Handle*>(handle);
+  return static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm()).ScaleSize(i);
+}
+uint64_t refa_scale_mask_count(void* handle) {
+  Handle* h = static_cast<Handle*>(handle);
+  return static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
+      .GetScaleMaskCount();
+}
+int refa_scale_mask(void* handle, uint64_t i, uint8_t* out) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] {
+    auto& m = static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
+                  .GetScaleMask(i);
+    for (size_t k = 0; k != m.size(); ++k) out[k] = m[k] ? 1 : 0;
+  });
+}
+
+}  // extern "C"

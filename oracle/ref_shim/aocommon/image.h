@@ -7,7 +7,10 @@
 #ifndef AOCOMMON_IMAGE_H_
 #define AOCOMMON_IMAGE_H_
 
+#include <math.h>
+
 #include <algorithm>
+#include <cassert>
 #include <cmath>
 #include <complex>
 #include <cstddef>
@@ -15,6 +18,8 @@
 #include <limits>
 #include <utility>
 #include <vector>
+
+#include "uvector.h"
 
 namespace aocommon {
 

@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <vector>
 
+#include "algorithms/multiscale/multiscale_transforms.h"
 #include "algorithms/simple_clean.h"
 #include "math/dijkstra_splitter.h"
 #include "math/peak_finder.h"
@@ -102,5 +103,34 @@ void ref_get_bounding_mask(const uint8_t* vertical_mask, uint64_t w, uint64_t h,
   *sub_y = y;
   *sub_w = sw;
   *sub_h = sh;
+}
+
+// multiscale_transforms.h:91-195 / multiscale_transforms.cc:11-23 of the reference itself
+uint64_t ref_make_shape_function(float scale, uint64_t max_n, int shape, float* out) {
+  size_t n = 0;
+  const aocommon::Image k = algorithms::multiscale::MultiScaleTransforms::MakeShapeFunction(
+      scale, n, max_n, shape == 1 ? MultiscaleShape::kGaussianShape
+                                  : MultiscaleShape::kTaperedQuadraticShape);
+  if (out) std::copy_n(k.Data(), n * n, out);
+  return n;
+}
+void ref_ms_transform(float* images, uint64_t n_images, uint64_t w, uint64_t h, float scale,
+                      int shape) {
+  algorithms::multiscale::MultiScaleTransforms t(
+      w, h, shape == 1 ? MultiscaleShape::kGaussianShape : MultiscaleShape::kTaperedQuadraticShape);
+  std::vector<aocommon::Image> list;
+  for (uint64_t i = 0; i != n_images; ++i) {
+    list.emplace_back(w, h);
+    std::copy_n(images + i * w * h, w * h, list.back().Data());
+  }
+  aocommon::Image scratch(w, h);
+  t.Transform(list, scratch, scale);
+  for (uint64_t i = 0; i != n_images; ++i) std::copy_n(list[i].Data(), w * h, images + i * w * h);
+}
+void ref_add_shape_component(float* image, uint64_t w, uint64_t h, float scale, uint64_t x,
+                             uint64_t y, float gain, int shape) {
+  algorithms::multiscale::MultiScaleTransforms::AddShapeComponent(
+      image, w, h, scale, x, y, gain,
+      shape == 1 ? MultiscaleShape::kGaussianShape : MultiscaleShape::kTaperedQuadraticShape);
 }
 }

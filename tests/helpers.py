@@ -75,6 +75,21 @@ def hogbom_case(n, n_channels=1, seed=1, n_src=None, fwhm=4.0, noise=1e-3, alpha
     return res, psfs, weights, freqs
 
 
+def multiscale_case(n, n_channels=1, seed=1, fwhm=6.0, noise=1e-3):
+    sky = point_source_sky(n, max(4, n * n // 8192), seed=seed, margin=n // 8)
+    sky = add_blobs(sky, max(2, n * n // 65536), seed=seed + 2)
+    rng = np.random.default_rng(seed + 100)
+    freqs = np.linspace(100e6, 250e6, n_channels) if n_channels > 1 else np.array([150e6])
+    res = np.zeros((n_channels, n, n), np.float32)
+    psfs = np.zeros((n_channels, n, n), np.float32)
+    alpha = rng.uniform(-1.2, -0.2)
+    for c in range(n_channels):
+        psfs[c] = gaussian_psf(n, fwhm * (freqs[0] / freqs[c]) ** 0.25)
+        res[c] = dirty_image(sky * (freqs[c] / freqs[0]) ** alpha, psfs[c], noise, seed=6 + c)
+    weights = rng.uniform(0.5, 1.5, n_channels).astype(np.float32) if n_channels > 1 else None
+    return res, psfs, weights, freqs
+
+
 def plus_psf_fixture(shift_x=0, shift_y=0, factor=2.5, n=64):
     """The 5-pixel 'plus' PSF and residual = factor * shifted PSF of cpp/test/test_radler.cc:54-82."""
     c = n // 2 * n + n // 2

@@ -8,27 +8,12 @@ import math
 import numpy as np
 import pytest
 
-from helpers import add_blobs, dirty_image, gaussian_psf, plus_psf_fixture, point_source_sky
+from helpers import multiscale_case, plus_psf_fixture
 
 pytestmark = pytest.mark.gpu
 REL_TOL = 1e-5
 NEAR_TIE_RTOL = 5e-5      # value gap under which two adjacent pixels count as tied
 NEAR_TIE_IMAGE_TOL = 2e-3  # image tolerance once a tie was broken differently
-
-
-def multiscale_case(n, n_channels=1, seed=1, fwhm=6.0, noise=1e-3):
-    sky = point_source_sky(n, max(4, n * n // 8192), seed=seed, margin=n // 8)
-    sky = add_blobs(sky, max(2, n * n // 65536), seed=seed + 2)
-    rng = np.random.default_rng(seed + 100)
-    freqs = np.linspace(100e6, 250e6, n_channels) if n_channels > 1 else np.array([150e6])
-    res = np.zeros((n_channels, n, n), np.float32)
-    psfs = np.zeros((n_channels, n, n), np.float32)
-    alpha = rng.uniform(-1.2, -0.2)
-    for c in range(n_channels):
-        psfs[c] = gaussian_psf(n, fwhm * (freqs[0] / freqs[c]) ** 0.25)
-        res[c] = dirty_image(sky * (freqs[c] / freqs[0]) ** alpha, psfs[c], noise, seed=6 + c)
-    weights = rng.uniform(0.5, 1.5, n_channels).astype(np.float32) if n_channels > 1 else None
-    return res, psfs, weights, freqs
 
 
 def run_both(rdl, oracle, res, psfs, weights, settings, beam=6.0, ms_kwargs=None, fit=None,
