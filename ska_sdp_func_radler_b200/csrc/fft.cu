@@ -305,6 +305,88 @@ __device__ __forceinline__ void RunFft(float2* s, int n_seq, int seq_stride, con
   }
 }
 
+// ---- column transforms on [len][TC] tiles ----------------------------------------------
+// A tile holds TC adjacent spectrum columns (TC * 8 bytes = whole 128-byte lines of every
+// spectrum row) with the column index fastest, so global loads/stores are full lines and the
+// TC lanes that share a butterfly index touch consecutive shared-memory words.
+template <int R, bool INV, int TC>
+__device__ __forceinline__ void TileStage(float2* s, int n, int L, const float2* __restrict__ tw) {
+  const int m = L / R;
+  const int tw_step = n / L;
+  const int work = (n / R) * TC;
+  for (int i = threadIdx.x; i < work; i += blockDim.x) {
+    const int c = i % TC, t = i / TC;
+    const int b = t / m, j = t - b * m;
+    float2* p = s + (b * L + j) * TC + c;
+    float2 v[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) v[q] = p[q * m * TC];
+    if (INV && m > 1) {
+#pragma unroll
+      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], Conj(__ldg(tw + j * q * tw_step)));
+    }
+    Dft<R, INV>::Run(v);
+    if (!INV && m > 1) {
+#pragma unroll
+      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], __ldg(tw + j * q * tw_step));
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) p[q * m * TC] = v[q];
+  }
+}
+
+template <bool INV, int TC>
+__device__ void TileGenericStage(float2* s, int n, int L, int p, const float2* __restrict__ tw) {
+  const int m = L / p;
+  const int tw_step = n / L;
+  const int root_step = n / p;
+  const int work = (n / p) * TC;
+  for (int i = threadIdx.x; i < work; i += blockDim.x) {
+    const int c = i % TC, t = i / TC;
+    const int b = t / m, j = t - b * m;
+    float2* ptr = s + (b * L + j) * TC + c;
+    float2 x[kMaxGenericRadix];
+    for (int q = 0; q < p; ++q) {
+      float2 v = ptr[q * m * TC];
+      if (INV && m > 1) v = CMul(v, Conj(__ldg(tw + j * q * tw_step)));
+      x[q] = v;
+    }
+    for (int q = 0; q < p; ++q) {
+      float2 acc = x[0];
+      int idx = 0;
+      for (int k = 1; k < p; ++k) {
+        idx += q;
+        if (idx >= p) idx -= p;
+        float2 r = __ldg(tw + idx * root_step);
+        if (INV) r.y = -r.y;
+        acc = acc + CMul(x[k], r);
+      }
+      if (!INV && m > 1) acc = CMul(acc, __ldg(tw + j * q * tw_step));
+      ptr[q * m * TC] = acc;
+    }
+  }
+}
+
+// Forward: natural order in, digit-reversed out; inverse the other way. Leaves the block
+// synchronised.
+template <bool INV, int TC>
+__device__ __forceinline__ void RunTileFft(float2* s, const Plan& plan) {
+  for (int k = 0; k < plan.n_stages; ++k) {
+    const int st = INV ? plan.n_stages - 1 - k : k;
+    const int n = plan.n, L = plan.len[st];
+    switch (plan.radix[st]) {
+      case 8: TileStage<8, INV, TC>(s, n, L, plan.tw); break;
+      case 4: TileStage<4, INV, TC>(s, n, L, plan.tw); break;
+      case 2: TileStage<2, INV, TC>(s, n, L, plan.tw); break;
+      case 3: TileStage<3, INV, TC>(s, n, L, plan.tw); break;
+      case 5: TileStage<5, INV, TC>(s, n, L, plan.tw); break;
+      case 7: TileStage<7, INV, TC>(s, n, L, plan.tw); break;
+      default: TileGenericStage<INV, TC>(s, n, L, plan.radix[st], plan.tw); break;
+    }
+    __syncthreads();
+  }
+}
+
 struct RowParams {
   // real image side
   const float* src;  // forward: source image (sw x sh)
@@ -392,55 +474,91 @@ struct ColParams {
   float2* spec;          // work spectrum, transformed in place
   const float2* kspec;   // kernel spectrum to multiply with (convolve mode)
   float2* kspec_out;     // forward-only mode: where the scaled spectrum goes
-  int pitch, n_cols, H;
+  int pitch, H;
+  int H1, H2;            // H = H1 * H2: column index y = r + H1 * j  (r < H1, j < H2)
   int y0, y1;            // rows of `spec` that hold data (others are zero by construction)
   int out_y0, out_y1;    // rows the inverse row pass will read
-  int cols_per_cta, seq_stride;
   float scale;
-  Plan plan;             // n = H
+  Plan plan1;            // n = H1 (contiguous row blocks)
+  Plan plan2;            // n = H2 (rows at stride H1)
+  const float2* tw_h;    // exp(-2 pi i t / H), t in [0, H)
+  const uint32_t* freq2; // frequency held by slot s after the forward H2 pass
 };
 
-template <bool CONVOLVE>
-__global__ void __launch_bounds__(512, 1) ColumnKernel(const __grid_constant__ ColParams p) {
+constexpr int kTileCols = 16;  // 16 complex columns = one 128-byte line per spectrum row
+
+// Four-step column transform, step 1 (forward) / step 3 (inverse): the H2-point transforms
+// over rows r, r + H1, r + 2 H1, ... of one column tile, fused with the step twiddle
+// w_H^(r k2). Forward leaves frequency k2 in the row block of its slot, so step 2 works on H1
+// CONTIGUOUS rows. One CTA per (column tile, r).
+template <bool INV, int TC>
+__global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant__ ColParams p) {
   extern __shared__ float2 smem[];
-  const int H = p.H, cx = p.cols_per_cta;
-  const int c0 = blockIdx.x * cx;
-  const int n_seq = min(cx, p.n_cols - c0);
-  const int rows_in = p.y1 - p.y0;
-  for (int i = threadIdx.x; i < rows_in * cx; i += blockDim.x) {
-    const int r = i / cx, c = i - r * cx;
-    if (c < n_seq) smem[c * p.seq_stride + Pad(p.y0 + r)] = p.spec[size_t(p.y0 + r) * p.pitch + c0 + c];
-  }
-  if (rows_in < H) {
-    const int rows_zero = H - rows_in;
-    for (int i = threadIdx.x; i < rows_zero * cx; i += blockDim.x) {
-      const int r = i / cx, c = i - r * cx;
-      const int y = r < p.y0 ? r : r + rows_in;
-      if (c < n_seq) smem[c * p.seq_stride + Pad(y)] = make_float2(0.0f, 0.0f);
+  const int r = blockIdx.y;
+  const int c0 = blockIdx.x * TC;
+  const int H1 = p.H1, H2 = p.H2;
+  float2* base = p.spec + size_t(r) * p.pitch + c0;
+  const size_t step = size_t(H1) * p.pitch;
+  for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
+    const int j = i / TC, c = i - j * TC;
+    float2 v;
+    if (!INV) {
+      const int y = r + H1 * j;
+      v = (y >= p.y0 && y < p.y1) ? base[j * step + c] : make_float2(0.0f, 0.0f);
+    } else {
+      v = CMul(base[j * step + c], Conj(__ldg(p.tw_h + r * int(__ldg(p.freq2 + j)))));
     }
+    smem[i] = v;
   }
   __syncthreads();
-  RunFft<false>(smem, n_seq, p.seq_stride, p.plan);
+  RunTileFft<INV, TC>(smem, p.plan2);
+  for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
+    const int j = i / TC, c = i - j * TC;
+    if (!INV) {
+      base[j * step + c] = CMul(smem[i], __ldg(p.tw_h + r * int(__ldg(p.freq2 + j))));
+    } else {
+      const int y = r + H1 * j;
+      if (y >= p.out_y0 && y < p.out_y1) base[j * step + c] = smem[i];
+    }
+  }
+}
+
+// Step 2: H1-point transforms over the contiguous rows of slot s, times the kernel spectrum,
+// and straight back (inverse H1-point transforms) — or, for a kernel image, the scaled
+// spectrum written out. With H2 == 1 this is the whole column transform in one pass.
+template <bool CONVOLVE, int TC>
+__global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__ ColParams p) {
+  extern __shared__ float2 smem[];
+  const int c0 = blockIdx.x * TC;
+  const int H1 = p.H1;
+  const size_t row0 = size_t(blockIdx.y) * H1;
+  float2* base = p.spec + row0 * p.pitch + c0;
+  const bool whole = p.H2 == 1;
+  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
+    const int y = i / TC, c = i - y * TC;
+    smem[i] = (!whole || (y >= p.y0 && y < p.y1)) ? base[size_t(y) * p.pitch + c]
+                                                    : make_float2(0.0f, 0.0f);
+  }
+  __syncthreads();
+  RunTileFft<false, TC>(smem, p.plan1);
   if (!CONVOLVE) {
-    for (int i = threadIdx.x; i < H * cx; i += blockDim.x) {
-      const int r = i / cx, c = i - r * cx;
-      if (c < n_seq) p.kspec_out[size_t(r) * p.pitch + c0 + c] = p.scale * smem[c * p.seq_stride + Pad(r)];
+    float2* out = p.kspec_out + row0 * p.pitch + c0;
+    for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
+      const int y = i / TC, c = i - y * TC;
+      out[size_t(y) * p.pitch + c] = p.scale * smem[i];
     }
     return;
   }
-  for (int i = threadIdx.x; i < H * cx; i += blockDim.x) {
-    const int r = i / cx, c = i - r * cx;
-    if (c < n_seq) {
-      float2* v = smem + c * p.seq_stride + Pad(r);
-      *v = CMul(*v, __ldg(p.kspec + size_t(r) * p.pitch + c0 + c));
-    }
+  const float2* k = p.kspec + row0 * p.pitch + c0;
+  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
+    const int y = i / TC, c = i - y * TC;
+    smem[i] = CMul(smem[i], __ldg(k + size_t(y) * p.pitch + c));
   }
   __syncthreads();
-  RunFft<true>(smem, n_seq, p.seq_stride, p.plan);
-  const int rows_out = p.out_y1 - p.out_y0;
-  for (int i = threadIdx.x; i < rows_out * cx; i += blockDim.x) {
-    const int r = i / cx, c = i - r * cx;
-    if (c < n_seq) p.spec[size_t(p.out_y0 + r) * p.pitch + c0 + c] = smem[c * p.seq_stride + Pad(p.out_y0 + r)];
+  RunTileFft<true, TC>(smem, p.plan1);
+  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
+    const int y = i / TC, c = i - y * TC;
+    if (!whole || (y >= p.out_y0 && y < p.out_y1)) base[size_t(y) * p.pitch + c] = smem[i];
   }
 }
 
@@ -537,15 +655,42 @@ struct HostPlan {
 
 struct FftConvolver::Impl {
   int W, H, n, pitch;
-  HostPlan row, col;
-  DeviceBuffer<uint32_t> perm;
+  int H1 = 1, H2 = 1;
+  HostPlan row, col, col1, col2;
+  DeviceBuffer<uint32_t> perm, freq2;
   DeviceBuffer<float2> split_tw;
   DeviceBuffer<float2> work, kernel_spectrum;
   DeviceBuffer<float> kernel_image;
   int rows_per_cta = 1, row_threads = 256, row_stride = 0;
-  int cols_per_cta = 1, col_threads = 256, col_stride = 0;
-  size_t row_smem = 0, col_smem = 0;
+  int threads1 = 256, threads2 = 256;
+  size_t row_smem = 0, smem1 = 0, smem2 = 0;
+
+  ColParams MakeColParams() const {
+    ColParams c{};
+    c.spec = work.get();
+    c.pitch = pitch;
+    c.H = H;
+    c.H1 = H1;
+    c.H2 = H2;
+    c.y0 = 0;
+    c.y1 = H;
+    c.out_y0 = 0;
+    c.out_y1 = H;
+    c.scale = 1.0f;
+    c.plan1 = col1.plan;
+    c.plan2 = col2.plan;
+    c.tw_h = col.plan.tw;
+    c.freq2 = freq2.get();
+    return c;
+  }
 };
+
+namespace {
+int TileThreads(int len) {
+  const int t = (len * kTileCols / 8 + 31) / 32 * 32;
+  return std::clamp(t, 64, 256);
+}
+}  // namespace
 
 FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width_(width), height_(height) {
   Impl& d = *impl_;
@@ -556,9 +701,10 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     d.W = int(width);
     d.H = int(height);
     d.n = d.W / 2;
-    d.pitch = (d.n + 1 + 3) & ~3;
+    // whole 128-byte lines per spectrum row: the column passes work on 16-column tiles
+    d.pitch = (d.n + 1 + kTileCols - 1) / kTileCols * kTileCols;
     d.row.Build(d.n);
-    d.col.Build(d.H);
+    d.col.Build(d.H);  // validates the factors and holds the exp(-2 pi i t / H) table
     std::vector<uint32_t> perm(d.n);
     for (int k = 0; k < d.n; ++k) perm[k] = d.row.Slot(uint32_t(k));
     d.perm.Resize(d.n);
@@ -578,19 +724,42 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     d.row_smem = row_bytes * d.rows_per_cta;
     d.row_threads = d.n * d.rows_per_cta >= 4096 ? 256 : 128;
 
-    d.col_stride = PaddedLength(d.H);
-    const size_t col_bytes = size_t(d.col_stride) * sizeof(float2);
-    if (col_bytes > kMaxSmemBytes) throw std::domain_error("image column does not fit in shared memory");
-    d.cols_per_cta = 4 * col_bytes <= kMaxSmemBytes ? 4 : (2 * col_bytes <= kMaxSmemBytes ? 2 : 1);
-    d.col_smem = col_bytes * d.cols_per_cta;
-    const int work_items = d.H * d.cols_per_cta;
-    d.col_threads = (work_items >= 4096 ? 512 : (work_items >= 1024 ? 256 : 64));
+    // Column split H = H1 * H2 (four-step). Short columns are done in one pass (H2 = 1);
+    // otherwise the most balanced factorisation, the larger factor on the contiguous side.
+    const size_t tile_row_bytes = kTileCols * sizeof(float2);
+    const int single_pass_max = 512;
+    d.H1 = d.H;
+    d.H2 = 1;
+    if (d.H > single_pass_max) {
+      int best = 0;
+      for (int f = 1; f * f <= d.H; ++f)
+        if (d.H % f == 0) best = f;
+      d.H2 = best;
+      d.H1 = d.H / best;
+    }
+    if (size_t(d.H1) * tile_row_bytes > kMaxSmemBytes)
+      throw std::domain_error("image height " + std::to_string(d.H) +
+                              " has no factorisation that fits in shared memory");
+    d.col1.Build(d.H1);
+    d.col2.Build(d.H2);
+    std::vector<uint32_t> freq2(d.H2);
+    for (int k = 0; k < d.H2; ++k) freq2[d.col2.Slot(uint32_t(k))] = uint32_t(k);
+    d.freq2.Resize(d.H2);
+    RDL_CUDA(cudaMemcpy(d.freq2.get(), freq2.data(), d.H2 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    d.smem1 = size_t(d.H1) * tile_row_bytes;
+    d.smem2 = size_t(d.H2) * tile_row_bytes;
+    d.threads1 = std::min(2 * TileThreads(d.H1), 512);
+    d.threads2 = TileThreads(d.H2);
 
     RDL_CUDA(cudaFuncSetAttribute(RowForwardKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
     RDL_CUDA(cudaFuncSetAttribute(RowInverseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<true, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<false, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<true, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<false, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
     d.work.Resize(size_t(d.H) * d.pitch);
+    // columns n+1 .. pitch-1 ride along in the column tiles: keep them finite
+    RDL_CUDA(cudaMemset(d.work.get(), 0, size_t(d.H) * d.pitch * sizeof(float2)));
   } catch (...) {
     delete impl_;
     impl_ = nullptr;
@@ -628,20 +797,15 @@ void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, cudaStrea
 void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectrum_out, cudaStream_t stream) {
   Impl& d = *impl_;
   ForwardRows(kernel_image, d.W, d.H, stream);
-  ColParams c{};
-  c.spec = d.work.get();
+  ColParams c = d.MakeColParams();
   c.kspec_out = spectrum_out;
-  c.pitch = d.pitch;
-  c.n_cols = d.n + 1;
-  c.H = d.H;
-  c.y0 = 0;
-  c.y1 = d.H;
-  c.cols_per_cta = d.cols_per_cta;
-  c.seq_stride = d.col_stride;
   c.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
-  c.plan = d.col.plan;
-  const int grid = (c.n_cols + d.cols_per_cta - 1) / d.cols_per_cta;
-  ColumnKernel<false><<<grid, d.col_threads, d.col_smem, stream>>>(c);
+  const int tiles = d.pitch / kTileCols;
+  if (d.H2 > 1) {
+    ColumnStridedKernel<false, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    ++launches_;
+  }
+  ColumnBlockKernel<false, kTileCols><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
   ++launches_;
 }
 
@@ -673,23 +837,23 @@ void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const fl
   Impl& d = *impl_;
   if (dw > size_t(d.W) || dh > size_t(d.H)) throw std::invalid_argument("destination larger than the FFT frame");
   ForwardRows(src, sw, sh, stream);
-  ColParams c{};
-  c.spec = d.work.get();
+  ColParams c = d.MakeColParams();
   c.kspec = kernel_spectrum;
-  c.pitch = d.pitch;
-  c.n_cols = d.n + 1;
-  c.H = d.H;
   c.y0 = (d.H - int(sh)) / 2;
   c.y1 = c.y0 + int(sh);
   c.out_y0 = (d.H - int(dh)) / 2;
   c.out_y1 = c.out_y0 + int(dh);
-  c.cols_per_cta = d.cols_per_cta;
-  c.seq_stride = d.col_stride;
-  c.scale = 1.0f;
-  c.plan = d.col.plan;
-  const int cgrid = (c.n_cols + d.cols_per_cta - 1) / d.cols_per_cta;
-  ColumnKernel<true><<<cgrid, d.col_threads, d.col_smem, stream>>>(c);
+  const int tiles = d.pitch / kTileCols;
+  if (d.H2 > 1) {
+    ColumnStridedKernel<false, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    ++launches_;
+  }
+  ColumnBlockKernel<true, kTileCols><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
   ++launches_;
+  if (d.H2 > 1) {
+    ColumnStridedKernel<true, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    ++launches_;
+  }
   RowParams p{};
   p.dst = dst;
   p.sw = int(dw);
