@@ -29,7 +29,7 @@ sys.path.insert(0, ROOT)
 # synthetic cube: point sources (*) Gaussian PSF + white noise, power-law
 # spectra, per-channel PSF widths, channel weights. Built with torch FFTs (plumbing, untimed).
 # --------------------------------------------------------------------------------------
-def make_cube(n, n_channels, device, seed=1):
+def make_cube(n, n_channels, device, seed=1, fwhm0=4.0, extended=False):
     import torch
     g = torch.Generator(device="cpu").manual_seed(seed)
     n_src = max(8, n * n // 4096)
@@ -38,6 +38,13 @@ def make_cube(n, n_channels, device, seed=1):
     flux = torch.exp(torch.empty(n_src).uniform_(np.log(0.01), np.log(10.0), generator=g))
     alpha = torch.empty(n_src).uniform_(-1.2, -0.2, generator=g)
     weights = torch.empty(n_channels).uniform_(0.5, 1.5, generator=g).numpy().astype(np.float32)
+    # K2/K4: A/262144 extended Gaussian blobs, sigma in {6,12,24,48} px, peak 0.05-0.5 Jy/px
+    n_ext = max(2, n * n // 262144) if extended else 0
+    ex = torch.randint(n // 8, n - n // 8, (n_ext,), generator=g) if n_ext else None
+    ey = torch.randint(n // 8, n - n // 8, (n_ext,), generator=g) if n_ext else None
+    es = torch.tensor([6.0, 12.0, 24.0, 48.0])[torch.randint(0, 4, (n_ext,), generator=g)] if n_ext else None
+    ep = torch.empty(n_ext).uniform_(0.05, 0.5, generator=g) if n_ext else None
+    ea = torch.empty(n_ext).uniform_(-1.2, -0.2, generator=g) if n_ext else None
     freqs = np.linspace(100e6, 250e6, n_channels) if n_channels > 1 else np.array([150e6])
     yy, xx = torch.meshgrid(torch.arange(n, device=device, dtype=torch.float32),
                             torch.arange(n, device=device, dtype=torch.float32), indexing="ij")
@@ -46,7 +53,7 @@ def make_cube(n, n_channels, device, seed=1):
     res = torch.empty((n_channels, n, n), dtype=torch.float32, device=device)
     psfs = torch.empty((n_channels, n, n), dtype=torch.float32, device=device)
     for c in range(n_channels):
-        fwhm = 4.0 * (freqs[0] / freqs[c]) ** 0.25
+        fwhm = fwhm0 * (freqs[0] / freqs[c]) ** 0.25
         sigma = fwhm / 2.3548200450309493
         p = torch.exp(-0.5 * (r / sigma) ** 2) + 0.01 * torch.cos(r / 8.0) * torch.exp(-r / 200.0) * (r > 0)
         p[p.abs() < 1e-7] = 0.0
@@ -55,6 +62,14 @@ def make_cube(n, n_channels, device, seed=1):
         sky = torch.zeros((n, n), dtype=torch.float32, device=device)
         f_c = flux * (freqs[c] / freqs[0]) ** alpha
         sky.index_put_((ys.to(device), xs.to(device)), f_c.to(device), accumulate=True)
+        for b in range(n_ext):
+            hw = int(5 * float(es[b]))
+            x0, y0 = int(ex[b]), int(ey[b])
+            xa, xb, ya, yb = max(x0 - hw, 0), min(x0 + hw + 1, n), max(y0 - hw, 0), min(y0 + hw + 1, n)
+            gx = torch.arange(xa, xb, device=device, dtype=torch.float32) - x0
+            gy = torch.arange(ya, yb, device=device, dtype=torch.float32) - y0
+            amp = float(ep[b]) * (freqs[c] / freqs[0]) ** float(ea[b])
+            sky[ya:yb, xa:xb] += amp * torch.exp(-0.5 * (gy[:, None] ** 2 + gx[None, :] ** 2) / float(es[b]) ** 2)
         # circular FFT convolution with the PSF centre moved to the origin (compact PSF)
         k = torch.roll(p, shifts=(-(n // 2), -(n // 2)), dims=(0, 1))
         d = torch.fft.irfft2(torch.fft.rfft2(sky) * torch.fft.rfft2(k), s=(n, n))
@@ -63,6 +78,11 @@ def make_cube(n, n_channels, device, seed=1):
         res[c] = d
         del sky, k, d, p
     return res, psfs, weights, freqs
+
+
+def make_ms_cube(n, n_channels, device, seed=1):
+    """K2/K4 cube of SURVEY 8(d): 6 px beam, point sources + extended blobs."""
+    return make_cube(n, n_channels, device, seed=seed, fwhm0=6.0, extended=True)
 
 
 class ClockSampler:
@@ -129,6 +149,40 @@ def window_area(n, x, y):
 # CPU arm: the oracle (a port of the reference's CPU path; the reference itself cannot be
 # built offline — see DESIGN.md) on all host cores, on a bounded sample of the workload.
 # --------------------------------------------------------------------------------------
+def cpu_kind():
+    import oracle
+    oracle.build()
+    return "reference" if oracle.ref_lib() is not None and oracle._refa() is not None else "port"
+
+
+def cpu_multiscale(res, psfs, weights, freqs, iters):
+    """One MultiScaleAlgorithm::ExecuteMajorIteration on the host cores (K2/K4 settings)."""
+    import oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    oracle.set_threads(cores)
+    c, n, _ = res.shape
+    model = np.zeros_like(res)
+    kind = cpu_kind()
+    if kind == "reference":
+        alg = oracle.Reference("multiscale", n, n, c, weights=weights, frequencies=freqs,
+                               max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1,
+                               major_loop_gain=0.8, threshold=0.0, max_scales=5, beam_size=6.0,
+                               pixel_scale=1.0, fit_terms=2 if c > 1 else 0, threads=cores)
+        t0 = time.perf_counter()
+        r = alg.execute(res, model, psfs)
+    else:
+        alg = oracle.MultiScale(beam_size=6.0, pixel_scale=1.0, max_scales=5)
+        st = oracle.Settings(max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1,
+                             major_loop_gain=0.8, threshold=0.0)
+        if c > 1:
+            st.spectral_mode, st.n_terms, st.frequencies, st.fit_weights = 1, 2, freqs, weights
+        t0 = time.perf_counter()
+        r = alg.execute(oracle.Cube(n, n, c, 1, weights), st, res, model, psfs)
+    dt = time.perf_counter() - t0
+    return dt, cores, r.iteration_number, kind
+
+
 def cpu_hogbom(res, psfs, weights, iters):
     import oracle
     oracle.build()
@@ -136,6 +190,15 @@ def cpu_hogbom(res, psfs, weights, iters):
     oracle.set_threads(cores)
     c, n, _ = res.shape
     model = np.zeros_like(res)
+    if cpu_kind() == "reference":
+        alg = oracle.Reference("generic", n, n, c, weights=weights,
+                               use_sub_minor_optimization=False, max_iterations=iters,
+                               clean_border_ratio=0.0, minor_loop_gain=0.1, threshold=0.0,
+                               threads=cores)
+        t0 = time.perf_counter()
+        r = alg.execute(res, model, psfs)
+        dt = time.perf_counter() - t0
+        return r.iteration_number / dt, dt, cores, r.iteration_number
     alg = oracle.GenericClean(use_sub_minor_optimization=False)
     s = oracle.Settings(max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1,
                         threshold=0.0)
@@ -166,9 +229,9 @@ def run_reference(args):
     line = base_line(args, value, float(np.mean(times)) * 1e3)
     line.update({
         "impl": "reference", "n_gpus": args.gpus,
-        "cpu_baseline": {"value": value, "unit": "iterations/s", "cores": cores, "kind": "port",
+        "cpu_baseline": {"value": value, "unit": "iterations/s", "cores": cores, "kind": cpu_kind(),
                          "sample": f"{sample_iters} minor iterations per step of the same "
-                                   f"{n}^2 x {c} cube (oracle GenericClean path B, all host cores)"},
+                                   f"{n}^2 x {c} cube (GenericClean path B, all host cores)"},
         "e2e": {"value": value, "unit": "iterations/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "dtype": "f32",
@@ -310,16 +373,235 @@ def run_ours(args):
                          "note": "achieved uses the fused-kernel minimum bytes (each image read "
                                  "once); achieved_survey_u3 uses SURVEY 8(d) U3 = U1 + U2"},
         })
+        if world == 1 and not args.no_ms:
+            # second half of BASELINE.json's metric: multiscale major-iteration ms on the K4 cube
+            # (full line incl. e2e, roofline and CPU arm: --workload multiscale)
+            ms_res0, ms_psfs, ms_w, ms_f = make_ms_cube(n, c, dev)
+            ms_alg = ms_algorithm(rdl, local, c, ms_f, ms_w, args.ms_iters)
+            ms_total, ms_r, ms_minor, ms_launches = run_multiscale_device(
+                rdl, ms_alg, rdl.Cube(n, n, c, 1, ms_w), ms_res0, ms_psfs, 2, 1, barrier, stream)
+            line["multiscale"] = {
+                "ms_per_major_iteration": ms_total / 2, "max_iterations": args.ms_iters,
+                "components_cleaned": int(ms_r.iteration_number),
+                "minor_iterations": ms_minor / 2, "gpu_launches": int(ms_launches),
+                "config": f"multiscale {n}^2 x {c} channels joined, 5 scales, polynomial fit 2 "
+                          "terms, mgain 0.8; device-resident, CUDA events"}
+            del ms_res0, ms_psfs, ms_alg
         if not args.no_cpu:
             h = res0.cpu().numpy()
             v, dt, cores, it = cpu_hogbom(h, np_psf, weights, args.cpu_iters)
             line["cpu_baseline"] = {
-                "value": v, "unit": "iterations/s", "cores": cores, "kind": "port",
+                "value": v, "unit": "iterations/s", "cores": cores, "kind": cpu_kind(),
                 "sample": f"{it} minor iterations of the same {n}^2 x {c} cube "
-                          f"({dt:.1f} s, oracle GenericClean path B, all host cores)"}
+                          f"({dt:.1f} s, GenericClean path B, all host cores)"}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------
+# multiscale workload (BASELINE.json: "multiscale major-iter ms at 8192^2 x 16ch")
+# --------------------------------------------------------------------------------------
+def ms_algorithm(rdl, local, c, freqs, weights, iters):
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=5, device=local)
+    alg.apply(max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1,
+              major_loop_gain=0.8, threshold=0.0, trace_capacity=0)
+    if c > 1:
+        alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, freqs, weights, 1)
+    return alg
+
+
+def fft_roofline(rdl, n_pad, dev):
+    """The dominant kernel group of a multiscale major iteration, timed alone: one circular FFT
+    convolution of an n_pad^2 frame (RowForward, ColumnStrided, ColumnBlock, ColumnStrided,
+    RowInverse). Algorithmic bytes = SURVEY U5 = 28 B per padded pixel."""
+    import torch
+    alg = rdl.GenericClean(device=dev.index)
+    side = torch.cuda.Stream(device=dev)
+    n_img, reps = 4, 3
+    with torch.cuda.stream(side):
+        imgs = torch.randn((n_img, n_pad, n_pad), device=dev)
+        ker = torch.randn((n_pad, n_pad), device=dev)
+        alg.convolve(imgs, ker, stream=side.cuda_stream)
+        side.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(side)
+        for _ in range(reps):
+            alg.convolve(imgs, ker, stream=side.cuda_stream)
+        e1.record(side)
+        side.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    per_conv_s = ms * 1e-3 / (n_img + 16.0 / 28.0)  # + one kernel spectrum (16 B/px) per call
+    peak, src = measured_peaks()
+    bytes_ = 28.0 * n_pad * n_pad
+    return {"bound": "hbm", "kernel": f"FFT convolution {n_pad}^2 (RowForward + ColumnStrided + "
+            "ColumnBlock + ColumnStrided + RowInverse), timed alone on its stream",
+            "achieved": bytes_ / per_conv_s / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": bytes_ / per_conv_s / 1e9 / peak, "traffic": 44.0 * n_pad * n_pad,
+            "traffic_note": "four-step column transform moves 44 B/px (ncu: profiles/"
+                            "r01_ncu_full_fft_8192.json); SURVEY U5 counts 28 B/px",
+            "peak_source": src, "bytes_per_launch": bytes_ / 5.0,
+            "avg_launch_us": per_conv_s * 1e6 / 5.0, "us_per_convolution": per_conv_s * 1e6}
+
+
+def run_multiscale_device(rdl, alg, cube, res0, psfs, steps, warmup, barrier, stream):
+    """Device-resident timing of `steps` major iterations; returns (ms_total, last result,
+    minor iterations, launches)."""
+    import torch
+    res = torch.empty_like(res0)
+    model = torch.empty_like(res0)
+
+    def one():
+        res.copy_(res0)
+        model.zero_()
+        alg.set_iteration_number(0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = alg.execute_major_iteration(cube, res, model, psfs, stream=stream)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1), r
+
+    for _ in range(warmup):
+        one()
+    barrier()
+    l0 = alg.kernel_launch_count
+    total, minor, r = 0.0, 0, None
+    for _ in range(steps):
+        ms, r = one()
+        total += ms
+        minor += alg.minor_iteration_count
+    barrier()
+    del res, model
+    return total, r, minor, alg.kernel_launch_count - l0
+
+
+def run_ours_multiscale(args):
+    import torch
+    import torch.distributed as dist
+
+    import ska_sdp_func_radler_b200 as rdl
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    n, c, iters = args.size, args.channels, args.ms_iters
+    res0, psfs, weights, freqs = make_ms_cube(n, c, dev, seed=1 + rank)
+    cube = rdl.Cube(n, n, c, 1, weights)
+    alg = ms_algorithm(rdl, local, c, freqs, weights, iters)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    # warm-up happens inside; the sampler also covers it (clocks are read as a median)
+    if rank == 0:
+        sampler.start()
+    total_ms, r, minor, launches = run_multiscale_device(rdl, alg, cube, res0, psfs, args.steps,
+                                                         args.warmup, barrier, stream)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t[0]) / args.steps
+
+    # ---- e2e: the same call with pinned HOST buffers --------------------------------------
+    h_res = torch.empty((c, n, n), dtype=torch.float32).pin_memory()
+    h_model = torch.zeros((c, n, n), dtype=torch.float32).pin_memory()
+    h_psf = torch.empty((c, n, n), dtype=torch.float32).pin_memory()
+    h_psf.copy_(psfs)
+    e2e_steps = max(1, min(args.steps, 2))
+    e2e_s = 0.0
+    for i in range(1 + e2e_steps):
+        h_res.copy_(res0)
+        h_model.zero_()
+        alg.set_iteration_number(0)
+        barrier()
+        t0 = time.perf_counter()
+        alg.execute_major_iteration(cube, h_res.numpy(), h_model.numpy(), h_psf.numpy())
+        barrier()
+        if i > 0:  # first call warms the staging buffers
+            e2e_s += time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t[0]) / e2e_steps * 1e3
+    plane = n * n * 4
+
+    if rank == 0:
+        n_pad = int(rdl.convolution_size(alg.scale_infos()[-1]["scale"], n, 1.1))
+        line = {
+            "metric": "multiscale major-iteration time (MultiScaleAlgorithm::ExecuteMajorIteration)",
+            "value": ms_per_step / world, "unit": "ms per major iteration (job average)",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"multiscale {n}^2 x {c} channels joined, 5 scales, polynomial "
+                                   f"fit 2 terms, mgain 0.8, max {iters} components per major "
+                                   "iteration (step)", "size": n, "channels": c,
+                       "max_iterations": iters, "components_cleaned": int(r.iteration_number),
+                       "minor_iterations_per_step": minor / args.steps,
+                       "l2": "inputs larger than L2" if n * n * c * 4 > 4 * 126e6 else
+                       "cube comparable to L2",
+                       "parallelism": "1 cube per GPU (replicas)" if world > 1 else "single GPU"},
+            "e2e": {"value": e2e_ms / world, "unit": "ms per major iteration (job average)",
+                    "ms_per_step": e2e_ms, "h2d_bytes_per_step": 3 * c * plane,
+                    "d2h_bytes_per_step": 2 * c * plane},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": fft_roofline(rdl, n_pad, dev),
+        }
+        if not args.no_cpu:
+            # identical call on both sides: max_iterations = cpu_iters (setup + first minor pass)
+            a2 = ms_algorithm(rdl, local, c, freqs, weights, args.cpu_iters)
+            ms_same, r2, _, _ = run_multiscale_device(rdl, a2, cube, res0, psfs, 1, 1, barrier,
+                                                      stream)
+            del a2
+            dt, cores, it, kind = cpu_multiscale(res0.cpu().numpy(), h_psf.numpy(), weights, freqs,
+                                                 args.cpu_iters)
+            line["cpu_baseline"] = {
+                "value": dt * 1e3, "unit": "ms", "cores": cores, "kind": kind,
+                "sample": f"the same {n}^2 x {c} major iteration capped at max_iterations="
+                          f"{args.cpu_iters} (scale setup + PSF convolutions + first minor pass; "
+                          f"{it} components)",
+                "gpu_same_sample_ms": ms_same, "gpu_same_sample_components": int(r2.iteration_number)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference_multiscale(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n, c = args.size, args.channels
+    res, psfs, weights, freqs = make_ms_cube(n, c, "cpu")
+    res, psfs = res.numpy(), psfs.numpy()
+    times = []
+    steps = max(1, min(args.steps, 2))
+    for _ in range(steps):
+        dt, cores, it, kind = cpu_multiscale(res.copy(), psfs, weights, freqs, args.cpu_iters)
+        times.append(dt * 1e3)
+    value = float(np.mean(times))
+    print(json.dumps({
+        "impl": "reference",
+        "metric": "multiscale major-iteration time (MultiScaleAlgorithm::ExecuteMajorIteration)",
+        "value": value, "unit": "ms per major iteration (job average)", "n_gpus": args.gpus,
+        "steps": steps, "warmup": 0, "ms_per_step": value, "higher_is_better": False,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"multiscale {n}^2 x {c} channels joined, 5 scales, capped at "
+                               f"max_iterations={args.cpu_iters} (bounded sample)", "size": n,
+                   "channels": c, "max_iterations": args.cpu_iters},
+        "cpu_baseline": {"value": value, "unit": "ms", "cores": cores, "kind": kind,
+                         "sample": f"max_iterations={args.cpu_iters}, {it} components"},
+        "e2e": {"value": value, "unit": "ms per major iteration (job average)",
+                "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
 
 
 def main():
@@ -328,16 +610,26 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="hogbom", choices=["hogbom"])
+    ap.add_argument("--workload", default="hogbom", choices=["hogbom", "multiscale"])
+    ap.add_argument("--ms-iters", type=int, default=500,
+                    help="multiscale: max components per major iteration")
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--channels", type=int, default=16)
     ap.add_argument("--iters", type=int, default=256, help="minor iterations per step")
-    ap.add_argument("--cpu-iters", type=int, default=6, help="CPU sample: minor iterations")
+    ap.add_argument("--cpu-iters", type=int, default=None,
+                    help="CPU sample: minor iterations (hogbom, default 6) / max_iterations "
+                         "(multiscale, default 1)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ms", action="store_true",
+                    help="hogbom: skip the extra multiscale measurement")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3 if args.impl == "ours" else args.warmup
-    if args.impl == "reference":
+    if args.cpu_iters is None:
+        args.cpu_iters = 6 if args.workload == "hogbom" else 1
+    if args.workload == "multiscale":
+        (run_reference_multiscale if args.impl == "reference" else run_ours_multiscale)(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

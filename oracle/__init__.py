@@ -63,6 +63,9 @@ def ref_lib():
         for n in ["ref_flood_vertical_area", "ref_flood_horizontal_area"]:
             getattr(L, n).argtypes = [vp, u64, u64, u64, vp, C.POINTER(u64), C.POINTER(u64)]
         L.ref_get_bounding_mask.argtypes = [vp, u64, u64, u64, u64, vp, vp] + [C.POINTER(u64)] * 4
+        L.ref_iuwt_decompose.argtypes = [vp, u64, u64, C.c_int32, C.c_int32, vp]
+        L.ref_iuwt_recompose.argtypes = [vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
+        L.ref_iuwt_smooth.argtypes = [vp, u64, u64, C.c_int32]
         _ref = L
     return _ref
 
@@ -207,6 +210,12 @@ def lib():
                                        C.c_int32]
         L.orc_add_shape_component.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_float,
                                               C.c_uint64, C.c_uint64, C.c_float, C.c_int32]
+        L.orc_iuwt_smooth.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32,
+                                      C.c_int32]
+        L.orc_iuwt_decompose.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32,
+                                         C.c_void_p]
+        L.orc_iuwt_recompose.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32,
+                                         C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -467,6 +476,59 @@ def untrim(src, dw, dh):
     dst = np.zeros((dh, dw), np.float32)
     lib().orc_untrim(_ptr(dst), dw, dh, _ptr(src), src.shape[1], src.shape[0])
     return dst
+
+
+def iuwt_smooth(image, scale, mt=True):
+    """One B3-spline a-trous smoothing (iuwt_decomposition.cc:55-67 convolveMT when mt, else the
+    "simple" convolve of iuwt_decomposition.h:249-267)."""
+    a = _f32(image)
+    out = np.empty_like(a)
+    lib().orc_iuwt_smooth(_ptr(out), _ptr(a), a.shape[1], a.shape[0], scale, int(mt))
+    return out
+
+
+def iuwt_decompose(image, n_scales, include_largest=True):
+    """IuwtDecomposition::DecomposeMt (iuwt_decomposition.cc:9-53) -> [n_scales(+1), H, W]."""
+    a = _f32(image)
+    out = np.zeros((n_scales + (1 if include_largest else 0),) + a.shape, np.float32)
+    lib().orc_iuwt_decompose(_ptr(a), a.shape[1], a.shape[0], n_scales, int(include_largest),
+                             _ptr(out))
+    return out
+
+
+def iuwt_recompose(coefficients, n_scales, include_largest=True, masks=None):
+    """ApplyMask (when masks) + IuwtDecomposition::Recompose (iuwt_decomposition.h:121-169)."""
+    c = _f32(coefficients)
+    out = np.empty(c.shape[1:], np.float32)
+    m = None if masks is None else np.ascontiguousarray(masks, np.uint8)
+    lib().orc_iuwt_recompose(_ptr(c), c.shape[2], c.shape[1], n_scales, int(include_largest),
+                             _ptr(m), _ptr(out))
+    return out
+
+
+def ref_iuwt_decompose(image, n_scales, include_largest=True):
+    a = _f32(image)
+    out = np.zeros((n_scales + (1 if include_largest else 0),) + a.shape, np.float32)
+    ref_lib().ref_iuwt_decompose(_ptr(a), a.shape[1], a.shape[0], n_scales, int(include_largest),
+                                 _ptr(out))
+    return out
+
+
+def ref_iuwt_recompose(coefficients, n_scales, include_largest=True, masks=None):
+    c = _f32(coefficients)
+    if c.shape[0] == n_scales:  # the wrapper reads n_scales + 1 planes
+        c = np.concatenate([c, np.zeros((1,) + c.shape[1:], np.float32)])
+    out = np.empty(c.shape[1:], np.float32)
+    m = None if masks is None else np.ascontiguousarray(masks, np.uint8)
+    ref_lib().ref_iuwt_recompose(_ptr(c), c.shape[2], c.shape[1], n_scales, int(include_largest),
+                                 _ptr(m), _ptr(out))
+    return out
+
+
+def ref_iuwt_smooth(image, to_scale):
+    a = _f32(image).copy()
+    ref_lib().ref_iuwt_smooth(_ptr(a), a.shape[1], a.shape[0], to_scale)
+    return a
 
 
 def good_fft_size(n):

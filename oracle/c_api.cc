@@ -315,6 +315,18 @@ void orc_untrim(float* dst, uint64_t dw, uint64_t dh, const float* src, uint64_t
                 uint64_t sh) {
   Untrim(dst, dw, dh, src, sw, sh);
 }
+void orc_iuwt_smooth(float* out, const float* in, uint64_t w, uint64_t h, int32_t scale, int32_t mt) {
+  std::vector<float> scratch(w * h);
+  IuwtSmooth(out, in, scratch.data(), w, h, scale, mt != 0);
+}
+void orc_iuwt_decompose(const float* input, uint64_t w, uint64_t h, int32_t n_scales,
+                        int32_t include_largest, float* coefficients) {
+  IuwtDecompose(input, w, h, n_scales, include_largest != 0, coefficients);
+}
+void orc_iuwt_recompose(const float* coefficients, uint64_t w, uint64_t h, int32_t n_scales,
+                        int32_t include_largest, const uint8_t* masks, float* out) {
+  IuwtRecompose(coefficients, w, h, n_scales, include_largest != 0, masks, out);
+}
 uint64_t orc_good_fft_size(uint64_t n) { return CalculateGoodFFTSize(n); }
 uint64_t orc_convolution_size(double scale, uint64_t n, double padding) {
   return GetConvolutionSize(scale, n, padding);

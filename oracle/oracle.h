@@ -352,5 +352,13 @@ class MultiScaleAlgorithm : public DeconvolutionAlgorithm {
   bool track_per_scale_masks_ = false, use_per_scale_masks_ = false;
 };
 
+// ---- IUWT decomposition (iuwt.cc) -----------------------------------------------------------
+void IuwtSmooth(float* out, const float* in, float* scratch, size_t width, size_t height, int scale,
+                bool mt);
+void IuwtDecompose(const float* input, size_t width, size_t height, int n_scales,
+                   bool include_largest, float* coefficients);
+void IuwtRecompose(const float* coefficients, size_t width, size_t height, int n_scales,
+                   bool include_largest, const uint8_t* masks, float* out);
+
 }  // namespace oracle
 #endif

@@ -8,6 +8,8 @@
 #include <cstdint>
 #include <vector>
 
+#include "algorithms/iuwt/iuwt_decomposition.h"
+#include "algorithms/iuwt/iuwt_mask.h"
 #include "algorithms/multiscale/multiscale_transforms.h"
 #include "algorithms/simple_clean.h"
 #include "math/dijkstra_splitter.h"
@@ -132,5 +134,44 @@ void ref_add_shape_component(float* image, uint64_t w, uint64_t h, float scale, 
   algorithms::multiscale::MultiScaleTransforms::AddShapeComponent(
       image, w, h, scale, x, y, gain,
       shape == 1 ? MultiscaleShape::kGaussianShape : MultiscaleShape::kTaperedQuadraticShape);
+}
+
+// ---- IUWT decomposition (iuwt_decomposition.{h,cc}) of the reference itself ----------------
+// coefficients: (n_scales + 1) planes; the last plane (the smooth remainder) is only filled
+// when include_largest != 0.
+void ref_iuwt_decompose(const float* input, uint64_t w, uint64_t h, int n_scales,
+                        int include_largest, float* coefficients) {
+  algorithms::iuwt::IuwtDecomposition d(n_scales, w, h);
+  aocommon::Image scratch(w, h);
+  d.Decompose(input, scratch.Data(), include_largest != 0);
+  for (int s = 0; s != n_scales + (include_largest ? 1 : 0); ++s)
+    std::copy_n(d[s].Coefficients().Data(), w * h, coefficients + size_t(s) * w * h);
+}
+// masks (optional): n_scales planes of w*h bytes, applied with ApplyMask before Recompose.
+void ref_iuwt_recompose(const float* coefficients, uint64_t w, uint64_t h, int n_scales,
+                        int include_largest, const uint8_t* masks, float* out) {
+  algorithms::iuwt::IuwtDecomposition d(n_scales, w, h);
+  for (int s = 0; s != n_scales + 1; ++s) {
+    d[s].Coefficients() = aocommon::Image(w, h, 0.0f);
+    if (s < n_scales || include_largest)
+      std::copy_n(coefficients + size_t(s) * w * h, w * h, d[s].Coefficients().Data());
+  }
+  if (masks) {
+    algorithms::iuwt::IuwtMask m(n_scales, w, h);
+    for (int s = 0; s != n_scales; ++s)
+      for (size_t i = 0; i != w * h; ++i) m[s][i] = masks[size_t(s) * w * h + i] != 0;
+    d.ApplyMask(m);
+  }
+  aocommon::Image o(w, h);
+  d.Recompose(o, include_largest != 0 && !masks);
+  std::copy_n(o.Data(), w * h, out);
+}
+// IuwtDecomposition::Convolve(image, to_scale): repeated B3 smoothing, "simple" tap order
+void ref_iuwt_smooth(float* image, uint64_t w, uint64_t h, int to_scale) {
+  algorithms::iuwt::IuwtDecomposition d(to_scale, w, h);
+  aocommon::Image img(w, h);
+  std::copy_n(image, w * h, img.Data());
+  d.Convolve(img, to_scale);
+  std::copy_n(img.Data(), w * h, image);
 }
 }

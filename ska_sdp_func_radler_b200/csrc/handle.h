@@ -164,6 +164,7 @@ struct rdl_handle {
   // FFT scratch: one W x H image, one kernel spectrum, one uploaded scale kernel
   rdl::DeviceBuffer<float> fft_scratch, small_kernel;
   rdl::DeviceBuffer<float2> fft_spectrum;
+  rdl::DeviceBuffer<float> iuwt_a, iuwt_b;  // IUWT ping-pong planes
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
   // FFT engines by frame size (plans, twiddle tables, work spectrum); not cloned

@@ -1,0 +1,254 @@
+// IUWT (isotropic undecimated wavelet transform) decomposition on the device — the B200-native
+// counterpart of radler::algorithms::iuwt::IuwtDecomposition
+//   cpp/algorithms/iuwt/iuwt_decomposition.cc:9-53    DecomposeMt
+//   cpp/algorithms/iuwt/iuwt_decomposition.cc:55-237  convolveMT (horizontal + vertical B3 pass)
+//   cpp/algorithms/iuwt/iuwt_decomposition.h:121-169  Recompose / ApplyMask, :249-267 convolve
+//
+// One smoothing is ONE kernel: the reference's row pass -> scratch image -> column pass
+// (16 bytes/pixel of traffic) becomes a shared-memory tile; the horizontally smoothed rows a
+// tile needs never leave the SM. Because the a-trous taps sit at multiples of d = 2^scale - 1,
+// a CTA owns a COMB of rows {r + k d}: TY output rows need only TY + 4 smoothed rows whatever
+// the scale (a block of contiguous rows would need TY + 4 d). The difference (w = i0 - i2,
+// iuwt_decomposition.cc:25,39) and the recomposition add / ApplyMask (iuwt_decomposition.h:141,
+// 162-169) are fused as epilogues, so a decomposition moves 20 bytes/pixel/scale instead of the
+// reference's 44 and no image is ever copied (i0 = i1 is a pointer swap).
+//
+// Arithmetic parity: taps {1,4,6,4,1}/16; only the 6/16 product is inexact. The reference's
+// -O3 build (GCC, -ffp-contract=fast) fuses the first product of each tap expression with the
+// second one left as a rounded product, and every later term as fma(v, h, acc); the "simple"
+// flavour accumulates fma(v, h, acc) onto zero in tap order. Both are written explicitly
+// (this file is compiled with --fmad=false) and checked bit-exactly against the reference's
+// own sources (tests/test_gpu_iuwt.py).
+#include "iuwt.cuh"
+
+#include <algorithm>
+
+namespace rdl {
+namespace {
+
+constexpr int kTX = 128;      // tile width (columns, contiguous)
+constexpr int kTY = 28;       // comb rows per tile -> 32 smoothed rows in shared memory
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ float TapWeight(int k) {
+  return k == 2 ? 0.375f : ((k == 1 || k == 3) ? 0.25f : 0.0625f);
+}
+
+// v[k], k = 0..4 = taps at offsets (k - 2) d; bit k of `present` set when the tap is inside the
+// image. ORDER_MT_H: tap order h2,h1,h0,h3,h4 (convolveHorizontalFast), else h0..h4.
+template <bool SIMPLE, bool ORDER_MT_H>
+__device__ __forceinline__ float Taps(const float (&v)[5], unsigned present) {
+  if (present == 31u) {  // interior fast path, same operation order as the general one
+    if (SIMPLE) {
+      float acc = __fmaf_rn(v[0], 0.0625f, 0.0f);
+      acc = __fmaf_rn(v[1], 0.25f, acc);
+      acc = __fmaf_rn(v[2], 0.375f, acc);
+      acc = __fmaf_rn(v[3], 0.25f, acc);
+      return __fmaf_rn(v[4], 0.0625f, acc);
+    }
+    if (ORDER_MT_H) {
+      float acc = __fmaf_rn(v[2], 0.375f, __fmul_rn(v[1], 0.25f));
+      acc = __fmaf_rn(v[0], 0.0625f, acc);
+      acc = __fmaf_rn(v[3], 0.25f, acc);
+      return __fmaf_rn(v[4], 0.0625f, acc);
+    }
+    float acc = __fmaf_rn(v[0], 0.0625f, __fmul_rn(v[1], 0.25f));
+    acc = __fmaf_rn(v[2], 0.375f, acc);
+    acc = __fmaf_rn(v[3], 0.25f, acc);
+    return __fmaf_rn(v[4], 0.0625f, acc);
+  }
+  float tv[5], th[5];
+  int n = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int k = ORDER_MT_H ? (i == 0 ? 2 : (i == 1 ? 1 : (i == 2 ? 0 : i))) : i;
+    if (present & (1u << k)) {
+      // compact without dynamic indexing: shift into slot n
+#pragma unroll
+      for (int s = 0; s < 5; ++s)
+        if (s == n) {
+          tv[s] = v[k];
+          th[s] = TapWeight(k);
+        }
+      ++n;
+    }
+  }
+  float acc;
+  if (SIMPLE) {
+    acc = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+      if (i < n) acc = __fmaf_rn(tv[i], th[i], acc);
+    return acc;
+  }
+  if (n == 1) return __fmul_rn(tv[0], th[0]);
+  acc = __fmaf_rn(tv[0], th[0], __fmul_rn(tv[1], th[1]));
+#pragma unroll
+  for (int i = 2; i < 5; ++i)
+    if (i < n) acc = __fmaf_rn(tv[i], th[i], acc);
+  return acc;
+}
+
+struct SmoothParams {
+  const float* in;
+  float* out;
+  const float* other;   // epilogue operand (EPI 1: minuend i0; EPI 2: coefficient plane)
+  const uint8_t* mask;  // EPI 2: optional ApplyMask plane
+  int width, height, d;
+  int blocks_per_residue;  // comb blocks per residue class
+};
+
+// EPI 0: out = B(in); 1: out = other - B(in); 2: out = B(in) + (mask ? other : 0)
+template <bool SIMPLE, int EPI>
+__global__ void __launch_bounds__(kThreads) IuwtSmoothKernel(const __grid_constant__ SmoothParams p) {
+  __shared__ float hs[kTY + 4][kTX];
+  const int W = p.width, H = p.height, d = p.d;
+  const int x0 = blockIdx.x * kTX;
+  const int r = blockIdx.y / p.blocks_per_residue;           // residue class of the comb
+  const int kb = blockIdx.y - r * p.blocks_per_residue;      // comb block
+  const int k0 = kb * kTY;                                   // first comb index of the tile
+  // phase 1: horizontally smoothed comb rows k0-2 .. k0+TY+1
+  for (int i = threadIdx.x; i < (kTY + 4) * kTX; i += kThreads) {
+    const int row = i / kTX, xl = i - row * kTX;
+    const int x = x0 + xl;
+    const long y = long(r) + long(k0 + row - 2) * d;
+    float val = 0.0f;
+    if (y >= 0 && y < H && x < W) {
+      const float* src = p.in + size_t(y) * W;
+      float v[5];
+      unsigned present = 0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int xx = x + (k - 2) * d;
+        const bool ok = xx >= 0 && xx < W;
+        v[k] = ok ? __ldg(src + xx) : 0.0f;
+        present |= ok ? (1u << k) : 0u;
+      }
+      val = Taps<SIMPLE, !SIMPLE>(v, present);
+    }
+    hs[row][xl] = val;
+  }
+  __syncthreads();
+  // phase 2: vertical pass over the comb + epilogue
+  for (int i = threadIdx.x; i < kTY * kTX; i += kThreads) {
+    const int row = i / kTX, xl = i - row * kTX;
+    const int x = x0 + xl;
+    const long y = long(r) + long(k0 + row) * d;
+    if (y >= H || x >= W) continue;
+    float v[5];
+    unsigned present = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const long yy = y + long(k - 2) * d;
+      const bool ok = yy >= 0 && yy < H;
+      v[k] = hs[row + k][xl];
+      present |= ok ? (1u << k) : 0u;
+    }
+    float s = Taps<SIMPLE, false>(v, present);
+    const size_t idx = size_t(y) * W + x;
+    if (EPI == 1) s = __fsub_rn(__ldg(p.other + idx), s);
+    if (EPI == 2) {
+      const float c = (p.mask == nullptr || p.mask[idx]) ? __ldg(p.other + idx) : 0.0f;
+      s = __fadd_rn(s, c);
+    }
+    p.out[idx] = s;
+  }
+}
+
+// out = mask ? in : 0 (ApplyMask of the first recomposed plane) or a plain copy
+__global__ void MaskCopyKernel(float* out, const float* in, const uint8_t* mask, size_t n) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = (mask == nullptr || mask[i]) ? in[i] : 0.0f;
+}
+
+template <bool SIMPLE, int EPI>
+void LaunchSmooth(rdl_handle& h, const float* in, float* out, const float* other,
+                  const uint8_t* mask, size_t width, size_t height, int scale, cudaStream_t stream) {
+  SmoothParams p{};
+  p.in = in;
+  p.out = out;
+  p.other = other;
+  p.mask = mask;
+  p.width = int(width);
+  p.height = int(height);
+  p.d = (1 << scale) - 1;
+  const int residues = std::min<long>(p.d, long(height));
+  const int comb_rows = (int(height) + p.d - 1) / p.d;  // rows of the longest comb
+  p.blocks_per_residue = (comb_rows + kTY - 1) / kTY;
+  dim3 grid((unsigned(width) + kTX - 1) / kTX, unsigned(residues) * p.blocks_per_residue);
+  IuwtSmoothKernel<SIMPLE, EPI><<<grid, kThreads, 0, stream>>>(p);
+  RDL_CUDA(cudaGetLastError());
+  ++h.launches;
+}
+
+void CheckScale(size_t width, size_t height, int scale) {
+  // the reference's loops assume 2 d <= size - 2 d (iuwt_decomposition.cc:90-95): callers keep
+  // scale <= EndScale(min(W,H)) = log2(size) - 3 (iuwt_decomposition.h:182-184)
+  const size_t d = (size_t(1) << scale) - 1;
+  if (scale < 1 || scale > 20 || 4 * d > std::min(width, height))
+    throw std::invalid_argument("IUWT scale " + std::to_string(scale) + " too large for a " +
+                                std::to_string(width) + " x " + std::to_string(height) + " image");
+}
+
+}  // namespace
+
+void IuwtSmooth(rdl_handle& h, const float* in, float* out, size_t width, size_t height, int scale,
+                bool simple, cudaStream_t stream) {
+  CheckScale(width, height, scale);
+  if (in == out) throw std::invalid_argument("IUWT smoothing is out of place");
+  if (simple)
+    LaunchSmooth<true, 0>(h, in, out, nullptr, nullptr, width, height, scale, stream);
+  else
+    LaunchSmooth<false, 0>(h, in, out, nullptr, nullptr, width, height, scale, stream);
+}
+
+void IuwtDecompose(rdl_handle& h, const float* input, size_t width, size_t height, int n_scales,
+                   bool include_largest, float* coefficients, cudaStream_t stream) {
+  if (n_scales < 1) throw std::invalid_argument("IUWT needs at least one scale");
+  CheckScale(width, height, n_scales);
+  const size_t a = width * height;
+  h.iuwt_a.Reserve(a);
+  h.iuwt_b.Reserve(a);
+  const float* i0 = input;
+  float* bufs[2] = {h.iuwt_a.get(), h.iuwt_b.get()};
+  int next = 0;
+  for (int s = 0; s != n_scales; ++s) {
+    const bool last = s + 1 == n_scales;
+    // i1 = B(i0): the smooth remainder goes straight to its plane on the last scale
+    float* i1 = (last && include_largest) ? coefficients + size_t(n_scales) * a : bufs[next];
+    LaunchSmooth<false, 0>(h, i0, i1, nullptr, nullptr, width, height, s + 1, stream);
+    // w_s = i0 - B(i1)
+    LaunchSmooth<false, 1>(h, i1, coefficients + size_t(s) * a, i0, nullptr, width, height, s + 1,
+                           stream);
+    i0 = i1;  // "i0 = i1" of the reference without the copy
+    next ^= 1;
+  }
+}
+
+void IuwtRecompose(rdl_handle& h, const float* coefficients, size_t width, size_t height,
+                   int n_scales, bool include_largest, const uint8_t* masks, float* out,
+                   cudaStream_t stream) {
+  if (n_scales < 1) throw std::invalid_argument("IUWT needs at least one scale");
+  CheckScale(width, height, n_scales);
+  const size_t a = width * height;
+  h.iuwt_a.Reserve(a);
+  const bool start_with_largest = include_largest && masks == nullptr;
+  // smoothing steps still to run after the first plane is in place
+  int steps = start_with_largest ? n_scales : n_scales - 1;
+  float* bufs[2] = {out, h.iuwt_a.get()};
+  int cur = steps % 2;  // so that the last step lands in `out`
+  const int first_scale = start_with_largest ? n_scales : n_scales - 1;
+  const float* first = coefficients + size_t(first_scale) * a;
+  const uint8_t* first_mask = (masks && !start_with_largest) ? masks + size_t(first_scale) * a : nullptr;
+  MaskCopyKernel<<<kSmCount * 8, 256, 0, stream>>>(bufs[cur], first, first_mask, a);
+  RDL_CUDA(cudaGetLastError());
+  ++h.launches;
+  for (int s = first_scale - 1; s != -1; --s) {
+    LaunchSmooth<true, 2>(h, bufs[cur], bufs[cur ^ 1], coefficients + size_t(s) * a,
+                          masks ? masks + size_t(s) * a : nullptr, width, height, s + 1, stream);
+    cur ^= 1;
+  }
+}
+
+}  // namespace rdl
