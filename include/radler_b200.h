@@ -206,6 +206,26 @@ rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_
                                     uint64_t width, uint64_t height, float scale, int32_t shape,
                                     void* stream);
 
+/* ---- IUWT decomposition (cpp/algorithms/iuwt/iuwt_decomposition.{h,cc}); device pointers ----
+ * One B3-spline a-trous smoothing, taps {1,4,6,4,1}/16 at (2^scale - 1) * {-2..2}, scale >= 1.
+ * flavour 0: IuwtDecomposition::convolveMT (iuwt_decomposition.cc:55-67, used by DecomposeMt);
+ * flavour 1: IuwtDecomposition::convolve (iuwt_decomposition.h:249-267, used by Recompose and
+ * Convolve). Out of place. */
+rdl_status rdl_iuwt_smooth(rdl_handle* h, const float* device_in, float* device_out,
+                           uint64_t width, uint64_t height, int32_t scale, int32_t flavour,
+                           void* stream);
+/* IuwtDecomposition::Decompose / DecomposeMt (iuwt_decomposition.cc:9-53): writes n_scales
+ * wavelet planes (+ the smooth remainder as plane n_scales when include_largest) of
+ * width*height floats each into device_coefficients. */
+rdl_status rdl_iuwt_decompose(rdl_handle* h, const float* device_input, uint64_t width,
+                              uint64_t height, int32_t n_scales, int32_t include_largest,
+                              float* device_coefficients, void* stream);
+/* IuwtDecomposition::ApplyMask (iuwt_decomposition.h:162-169; device_masks = n_scales planes of
+ * width*height bytes, NULL = no mask) followed by Recompose (iuwt_decomposition.h:121-147). */
+rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, uint64_t width,
+                              uint64_t height, int32_t n_scales, int32_t include_largest,
+                              const uint8_t* device_masks, float* device_out, void* stream);
+
 /* utils::CalculateGoodFFTSize / GetConvolutionSize (cpp/utils/fft_size_calculations.h:15-50) */
 uint64_t rdl_good_fft_size(uint64_t minimum_size);
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);

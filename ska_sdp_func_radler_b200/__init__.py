@@ -86,7 +86,8 @@ EXPORTED_SYMBOLS = [
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
-    "rdl_multiscale_transform", "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
+    "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
     "rdl_device_count",
 ]
 
@@ -148,6 +149,9 @@ def lib():
     L.rdl_multiscale_transform.argtypes = [vp, vp, u64, u64, u64, f32, i32, vp]
     L.rdl_good_fft_size.argtypes = [u64]
     L.rdl_good_fft_size.restype = u64
+    L.rdl_iuwt_smooth.argtypes = [vp, vp, vp, u64, u64, C.c_int32, C.c_int32, vp]
+    L.rdl_iuwt_decompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
+    L.rdl_iuwt_recompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp, vp]
     L.rdl_convolution_size.argtypes = [C.c_double, u64, C.c_double]
     L.rdl_convolution_size.restype = u64
     L.rdl_version.restype = C.c_char_p
@@ -411,6 +415,28 @@ class DeconvolutionAlgorithm:
         t, space = _plane_pointers(images, n, h * w)
         assert space == MEM_DEVICE
         self._check(lib().rdl_multiscale_transform(self._h, t, n, w, h, scale, shape, stream))
+
+
+    # ---- IUWT decomposition (iuwt_decomposition.{h,cc}); torch device tensors ------------------
+    def iuwt_smooth(self, image, out, scale, simple=False, stream=None):
+        h, w = image.shape
+        self._check(lib().rdl_iuwt_smooth(self._h, image.data_ptr(), out.data_ptr(), w, h, scale,
+                                          int(simple), stream))
+
+    def iuwt_decompose(self, image, coefficients, n_scales, include_largest=True, stream=None):
+        """coefficients: [n_scales (+1), H, W] device tensor, filled in place."""
+        h, w = image.shape
+        assert coefficients.shape[0] >= n_scales + (1 if include_largest else 0)
+        self._check(lib().rdl_iuwt_decompose(self._h, image.data_ptr(), w, h, n_scales,
+                                             int(include_largest), coefficients.data_ptr(), stream))
+
+    def iuwt_recompose(self, coefficients, out, n_scales, include_largest=True, masks=None,
+                       stream=None):
+        h, w = out.shape
+        self._check(lib().rdl_iuwt_recompose(self._h, coefficients.data_ptr(), w, h, n_scales,
+                                             int(include_largest),
+                                             None if masks is None else masks.data_ptr(),
+                                             out.data_ptr(), stream))
 
 
 def GenericClean(use_sub_minor_optimization: bool = True, **kw) -> DeconvolutionAlgorithm:

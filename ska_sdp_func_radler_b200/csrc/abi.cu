@@ -6,6 +6,7 @@
 #include <new>
 
 #include "fft.cuh"
+#include "iuwt.cuh"
 #include "handle.h"
 #include "multiscale.cuh"
 
@@ -130,7 +131,8 @@ rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out) {
     g_create_error = why;
     return RDL_ERR_NO_DEVICE;
   }
-  if (cfg->algorithm != RDL_GENERIC_CLEAN && cfg->algorithm != RDL_MULTISCALE) {
+  if (cfg->algorithm != RDL_GENERIC_CLEAN && cfg->algorithm != RDL_MULTISCALE &&
+      cfg->algorithm != RDL_IUWT) {
     g_create_error = "algorithm not supported by this build";
     return RDL_ERR_UNSUPPORTED;
   }
@@ -370,8 +372,10 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
     rdl_result r{};
     if (h->config.algorithm == RDL_GENERIC_CLEAN)
       r = RunGenericClean(*h, cube, stream);
-    else
+    else if (h->config.algorithm == RDL_MULTISCALE)
       r = RunMultiScale(*h, cube, stream);
+    else
+      r = RunIuwt(*h, cube, stream);
     if (host) {
       for (size_t i = 0; i != cube.n_images; ++i) {
         RDL_CUDA(cudaMemcpyAsync(residual[i], cube.residual.p[i], bytes, cudaMemcpyDeviceToHost, stream));
@@ -490,6 +494,38 @@ rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_
     cudaStream_t stream = StreamOf(h, stream_v);
     MultiScaleTransform(*h, images, n_images, width, height, scale, shape, stream);
     RDL_CUDA(cudaGetLastError());
+  });
+}
+
+rdl_status rdl_iuwt_smooth(rdl_handle* h, const float* device_in, float* device_out,
+                           uint64_t width, uint64_t height, int32_t scale, int32_t flavour,
+                           void* stream_v) {
+  if (!h || !device_in || !device_out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    IuwtSmooth(*h, device_in, device_out, width, height, scale, flavour != 0, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_decompose(rdl_handle* h, const float* device_input, uint64_t width,
+                              uint64_t height, int32_t n_scales, int32_t include_largest,
+                              float* device_coefficients, void* stream_v) {
+  if (!h || !device_input || !device_coefficients) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    IuwtDecompose(*h, device_input, width, height, n_scales, include_largest != 0,
+                  device_coefficients, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, uint64_t width,
+                              uint64_t height, int32_t n_scales, int32_t include_largest,
+                              const uint8_t* device_masks, float* device_out, void* stream_v) {
+  if (!h || !device_coefficients || !device_out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    IuwtRecompose(*h, device_coefficients, width, height, n_scales, include_largest != 0,
+                  device_masks, device_out, StreamOf(h, stream_v));
   });
 }
 

@@ -174,6 +174,7 @@ struct rdl_handle {
 namespace rdl {
 rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream);
 rdl_result RunMultiScale(rdl_handle& h, DeviceCube& cube, cudaStream_t stream);
+rdl_result RunIuwt(rdl_handle& h, DeviceCube& cube, cudaStream_t stream);
 }  // namespace rdl
 
 #endif

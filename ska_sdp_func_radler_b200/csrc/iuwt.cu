@@ -251,4 +251,15 @@ void IuwtRecompose(rdl_handle& h, const float* coefficients, size_t width, size_
   }
 }
 
+// IuwtDeconvolution::ExecuteMajorIteration (iuwt_deconvolution.h:21-40 ->
+// IuwtDeconvolutionAlgorithm::PerformMajorIteration, iuwt_deconvolution_algorithm.cc:733-918).
+// The decomposition kernels above are in place; the structure search (SelectStructures flood
+// fill, conjugate-gradient deconvolution of the masked structure) is not yet on the device.
+// There is no CPU fallback in this library, so the call fails loudly instead.
+rdl_result RunIuwt(rdl_handle&, DeviceCube&, cudaStream_t) {
+  throw std::domain_error(
+      "IuwtDeconvolution::ExecuteMajorIteration is not implemented on the device yet; the IUWT "
+      "decomposition kernels are available through rdl_iuwt_decompose / rdl_iuwt_recompose");
+}
+
 }  // namespace rdl
