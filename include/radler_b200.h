@@ -206,6 +206,26 @@ rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_
                                     uint64_t width, uint64_t height, float scale, int32_t shape,
                                     void* stream);
 
+/* ---- multi-GPU: one process per GPU, rows of the cube sharded over the ranks ----------------
+ * The reference has no multi-device path; its closest analogue is the row split of
+ * SubtractImage / FindPeak over threads (threaded_deconvolution_tools.cc:18-28,
+ * peak_finder.h start_y/end_y). Here every rank holds the rows [y_offset, y_offset + height)
+ * of every image (cube->height is the band's row count) plus the full-frame PSFs; FindPeak and
+ * SubtractImage are local to the band, and the only exchange of a minor iteration is the joined
+ * arg-max: an NCCL all-gather of (64-bit peak key with the frame's row-major index, per-image
+ * values at that pixel) per rank, after which every rank runs the identical loop control.
+ * Results are bit-identical to the single-GPU loop. GenericClean without the sub-minor
+ * optimisation only. */
+/* ncclGetUniqueId: call on one rank, ship the 128 bytes to all ranks (e.g. torch.distributed). */
+rdl_status rdl_dist_unique_id(uint8_t* out128);
+/* ncclCommInitRank on the handle's device (collective over all ranks). */
+rdl_status rdl_dist_init(rdl_handle* h, const uint8_t* id128, int32_t rank, int32_t world);
+/* The next rdl_execute_major_iteration calls work on rows [y_offset, y_offset + cube->height) of
+ * a width x global_height frame; PSFs, clean mask and RMS image stay full-frame.
+ * global_height = 0 returns to whole frames. */
+rdl_status rdl_dist_set_row_band(rdl_handle* h, uint64_t y_offset, uint64_t global_height);
+rdl_status rdl_dist_finalize(rdl_handle* h);
+
 /* ---- IUWT decomposition (cpp/algorithms/iuwt/iuwt_decomposition.{h,cc}); device pointers ----
  * One B3-spline a-trous smoothing, taps {1,4,6,4,1}/16 at (2^scale - 1) * {-2..2}, scale >= 1.
  * flavour 0: IuwtDecomposition::convolveMT (iuwt_decomposition.cc:55-67, used by DecomposeMt);

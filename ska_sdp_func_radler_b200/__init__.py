@@ -87,6 +87,7 @@ EXPORTED_SYMBOLS = [
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_finalize",
     "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
     "rdl_device_count",
 ]
@@ -149,6 +150,10 @@ def lib():
     L.rdl_multiscale_transform.argtypes = [vp, vp, u64, u64, u64, f32, i32, vp]
     L.rdl_good_fft_size.argtypes = [u64]
     L.rdl_good_fft_size.restype = u64
+    L.rdl_dist_unique_id.argtypes = [vp]
+    L.rdl_dist_init.argtypes = [vp, vp, i32, i32]
+    L.rdl_dist_set_row_band.argtypes = [vp, u64, u64]
+    L.rdl_dist_finalize.argtypes = [vp]
     L.rdl_iuwt_smooth.argtypes = [vp, vp, vp, u64, u64, C.c_int32, C.c_int32, vp]
     L.rdl_iuwt_decompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
     L.rdl_iuwt_recompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp, vp]
@@ -360,7 +365,9 @@ class DeconvolutionAlgorithm:
         n = cube.width * cube.height
         rt, s0 = _plane_pointers(residual, cube.n_images, n)
         mt, s1 = _plane_pointers(model, cube.n_images, n)
-        pt, s2 = _plane_pointers(psfs, cube.n_channels, n)
+        # row-sharded cubes (dist_set_row_band) carry full-frame PSFs
+        psf_n = cube.width * self._frame_height if getattr(self, "_frame_height", 0) else n
+        pt, s2 = _plane_pointers(psfs, cube.n_channels, psf_n)
         if not (s0 == s1 == s2):
             raise ValueError("residual, model and psfs must live in the same memory space")
         d = cube.desc(s0)
@@ -417,6 +424,18 @@ class DeconvolutionAlgorithm:
         self._check(lib().rdl_multiscale_transform(self._h, t, n, w, h, scale, shape, stream))
 
 
+    # ---- multi-GPU: rows of the cube sharded over one process per GPU ---------------------------
+    def dist_init(self, unique_id: bytes, rank: int, world: int):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(lib().rdl_dist_init(self._h, buf, rank, world))
+
+    def dist_set_row_band(self, y_offset: int, global_height: int):
+        self._check(lib().rdl_dist_set_row_band(self._h, y_offset, global_height))
+        self._frame_height = global_height
+
+    def dist_finalize(self):
+        self._check(lib().rdl_dist_finalize(self._h))
+
     # ---- IUWT decomposition (iuwt_decomposition.{h,cc}); torch device tensors ------------------
     def iuwt_smooth(self, image, out, scale, simple=False, stream=None):
         h, w = image.shape
@@ -448,6 +467,15 @@ def GenericClean(use_sub_minor_optimization: bool = True, **kw) -> Deconvolution
 def MultiScaleAlgorithm(beam_size: float, pixel_scale: float = 1.0, **kw) -> DeconvolutionAlgorithm:
     """MultiScaleAlgorithm (cpp/algorithms/multiscale_algorithm.h)."""
     return DeconvolutionAlgorithm(MULTISCALE, beam_size=beam_size, pixel_scale=pixel_scale, **kw)
+
+
+def dist_unique_id() -> bytes:
+    """ncclGetUniqueId (128 bytes) for rdl_dist_init; create on rank 0 and broadcast."""
+    buf = (C.c_uint8 * 128)()
+    st = lib().rdl_dist_unique_id(buf)
+    if st != RDL_OK:
+        raise RadlerError(st, "ncclGetUniqueId failed (is libnccl.so.2 loadable?)")
+    return bytes(buf)
 
 
 def good_fft_size(n: int) -> int:

@@ -201,6 +201,10 @@ void rdl_destroy(rdl_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   h->ms.reset();
+  try {
+    NcclDestroy(h->dist);
+  } catch (...) {
+  }
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -333,9 +337,16 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
   return Guard(h, [&] {
     CheckCube(c);
     if (!residual || !model || !psfs) throw std::invalid_argument("null image table");
-    if (h->mask.get() && (h->mask_w != c->width || h->mask_h != c->height))
+    const bool sharded = h->dist.band_set;
+    const uint64_t frame_height = sharded ? h->dist.global_height : c->height;
+    if (sharded && (h->config.algorithm != RDL_GENERIC_CLEAN ||
+                    h->dist.y_offset + c->height > h->dist.global_height))
+      throw std::invalid_argument(sharded && h->config.algorithm != RDL_GENERIC_CLEAN
+                                      ? "row bands are supported by GenericClean only"
+                                      : "row band exceeds the frame");
+    if (h->mask.get() && (h->mask_w != c->width || h->mask_h != frame_height))
       throw std::invalid_argument("clean mask dimensions do not match the image");
-    if (h->rms.get() && (h->rms_w != c->width || h->rms_h != c->height))
+    if (h->rms.get() && (h->rms_w != c->width || h->rms_h != frame_height))
       throw std::invalid_argument("Error in RMS factor image dimensions!");
     if (h->fit_mode == RDL_FIT_POLYNOMIAL &&
         (h->fit_freqs.size() != c->n_channels || h->fit_n_pol != c->n_pol))
@@ -349,7 +360,8 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
     if (host) {
       h->stage_residual.Reserve(cube.n_images * n);
       h->stage_model.Reserve(cube.n_images * n);
-      h->stage_psf.Reserve(cube.n_channels * n);
+      const size_t psf_n = cube.width * frame_height, psf_bytes = psf_n * sizeof(float);
+      h->stage_psf.Reserve(cube.n_channels * psf_n);
       for (size_t i = 0; i != cube.n_images; ++i) {
         cube.residual.p[i] = h->stage_residual.get() + i * n;
         cube.model.p[i] = h->stage_model.get() + i * n;
@@ -357,8 +369,8 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
         RDL_CUDA(cudaMemcpyAsync(cube.model.p[i], model[i], bytes, cudaMemcpyHostToDevice, stream));
       }
       for (size_t i = 0; i != cube.n_channels; ++i) {
-        float* dst = h->stage_psf.get() + i * n;
-        RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], bytes, cudaMemcpyHostToDevice, stream));
+        float* dst = h->stage_psf.get() + i * psf_n;
+        RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], psf_bytes, cudaMemcpyHostToDevice, stream));
         cube.psf.p[i] = dst;
       }
     } else {
@@ -494,6 +506,42 @@ rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_
     cudaStream_t stream = StreamOf(h, stream_v);
     MultiScaleTransform(*h, images, n_images, width, height, scale, shape, stream);
     RDL_CUDA(cudaGetLastError());
+  });
+}
+
+// ---- multi-GPU: row-sharded GenericClean ----------------------------------------------------
+rdl_status rdl_dist_unique_id(uint8_t* out128) {
+  if (!out128) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(nullptr, [&] { NcclGetUniqueId(out128); });
+}
+
+rdl_status rdl_dist_init(rdl_handle* h, const uint8_t* id128, int32_t rank, int32_t world) {
+  if (!h || !id128) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    NcclInit(h->dist, id128, rank, world);
+  });
+}
+
+rdl_status rdl_dist_set_row_band(rdl_handle* h, uint64_t y_offset, uint64_t global_height) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    if (global_height == 0) {  // back to whole frames
+      h->dist.band_set = false;
+      return;
+    }
+    if (y_offset >= global_height) throw std::invalid_argument("row band starts outside the frame");
+    h->dist.band_set = true;
+    h->dist.y_offset = y_offset;
+    h->dist.global_height = global_height;
+  });
+}
+
+rdl_status rdl_dist_finalize(rdl_handle* h) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    NcclDestroy(h->dist);
+    h->dist = DistContext{};
   });
 }
 

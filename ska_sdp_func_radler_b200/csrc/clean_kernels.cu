@@ -70,7 +70,8 @@ __device__ __forceinline__ void IntegrateVec(const IntegSpec& s, const ConstPtrT
 // Key of VEC integrated values (applies RMS factor, mask and the search window).
 template <int VEC>
 __device__ __forceinline__ unsigned long long KeysOf(const float (&val)[VEC], size_t i0, int y,
-                                                     int x0, const PeakWindow& w) {
+                                                     int x0, const PeakWindow& w,
+                                                     uint32_t key_offset = 0u) {
   unsigned long long best = 0ull;
   if (y < w.y0 || y >= w.y1) return best;
   if (x0 + VEC <= w.x0 || x0 >= w.x1) return best;
@@ -84,7 +85,8 @@ __device__ __forceinline__ unsigned long long KeysOf(const float (&val)[VEC], si
     if (x < w.x0 || x >= w.x1) continue;
     if (w.mask && !m[l]) continue;
     const float v = w.rms_factor ? __fmul_rn(val[l], r[l]) : val[l];
-    const unsigned long long k = MakePeakKey(v, w.allow_negative != 0, uint32_t(i0 + l));
+    const unsigned long long k =
+        MakePeakKey(v, w.allow_negative != 0, uint32_t(i0 + l) + key_offset);
     best = k > best ? k : best;
   }
   return best;
@@ -187,11 +189,13 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // Loop control run by warp 0 of the last block (generic_clean.cc:99-112, 169-206).
+// `key` indexes the width x global_height frame. values_ready: s_values already holds the
+// per-image residual values at the peak (row-sharded path); otherwise they are read here.
 template <bool FIRST>
-__device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_values) {
+__device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_values,
+                              unsigned long long key, bool values_ready) {
   const int lane = threadIdx.x;
   const int slot = st->slot;
-  const unsigned long long key = __ldcg(&st->key[slot]);
   float val = 0.0f;
   uint32_t index = 0;
   const bool has = DecodePeakKey(key, val, index);
@@ -228,10 +232,14 @@ __device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_va
     if (!cont) done = 1;
   }
   const int x = has ? int(index % uint32_t(p.width)) : p.width;
-  const int y = has ? int(index / uint32_t(p.width)) : p.height;
+  const int y = has ? int(index / uint32_t(p.width)) : p.global_height;
+  // position inside this rank's row band (the whole frame on a single GPU)
+  const bool owner = has && y >= p.y_offset && y < p.y_offset + p.height;
+  const size_t local_index = owner ? size_t(index) - size_t(p.y_offset) * p.width : 0;
   if (!done) {
     // peakValues[i] = dirty[i][peak]; PerformSpectralFit; *= gain; model[i][peak] += ...
-    for (int i = lane; i < p.n_images; i += 32) s_values[i] = __ldcg(p.img.p[i] + index);
+    if (!values_ready)
+      for (int i = lane; i < p.n_images; i += 32) s_values[i] = __ldcg(p.img.p[i] + local_index);
     __syncwarp();
     if (p.projection) {
       // values of polarisation pol sit at [ch * n_pol + pol]
@@ -251,8 +259,10 @@ __device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_va
     }
     for (int i = lane; i < p.n_images; i += 32) {
       const float v = __fmul_rn(s_values[i], p.gain);
-      float* m = p.model.p[i] + index;
-      *m = __fadd_rn(*m, v);
+      if (owner) {
+        float* m = p.model.p[i] + local_index;
+        *m = __fadd_rn(*m, v);
+      }
       st->factors[i] = v;
     }
     if (lane == 0 && st->n_trace < p.trace_capacity) {
@@ -289,10 +299,11 @@ __global__ void __launch_bounds__(kThreads)
   const int width = p.width, height = p.height;
   SubtractWindow sw{};
   if (!FIRST) {
-    sw = MakeSubtractWindow(st->px, st->py, width, height);
+    sw = MakeSubtractWindow(st->px, st->py, width, p.global_height);
     if (threadIdx.x < p.n_images) s_factors[threadIdx.x] = st->factors[threadIdx.x];
     __syncthreads();
   }
+  const uint32_t key_offset = uint32_t(p.y_offset) * uint32_t(width);
   const IntegSpec& spec = FIRST ? p.first_spec : p.step_spec;
   const ConstPtrTable& cimg = reinterpret_cast<const ConstPtrTable&>(p.img);
   const size_t n_vec = size_t(width) * height / VEC;
@@ -300,7 +311,8 @@ __global__ void __launch_bounds__(kThreads)
   for (size_t v = size_t(blockIdx.x) * kThreads + threadIdx.x; v < n_vec;
        v += size_t(gridDim.x) * kThreads) {
     const size_t i0 = v * VEC;
-    const int y = int(i0 / width), x0 = int(i0 - size_t(y) * width);
+    const int y_local = int(i0 / width), x0 = int(i0 - size_t(y_local) * width);
+    const int y = y_local + p.y_offset;  // frame row
     const bool in_window =
         !FIRST && y >= sw.sy && y < sw.ey && x0 + VEC > sw.sx && x0 < sw.ex;
     float val[VEC];
@@ -355,7 +367,7 @@ __global__ void __launch_bounds__(kThreads)
       }
       IntegrateVec<VEC>(spec, cimg, i0, val);  // re-reads this thread's own stores
     }
-    const unsigned long long k = KeysOf<VEC>(val, i0, y, x0, p.window);
+    const unsigned long long k = KeysOf<VEC>(val, i0, y, x0, p.window, key_offset);
     best = k > best ? k : best;
   }
   __threadfence();  // publish this thread's image stores before the ticket
@@ -369,8 +381,43 @@ __global__ void __launch_bounds__(kThreads)
   __syncthreads();
   if (s_is_last && threadIdx.x < 32) {
     __threadfence();
-    HogbomControl<FIRST>(p, st, s_factors);
+    const unsigned long long key = __ldcg(&st->key[slot]);
+    if (!p.dist) {
+      HogbomControl<FIRST>(p, st, s_factors, key, false);
+    } else {
+      // row-sharded: publish this rank's candidate; the joined control runs after the exchange
+      float val;
+      uint32_t index;
+      const bool has = DecodePeakKey(key, val, index);
+      const size_t local_index = has ? size_t(index) - size_t(key_offset) : 0;
+      for (int i = threadIdx.x; i < kMaxImages; i += 32)
+        p.cand_local->values[i] =
+            (has && i < p.n_images) ? __ldcg(p.img.p[i] + local_index) : 0.0f;
+      if (threadIdx.x == 0) {
+        p.cand_local->key = key;  // the joined control resets key / slot / ticket
+      }
+    }
   }
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(32)
+    HogbomDistControlKernel(const __grid_constant__ HogbomParams p, CleanState* st,
+                            const DistCandidate* all, int world) {
+  if (st->done) return;
+  __shared__ float s_values[kMaxImages];
+  unsigned long long best = 0ull;
+  int winner = 0;
+  for (int r = 0; r < world; ++r) {
+    const unsigned long long k = all[r].key;
+    if (k > best) {
+      best = k;
+      winner = r;
+    }
+  }
+  for (int i = threadIdx.x; i < p.n_images; i += 32) s_values[i] = all[winner].values[i];
+  __syncwarp();
+  HogbomControl<FIRST>(p, st, s_values, best, true);
 }
 
 int GridFor(size_t work_items, int blocks_per_sm) {
@@ -395,6 +442,14 @@ void LaunchHogbomStep(const HogbomParams& p, CleanState* state, bool first, int 
     else       { if (simple) RDL_LAUNCH(1, false, true); else RDL_LAUNCH(1, false, false); }
   }
 #undef RDL_LAUNCH
+}
+
+void LaunchHogbomDistControl(const HogbomParams& p, CleanState* state, const DistCandidate* all,
+                             int world, bool first, cudaStream_t stream) {
+  if (first)
+    HogbomDistControlKernel<true><<<1, 32, 0, stream>>>(p, state, all, world);
+  else
+    HogbomDistControlKernel<false><<<1, 32, 0, stream>>>(p, state, all, world);
 }
 
 void LaunchFindPeak(const IntegSpec& spec, const ConstPtrTable& images, int width, int height,

@@ -51,6 +51,14 @@ struct CleanState {
   float factors[kMaxImages];  // per image: fitted peak value * gain
 };
 
+// Row-sharded (multi-GPU) Hogbom: what one rank contributes to the joined arg-max — its best
+// key (global row-major index, so the lowest index still wins ties across ranks) and the
+// per-image residual values at that pixel, which only the owning rank holds.
+struct DistCandidate {
+  unsigned long long key;
+  float values[kMaxImages];
+};
+
 struct TraceEntry {  // == rdl_trace_entry
   uint32_t iteration, scale_index, x, y;
   float value;
@@ -75,10 +83,20 @@ struct HogbomParams {
   int n_fit, n_pol;
   TraceEntry* trace;
   unsigned long long trace_capacity;
+  // row band of a sharded cube: the images hold rows [y_offset, y_offset + height) of a
+  // width x global_height frame; PSFs, borders and peak indices stay in frame coordinates.
+  int y_offset, global_height;
+  int dist;                   // 1: the last block writes cand_local instead of running the control
+  DistCandidate* cand_local;
 };
 
 void LaunchHogbomStep(const HogbomParams& p, CleanState* state, bool first, int vec,
                       cudaStream_t stream);
+
+// Joined control step of the row-sharded loop: picks the best of the gathered candidates and
+// runs the same loop control as the single-GPU path (every rank redundantly, bit-identically).
+void LaunchHogbomDistControl(const HogbomParams& p, CleanState* state, const DistCandidate* all,
+                             int world, bool first, cudaStream_t stream);
 
 void LaunchFindPeak(const IntegSpec& spec, const ConstPtrTable& images, int width, int height,
                     const PeakWindow& window, unsigned long long* key, int vec,

@@ -1,0 +1,91 @@
+// NCCL bindings resolved with dlopen (see dist.h).
+#include "dist.h"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <mutex>
+#include <string>
+
+#include "common.cuh"
+
+namespace rdl {
+namespace {
+
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+const NcclApi& Api() {
+  static NcclApi api;
+  static std::once_flag once;
+  static std::string error;
+  std::call_once(once, [] {
+    // a process that imported torch already has its bundled libnccl.so.2 loaded: same SONAME
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) {
+      error = std::string("cannot load libnccl: ") + dlerror();
+      return;
+    }
+    auto sym = [&](const char* name) {
+      void* p = dlsym(lib, name);
+      if (!p && error.empty()) error = std::string("libnccl lacks ") + name;
+      return p;
+    };
+    api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+    api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+    api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+    api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+    api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+  });
+  if (!error.empty()) throw CudaError(error);
+  return api;
+}
+
+void Check(ncclResult_t r, const char* what) {
+  if (r != ncclSuccess) throw CudaError(std::string(what) + ": " + Api().GetErrorString(r));
+}
+
+static_assert(sizeof(ncclUniqueId) == kUniqueIdBytes, "ncclUniqueId size");
+
+}  // namespace
+
+void NcclGetUniqueId(uint8_t out[kUniqueIdBytes]) {
+  ncclUniqueId id;
+  Check(Api().GetUniqueId(&id), "ncclGetUniqueId");
+  memcpy(out, &id, kUniqueIdBytes);
+}
+
+void NcclInit(DistContext& ctx, const uint8_t id_bytes[kUniqueIdBytes], int rank, int world) {
+  if (world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("bad rank / world size");
+  NcclDestroy(ctx);
+  ctx.rank = rank;
+  ctx.world = world;
+  if (world == 1) return;
+  ncclUniqueId id;
+  memcpy(&id, id_bytes, kUniqueIdBytes);
+  ncclComm_t comm = nullptr;
+  Check(Api().CommInitRank(&comm, world, id, rank), "ncclCommInitRank");
+  ctx.comm = comm;
+}
+
+void NcclDestroy(DistContext& ctx) {
+  if (ctx.comm) Api().CommDestroy(static_cast<ncclComm_t>(ctx.comm));
+  ctx.comm = nullptr;
+}
+
+void NcclAllGatherBytes(DistContext& ctx, const void* send, void* recv, size_t bytes_per_rank,
+                        cudaStream_t stream) {
+  if (!ctx.comm) throw std::invalid_argument("rdl_dist_init was not called on this handle");
+  Check(Api().AllGather(send, recv, bytes_per_rank, ncclChar, static_cast<ncclComm_t>(ctx.comm),
+                        stream),
+        "ncclAllGather");
+}
+
+}  // namespace rdl

@@ -1,0 +1,32 @@
+// Multi-GPU plumbing of the row-sharded Hogbom loop: NCCL (over NVLink / NVSwitch) is loaded at
+// run time, so single-GPU users carry no NCCL dependency. One process per GPU; the only exchange
+// of the path is the joined arg-max: an all-gather of one DistCandidate (264 bytes) per rank per
+// minor iteration.
+#ifndef RDL_DIST_H_
+#define RDL_DIST_H_
+
+#include <cstddef>
+#include <cstdint>
+
+#include <cuda_runtime.h>
+
+namespace rdl {
+
+constexpr size_t kUniqueIdBytes = 128;  // sizeof(ncclUniqueId)
+
+struct DistContext {
+  void* comm = nullptr;  // ncclComm_t
+  int rank = 0, world = 1;
+  bool band_set = false;
+  size_t y_offset = 0, global_height = 0;
+};
+
+// Throws CudaError when libnccl cannot be loaded or a call fails.
+void NcclGetUniqueId(uint8_t out[kUniqueIdBytes]);
+void NcclInit(DistContext& ctx, const uint8_t id[kUniqueIdBytes], int rank, int world);
+void NcclDestroy(DistContext& ctx);
+void NcclAllGatherBytes(DistContext& ctx, const void* send, void* recv, size_t bytes_per_rank,
+                        cudaStream_t stream);
+
+}  // namespace rdl
+#endif

@@ -53,6 +53,9 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   const size_t width = cube.width, height = cube.height;
   const uint64_t iteration_at_start = h.iteration_number;
 
+  if (h.dist.band_set && h.config.use_sub_minor_optimization)
+    throw std::domain_error("row-sharded cubes are supported by GenericClean without the sub-minor "
+                            "optimisation only");
   if (h.config.use_sub_minor_optimization) return RunGenericCleanSubMinor(h, cube, stream);
 
   HogbomParams p{};
@@ -84,6 +87,38 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   h.trace_dev.Reserve(std::max<uint64_t>(h.trace_capacity, 1));
   p.trace = h.trace_dev.get();
   p.trace_capacity = h.trace_capacity;
+  p.y_offset = 0;
+  p.global_height = int(height);
+  const bool sharded = h.dist.band_set;
+  if (sharded) {
+    // Row band of a width x global_height frame (rdl_dist_set_row_band): borders, window and
+    // peak indices are the frame's; mask / RMS image are full-frame, offset to this band.
+    const size_t gh = h.dist.global_height;
+    p.y_offset = int(h.dist.y_offset);
+    p.global_height = int(gh);
+    const size_t gvb = size_t(std::round(gh * h.settings.clean_border_ratio));
+    const size_t band = h.dist.y_offset * width;
+    p.window = MakePeakWindow(width, gh, 0, gh, hb, gvb, h.mask.get() ? h.mask.get() + band : nullptr,
+                              h.rms.get() ? h.rms.get() + band : nullptr,
+                              h.settings.allow_negative_components);
+    p.dist = 1;
+    h.cand_local.Reserve(1);
+    h.cand_all.Reserve(size_t(h.dist.world));
+    p.cand_local = h.cand_local.get();
+  }
+  auto step = [&](bool first) {
+    LaunchHogbomStep(p, h.state.get(), first, cube.vec, stream);
+    ++h.launches;
+    if (sharded) {
+      if (h.dist.world > 1)
+        NcclAllGatherBytes(h.dist, h.cand_local.get(), h.cand_all.get(), sizeof(DistCandidate),
+                           stream);
+      LaunchHogbomDistControl(p, h.state.get(),
+                              h.dist.world > 1 ? h.cand_all.get() : h.cand_local.get(),
+                              h.dist.world, first, stream);
+      ++h.launches;
+    }
+  };
 
   h.state.Reserve(1);
   PinnedState host;
@@ -91,11 +126,13 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   host.p->iteration = h.iteration_number;
   RDL_CUDA(cudaMemcpyAsync(h.state.get(), host.p, sizeof(CleanState), cudaMemcpyHostToDevice,
                            stream));
-  LaunchHogbomStep(p, h.state.get(), true, cube.vec, stream);
-  ++h.launches;
+  step(true);
 
   // Batch size: about a millisecond of device work between polls.
-  const double bytes_per_iteration = 12.0 * double(cube.n_images) * double(cube.Pixels());
+  // (identical on every rank of a sharded run: the ranks must issue the same number of exchanges)
+  const double pixels = sharded ? double(width) * double(h.dist.global_height) / h.dist.world
+                                : double(cube.Pixels());
+  const double bytes_per_iteration = 12.0 * double(cube.n_images) * pixels;
   const double t_iteration = std::max(bytes_per_iteration / 6.0e12, 3.0e-6);
   const int batch = int(std::clamp(1.0e-3 / t_iteration, 8.0, 256.0));
   for (;;) {
@@ -103,8 +140,7 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
                              stream));
     RDL_CUDA(cudaStreamSynchronize(stream));
     if (host.p->done) break;
-    for (int b = 0; b != batch; ++b) LaunchHogbomStep(p, h.state.get(), false, cube.vec, stream);
-    h.launches += batch;
+    for (int b = 0; b != batch; ++b) step(false);
     RDL_CUDA(cudaGetLastError());
   }
   const CleanState s = *host.p;

@@ -12,6 +12,7 @@
 #include "../../include/radler_b200.h"
 #include "clean_kernels.cuh"
 #include "common.cuh"
+#include "dist.h"
 
 namespace rdl {
 
@@ -165,6 +166,9 @@ struct rdl_handle {
   rdl::DeviceBuffer<float> fft_scratch, small_kernel;
   rdl::DeviceBuffer<float2> fft_spectrum;
   rdl::DeviceBuffer<float> iuwt_a, iuwt_b;  // IUWT ping-pong planes
+  // row-sharded multi-GPU loop (not cloned)
+  rdl::DistContext dist;
+  rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
   // FFT engines by frame size (plans, twiddle tables, work spectrum); not cloned
