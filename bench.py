@@ -136,15 +136,21 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def window_area(n, x, y, y0=0, y1=None):
+def window_area(n, x, y, owned_rows=None):
     """Clipped PSF window of SubtractImage (simple_clean.cc:61-96), per component, restricted
-    to the rows [y0, y1) a rank owns."""
-    y1 = n if y1 is None else y1
+    to the frame rows a rank owns (all rows when None)."""
     sx = np.maximum(x - n // 2, 0)
     ex = np.minimum(x + n // 2, n)
-    sy = np.maximum(np.maximum(y - n // 2, 0), y0)
-    ey = np.minimum(np.minimum(y + n // 2, n), y1)
-    return (ex - sx).astype(np.float64) * np.maximum(ey - sy, 0)
+    sy = np.maximum(y - n // 2, 0)
+    ey = np.minimum(y + n // 2, n)
+    if owned_rows is None:
+        rows = ey - sy
+    else:
+        own = np.zeros(n + 1, np.int64)
+        own[np.asarray(owned_rows) + 1] = 1
+        cum = np.cumsum(own)
+        rows = cum[ey] - cum[sy]
+    return (ex - sx).astype(np.float64) * rows
 
 
 # --------------------------------------------------------------------------------------
@@ -253,7 +259,7 @@ def base_line(args, value, ms_per_step):
                    "size": args.size, "channels": args.channels, "iters_per_step": args.iters,
                    "l2": "inputs larger than L2 (cube >> 126 MB)" if
                    args.size * args.size * args.channels * 4 > 4 * 126e6 else "L2-resident cube",
-                   "parallelism": f"rows of one cube sharded over {args.gpus} GPUs, NCCL joined "
+                   "parallelism": f"rows of one cube sharded over {args.gpus} GPUs (cyclic 64-row blocks), NCCL joined "
                                   "arg-max (all-gather of one 264-byte candidate per rank per "
                                   "minor iteration)" if args.gpus > 1 else "single GPU"},
     }
@@ -276,17 +282,19 @@ def run_ours(args):
     # N > 1: ONE cube, its rows sharded over the ranks (strong scaling); every rank generates the
     # same synthetic frame and keeps its band. The joined arg-max is the only exchange.
     res0, psfs, weights, freqs = make_cube(n, c, dev, seed=1)
-    y0, y1 = rd.row_band(n, rank, world)
+    block_rows = 64  # cyclic row blocks: every rank sees the same share of each PSF window
+    owned = None
     if world > 1:
-        res0 = res0[:, y0:y1].contiguous()
-    rows = y1 - y0
+        owned = rd.cyclic_rows(n, rank, world, block_rows)
+        res0 = res0.index_select(1, torch.from_numpy(owned).to(dev)).contiguous()
+    rows = n // world
     cube = rdl.Cube(n, rows, c, 1, weights)
     alg = rdl.GenericClean(use_sub_minor_optimization=False, device=local)
     alg.apply(max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1, threshold=0.0,
               trace_capacity=iters)
     if world > 1:
         alg.dist_init(rd.share_unique_id(rdl.dist_unique_id, rank, world, device=dev), rank, world)
-        alg.dist_set_row_band(y0, n)
+        alg.dist_set_row_blocks(block_rows, n)
     stream = torch.cuda.current_stream().cuda_stream
     res = res0.clone()
     model = torch.zeros_like(res)
@@ -315,7 +323,7 @@ def run_ours(args):
         r = step_device()
         total_iters += r.iteration_number
         tr = alg.trace()
-        a_sub = window_area(n, tr["x"].astype(np.int64), tr["y"].astype(np.int64), y0, y1)
+        a_sub = window_area(n, tr["x"].astype(np.int64), tr["y"].astype(np.int64), owned)
         # fused kernel minimum: every image read once (4*C*A) + PSF read and residual
         # write-back inside the window (8*C*A_sub). SURVEY U3 = 12*C*A_sub + 4*C*A_pk.
         # (A = this rank's row band, A_sub = the window clipped to it.)

@@ -224,6 +224,12 @@ rdl_status rdl_dist_init(rdl_handle* h, const uint8_t* id128, int32_t rank, int3
  * a width x global_height frame; PSFs, clean mask and RMS image stay full-frame.
  * global_height = 0 returns to whole frames. */
 rdl_status rdl_dist_set_row_band(rdl_handle* h, uint64_t y_offset, uint64_t global_height);
+/* Cyclic variant (after rdl_dist_init): rank r owns the row blocks b with b % world == r, block b
+ * = rows [b * block_rows, (b + 1) * block_rows), stored one after the other; cube->height =
+ * global_height / world. A PSF window covers half the frame, so contiguous bands leave some
+ * ranks with three times the work of others; cyclic blocks balance it. global_height must be a
+ * multiple of block_rows * world. */
+rdl_status rdl_dist_set_row_blocks(rdl_handle* h, uint64_t block_rows, uint64_t global_height);
 rdl_status rdl_dist_finalize(rdl_handle* h);
 
 /* ---- IUWT decomposition (cpp/algorithms/iuwt/iuwt_decomposition.{h,cc}); device pointers ----

@@ -87,7 +87,8 @@ EXPORTED_SYMBOLS = [
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
-    "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_finalize",
+    "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
+    "rdl_dist_finalize",
     "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
     "rdl_device_count",
 ]
@@ -153,6 +154,7 @@ def lib():
     L.rdl_dist_unique_id.argtypes = [vp]
     L.rdl_dist_init.argtypes = [vp, vp, i32, i32]
     L.rdl_dist_set_row_band.argtypes = [vp, u64, u64]
+    L.rdl_dist_set_row_blocks.argtypes = [vp, u64, u64]
     L.rdl_dist_finalize.argtypes = [vp]
     L.rdl_iuwt_smooth.argtypes = [vp, vp, vp, u64, u64, C.c_int32, C.c_int32, vp]
     L.rdl_iuwt_decompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
@@ -431,6 +433,10 @@ class DeconvolutionAlgorithm:
 
     def dist_set_row_band(self, y_offset: int, global_height: int):
         self._check(lib().rdl_dist_set_row_band(self._h, y_offset, global_height))
+        self._frame_height = global_height
+
+    def dist_set_row_blocks(self, block_rows: int, global_height: int):
+        self._check(lib().rdl_dist_set_row_blocks(self._h, block_rows, global_height))
         self._frame_height = global_height
 
     def dist_finalize(self):

@@ -340,7 +340,9 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
     const bool sharded = h->dist.band_set;
     const uint64_t frame_height = sharded ? h->dist.global_height : c->height;
     if (sharded && (h->config.algorithm != RDL_GENERIC_CLEAN ||
-                    h->dist.y_offset + c->height > h->dist.global_height))
+                    (h->dist.block_rows
+                         ? c->height * uint64_t(h->dist.world) != h->dist.global_height
+                         : h->dist.y_offset + c->height > h->dist.global_height)))
       throw std::invalid_argument(sharded && h->config.algorithm != RDL_GENERIC_CLEAN
                                       ? "row bands are supported by GenericClean only"
                                       : "row band exceeds the frame");
@@ -534,6 +536,20 @@ rdl_status rdl_dist_set_row_band(rdl_handle* h, uint64_t y_offset, uint64_t glob
     h->dist.band_set = true;
     h->dist.y_offset = y_offset;
     h->dist.global_height = global_height;
+    h->dist.block_rows = 0;
+  });
+}
+
+rdl_status rdl_dist_set_row_blocks(rdl_handle* h, uint64_t block_rows, uint64_t global_height) {
+  if (!h) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    if (block_rows == 0 || global_height == 0 ||
+        global_height % (block_rows * uint64_t(h->dist.world)) != 0)
+      throw std::invalid_argument("the frame height must be a multiple of block_rows * world");
+    h->dist.band_set = true;
+    h->dist.y_offset = 0;
+    h->dist.global_height = global_height;
+    h->dist.block_rows = block_rows;
   });
 }
 

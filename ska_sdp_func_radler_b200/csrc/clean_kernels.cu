@@ -77,8 +77,9 @@ __device__ __forceinline__ unsigned long long KeysOf(const float (&val)[VEC], si
   if (x0 + VEC <= w.x0 || x0 >= w.x1) return best;
   float r[VEC];
   bool m[VEC];
-  if (w.rms_factor) Vec<VEC>::Load(w.rms_factor + i0, r);
-  if (w.mask) Vec<VEC>::LoadMask(w.mask + i0, m);
+  // mask / RMS image are full-frame: index them (and the key) in frame coordinates
+  if (w.rms_factor) Vec<VEC>::Load(w.rms_factor + i0 + key_offset, r);
+  if (w.mask) Vec<VEC>::LoadMask(w.mask + i0 + key_offset, m);
 #pragma unroll
   for (int l = 0; l < VEC; ++l) {
     const int x = x0 + l;
@@ -234,8 +235,9 @@ __device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_va
   const int x = has ? int(index % uint32_t(p.width)) : p.width;
   const int y = has ? int(index / uint32_t(p.width)) : p.global_height;
   // position inside this rank's row band (the whole frame on a single GPU)
-  const bool owner = has && y >= p.y_offset && y < p.y_offset + p.height;
-  const size_t local_index = owner ? size_t(index) - size_t(p.y_offset) * p.width : 0;
+  int y_local = 0;
+  const bool owner = has && LocalRow(p, y, y_local);
+  const size_t local_index = owner ? size_t(y_local) * p.width + x : 0;
   if (!done) {
     // peakValues[i] = dirty[i][peak]; PerformSpectralFit; *= gain; model[i][peak] += ...
     if (!values_ready)
@@ -303,7 +305,6 @@ __global__ void __launch_bounds__(kThreads)
     if (threadIdx.x < p.n_images) s_factors[threadIdx.x] = st->factors[threadIdx.x];
     __syncthreads();
   }
-  const uint32_t key_offset = uint32_t(p.y_offset) * uint32_t(width);
   const IntegSpec& spec = FIRST ? p.first_spec : p.step_spec;
   const ConstPtrTable& cimg = reinterpret_cast<const ConstPtrTable&>(p.img);
   const size_t n_vec = size_t(width) * height / VEC;
@@ -312,7 +313,8 @@ __global__ void __launch_bounds__(kThreads)
        v += size_t(gridDim.x) * kThreads) {
     const size_t i0 = v * VEC;
     const int y_local = int(i0 / width), x0 = int(i0 - size_t(y_local) * width);
-    const int y = y_local + p.y_offset;  // frame row
+    const int y = FrameRow(p, y_local);  // frame row
+    const uint32_t key_offset = uint32_t(y - y_local) * uint32_t(width);
     const bool in_window =
         !FIRST && y >= sw.sy && y < sw.ey && x0 + VEC > sw.sx && x0 < sw.ex;
     float val[VEC];
@@ -389,7 +391,9 @@ __global__ void __launch_bounds__(kThreads)
       float val;
       uint32_t index;
       const bool has = DecodePeakKey(key, val, index);
-      const size_t local_index = has ? size_t(index) - size_t(key_offset) : 0;
+      int yl = 0;
+      if (has) LocalRow(p, int(index / uint32_t(width)), yl);
+      const size_t local_index = has ? size_t(yl) * width + index % uint32_t(width) : 0;
       for (int i = threadIdx.x; i < kMaxImages; i += 32)
         p.cand_local->values[i] =
             (has && i < p.n_images) ? __ldcg(p.img.p[i] + local_index) : 0.0f;

@@ -83,9 +83,13 @@ struct HogbomParams {
   int n_fit, n_pol;
   TraceEntry* trace;
   unsigned long long trace_capacity;
-  // row band of a sharded cube: the images hold rows [y_offset, y_offset + height) of a
-  // width x global_height frame; PSFs, borders and peak indices stay in frame coordinates.
+  // rows of a sharded cube: local row yl is frame row
+  //   y = y_offset + ((yl / block_rows) * block_world + block_rank) * block_rows + yl % block_rows
+  // of a width x global_height frame. Contiguous band: block_rows = height, block_world = 1;
+  // cyclic row blocks (balances the PSF-window work over the ranks): y_offset = 0,
+  // block_world = world. PSFs, mask, RMS image, borders and peak indices are the frame's.
   int y_offset, global_height;
+  int block_rows, block_world, block_rank;
   int dist;                   // 1: the last block writes cand_local instead of running the control
   DistCandidate* cand_local;
 };
@@ -95,6 +99,20 @@ void LaunchHogbomStep(const HogbomParams& p, CleanState* state, bool first, int 
 
 // Joined control step of the row-sharded loop: picks the best of the gathered candidates and
 // runs the same loop control as the single-GPU path (every rank redundantly, bit-identically).
+// frame row of local row yl / local row of frame row y (false when another rank owns it)
+__host__ __device__ inline int FrameRow(const HogbomParams& p, int yl) {
+  const int b = yl / p.block_rows;
+  return p.y_offset + (b * p.block_world + p.block_rank) * p.block_rows + (yl - b * p.block_rows);
+}
+__host__ __device__ inline bool LocalRow(const HogbomParams& p, int y, int& yl) {
+  const int yy = y - p.y_offset;
+  if (yy < 0) return false;
+  const int b = yy / p.block_rows;
+  if (b % p.block_world != p.block_rank) return false;
+  yl = (b / p.block_world) * p.block_rows + (yy - b * p.block_rows);
+  return yl < p.height;
+}
+
 void LaunchHogbomDistControl(const HogbomParams& p, CleanState* state, const DistCandidate* all,
                              int world, bool first, cudaStream_t stream);
 

@@ -19,6 +19,7 @@ struct DistContext {
   int rank = 0, world = 1;
   bool band_set = false;
   size_t y_offset = 0, global_height = 0;
+  size_t block_rows = 0;  // > 0: cyclic row blocks (rank owns blocks b with b % world == rank)
 };
 
 // Throws CudaError when libnccl cannot be loaded or a call fails.

@@ -89,6 +89,9 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   p.trace_capacity = h.trace_capacity;
   p.y_offset = 0;
   p.global_height = int(height);
+  p.block_rows = int(height);
+  p.block_world = 1;
+  p.block_rank = 0;
   const bool sharded = h.dist.band_set;
   if (sharded) {
     // Row band of a width x global_height frame (rdl_dist_set_row_band): borders, window and
@@ -97,9 +100,13 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
     p.y_offset = int(h.dist.y_offset);
     p.global_height = int(gh);
     const size_t gvb = size_t(std::round(gh * h.settings.clean_border_ratio));
-    const size_t band = h.dist.y_offset * width;
-    p.window = MakePeakWindow(width, gh, 0, gh, hb, gvb, h.mask.get() ? h.mask.get() + band : nullptr,
-                              h.rms.get() ? h.rms.get() + band : nullptr,
+    if (h.dist.block_rows) {
+      p.y_offset = 0;
+      p.block_rows = int(h.dist.block_rows);
+      p.block_world = h.dist.world;
+      p.block_rank = h.dist.rank;
+    }
+    p.window = MakePeakWindow(width, gh, 0, gh, hb, gvb, h.mask.get(), h.rms.get(),
                               h.settings.allow_negative_components);
     p.dist = 1;
     h.cand_local.Reserve(1);

@@ -18,6 +18,14 @@ def row_band(height: int, rank: int, world: int, align: int = 1) -> tuple[int, i
     return y0, y1
 
 
+def cyclic_rows(height: int, rank: int, world: int, block_rows: int) -> np.ndarray:
+    """Frame rows of rank `rank` under rdl_dist_set_row_blocks, in local storage order."""
+    if height % (block_rows * world):
+        raise ValueError("height must be a multiple of block_rows * world")
+    blocks = np.arange(rank, height // block_rows, world)
+    return (blocks[:, None] * block_rows + np.arange(block_rows)[None, :]).reshape(-1)
+
+
 def facets_of_rank(n_facets: int, rank: int, world: int) -> list[int]:
     """Round-robin facet ownership (ParallelDeconvolution runs its sub-images as independent
     ExecuteMajorIteration calls between two barriers, parallel_deconvolution.cc:582-617)."""

@@ -26,7 +26,10 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 dev = torch.device("cuda", local)
 ok = True
-for (n, c, iters, fit) in [(256, 1, 150, False), (192, 3, 120, False), (256, 4, 100, True)]:
+# (size, channels, iterations, spectral fit, cyclic block rows or 0 = contiguous bands)
+for (n, c, iters, fit, block) in [(256, 1, 150, False, 0), (192, 3, 120, False, 0),
+                                  (256, 4, 100, True, 0), (256, 2, 150, False, 16),
+                                  (192, 3, 100, True, 4)]:
     res, psfs, weights, freqs = hogbom_case(n, c)
     st = oracle.Settings(max_iterations=iters, clean_border_ratio=0.02, record_trace=True)
     if fit:
@@ -39,21 +42,26 @@ for (n, c, iters, fit) in [(256, 1, 150, False), (192, 3, 120, False), (256, 4, 
         alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, freqs, weights, 1)
     uid = rd.share_unique_id(rdl.dist_unique_id, rank, world, device=dev)
     alg.dist_init(uid, rank, world)
-    y0, y1 = rd.row_band(n, rank, world)
-    alg.dist_set_row_band(y0, n)
-    d_res = torch.from_numpy(np.ascontiguousarray(res[:, y0:y1])).to(dev)
+    if block:
+        rows = rd.cyclic_rows(n, rank, world, block)
+        alg.dist_set_row_blocks(block, n)
+    else:
+        y0, y1 = rd.row_band(n, rank, world)
+        rows = np.arange(y0, y1)
+        alg.dist_set_row_band(y0, n)
+    d_res = torch.from_numpy(np.ascontiguousarray(res[:, rows])).to(dev)
     d_model = torch.zeros_like(d_res)
-    g = alg.execute_major_iteration(rdl.Cube(n, y1 - y0, c, 1, weights), d_res, d_model,
+    g = alg.execute_major_iteration(rdl.Cube(n, len(rows), c, 1, weights), d_res, d_model,
                                     torch.from_numpy(psfs).to(dev))
     tr = alg.trace()
     good = (g.iteration_number == o.iteration_number and
             np.array_equal(tr["x"], o.trace["x"]) and np.array_equal(tr["y"], o.trace["y"]) and
             np.array_equal(tr["value"], o.trace["value"]) and
-            np.array_equal(d_res.cpu().numpy(), o_res[:, y0:y1]) and
-            np.array_equal(d_model.cpu().numpy(), o_model[:, y0:y1]) and
+            np.array_equal(d_res.cpu().numpy(), o_res[:, rows]) and
+            np.array_equal(d_model.cpu().numpy(), o_model[:, rows]) and
             g.final_peak_value == o.final_peak_value)
     if not good:
-        print(f"rank {rank}: MISMATCH case n={n} c={c} fit={fit}: iterations "
+        print(f"rank {rank}: MISMATCH case n={n} c={c} fit={fit} block={block}: iterations "
               f"{g.iteration_number} vs {o.iteration_number}", flush=True)
     ok = ok and good
     alg.dist_finalize()

@@ -96,6 +96,10 @@ def test_row_bands_partition_the_frame():
             assert bands[0][0] == 0 and bands[-1][1] == h
             assert all(a[1] == b[0] for a, b in zip(bands, bands[1:]))
     assert sorted(sum((facets_of_rank(64, r, 8) for r in range(8)), [])) == list(range(64))
+    from ska_sdp_func_radler_b200.distributed import cyclic_rows
+    allrows = np.concatenate([cyclic_rows(256, r, 4, 16) for r in range(4)])
+    assert sorted(allrows.tolist()) == list(range(256))
+    assert cyclic_rows(256, 1, 4, 16)[:17].tolist() == list(range(16, 32)) + [80]
 
 
 def test_peak_key_orders_like_the_reference_scan():
