@@ -1,0 +1,229 @@
+// Facet geometry of ParallelDeconvolution on the host (see facets.h for the reference lines).
+// Both orientations of the reference's splitter share one routine here, written in
+// (lateral, primary) coordinates: a vertical divider advances along y (primary) and wanders in
+// x (lateral); a horizontal one advances along x and wanders in y. The order in which
+// neighbours enter the priority queue is the reference's, because std::priority_queue breaks
+// equal-distance ties by insertion history and the chosen path must match pixel for pixel.
+#include "facets.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <queue>
+#include <stdexcept>
+#include <thread>
+
+namespace rdl {
+namespace {
+
+struct Step {
+  float distance;
+  uint32_t lat, prim;            // cell to visit
+  uint32_t from_lat, from_prim;  // cell we came from
+  bool operator<(const Step& rhs) const { return distance > rhs.distance; }  // min-heap
+};
+
+struct Axes {
+  size_t width;
+  bool vertical;
+  size_t operator()(size_t lat, size_t prim) const {
+    return vertical ? lat + prim * width : prim + lat * width;
+  }
+};
+
+void FillStrip(float* output, const Axes& at, size_t lo, size_t hi, size_t n_prim, float v) {
+  for (size_t prim = 0; prim != n_prim; ++prim)
+    for (size_t lat = lo; lat != hi; ++lat) output[at(lat, prim)] = v;
+}
+
+}  // namespace
+
+void DividingPath(const float* image, float* output, size_t width, size_t height, size_t lo,
+                  size_t hi, bool vertical) {
+  if (hi <= lo) throw std::invalid_argument("empty divider strip");
+  const Axes at{width, vertical};
+  const size_t n_prim = vertical ? height : width;
+  const size_t span = hi - lo;
+  std::priority_queue<Step> queue;
+  for (size_t lat = lo; lat != hi; ++lat)
+    queue.push(Step{0.0f, uint32_t(lat), 0u, uint32_t(lat), 0u});
+  std::vector<uint32_t> back_lat(span * n_prim), back_prim(span * n_prim);
+  FillStrip(output, at, lo, hi, n_prim, FLT_MAX);
+  Step s{};
+  while (!queue.empty()) {
+    s = queue.top();
+    queue.pop();
+    if (s.prim == n_prim) break;  // first path to leave the far edge is the cheapest
+    const size_t cell = at(s.lat, s.prim);
+    const float reached = s.distance + std::fabs(image[cell]);
+    if (reached < output[cell]) {
+      output[cell] = reached;
+      back_lat[(s.lat - lo) + s.prim * span] = s.from_lat;
+      back_prim[(s.lat - lo) + s.prim * span] = s.from_prim;
+      Step next{reached, 0u, 0u, s.lat, s.prim};
+      auto push = [&](uint32_t lat, uint32_t prim) {
+        next.lat = lat;
+        next.prim = prim;
+        queue.push(next);
+      };
+      if (s.lat > lo) {
+        push(s.lat - 1, s.prim + 1);
+        push(s.lat - 1, s.prim);
+      }
+      push(s.lat, s.prim + 1);
+      if (s.lat + 1 < hi) {
+        push(s.lat + 1, s.prim + 1);
+        push(s.lat + 1, s.prim);
+      }
+    }
+  }
+  FillStrip(output, at, lo, hi, n_prim, 0.0f);
+  uint32_t lat = s.from_lat, prim = s.from_prim;
+  while (prim > 0) {
+    output[at(lat, prim)] = 1.0f;
+    const size_t k = (lat - lo) + size_t(prim) * span;
+    lat = back_lat[k];
+    prim = back_prim[k];
+  }
+  output[at(lat, 0)] = 1.0f;
+}
+
+void FloodArea(const float* dividers, size_t width, size_t height, size_t inside, bool vertical,
+               uint8_t* mask, size_t& start, size_t& extent) {
+  const Axes at{width, vertical};
+  const long n_lat = long(vertical ? width : height);
+  const size_t n_prim = vertical ? height : width;
+  std::fill(mask, mask + width * height, uint8_t(0));
+  start = size_t(n_lat);
+  size_t end = 0;
+  for (size_t prim = 0; prim != n_prim; ++prim) {
+    long lat = long(inside);
+    // towards lower coordinates: the free area, then through the divider that bounds it
+    while (lat >= 0 && dividers[at(size_t(lat), prim)] == 0.0f) mask[at(size_t(lat--), prim)] = 1;
+    while (lat >= 0 && dividers[at(size_t(lat), prim)] != 0.0f) mask[at(size_t(lat--), prim)] = 1;
+    start = std::min(start, size_t(lat + 1));
+    // towards higher coordinates: up to (not including) the next divider
+    lat = long(inside) + 1;
+    while (lat < n_lat && dividers[at(size_t(lat), prim)] == 0.0f) mask[at(size_t(lat++), prim)] = 1;
+    end = std::max(end, size_t(lat));
+  }
+  extent = end < start ? 0 : end - start;
+}
+
+void BoundingMask(const uint8_t* vertical_mask, size_t vertical_mask_x, size_t vertical_mask_width,
+                  const uint8_t* horizontal_mask, uint8_t* mask, size_t width, size_t height,
+                  size_t& sub_x, size_t& sub_y, size_t& sub_width, size_t& sub_height) {
+  size_t x_lo = vertical_mask_x + vertical_mask_width, y_lo = height, x_hi = 0, y_hi = 0;
+  // like the reference, pixels of `mask` outside the vertical area's columns are left as they are
+  for (size_t y = 0; y != height; ++y) {
+    for (size_t x = 0; x != vertical_mask_width; ++x) {
+      const size_t fx = x + vertical_mask_x;
+      const bool in = vertical_mask[y * vertical_mask_width + x] && horizontal_mask[y * width + fx];
+      mask[y * width + fx] = in ? 1 : 0;
+      if (in) {
+        x_lo = std::min(x_lo, fx);
+        y_lo = std::min(y_lo, y);
+        x_hi = std::max(x_hi, fx);
+        y_hi = y;
+      }
+    }
+  }
+  sub_x = x_lo;
+  sub_y = y_lo;
+  if (x_hi < x_lo) {
+    sub_width = sub_height = 0;
+  } else {
+    sub_width = x_hi + 1 - x_lo;
+    sub_height = y_hi + 1 - y_lo;
+  }
+  // even frames keep even facets: grow by one masked-out column / row
+  if (width % 2 == 0 && sub_width % 2 != 0) {
+    ++sub_width;
+    size_t clear_x = sub_x + sub_width - 1;
+    if (sub_width + sub_x >= width) clear_x = --sub_x;
+    for (size_t y = sub_y; y != sub_y + sub_height; ++y) mask[clear_x + y * width] = 0;
+  }
+  if (height % 2 == 0 && sub_height % 2 != 0) {
+    ++sub_height;
+    size_t clear_y = sub_y + sub_height - 1;
+    if (sub_height + sub_y >= height) clear_y = --sub_y;
+    std::fill_n(mask + clear_y * width + sub_x, sub_width, uint8_t(0));
+  }
+}
+
+namespace {
+// aocommon::Image::TrimBox for byte masks
+void CropBox(uint8_t* dst, size_t x, size_t y, size_t w, size_t h, const uint8_t* src,
+             size_t src_width) {
+  for (size_t row = 0; row != h; ++row)
+    std::copy_n(src + (y + row) * src_width + x, w, dst + row * w);
+}
+
+template <typename F>
+void RunOnThreads(size_t begin, size_t end, F&& f) {
+  std::vector<std::thread> pool;
+  for (size_t i = begin; i < end; ++i) pool.emplace_back([&f, i] { f(i); });
+  for (std::thread& t : pool) t.join();
+}
+}  // namespace
+
+std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
+                              const uint8_t* user_mask, size_t grid_width, size_t grid_height) {
+  if (grid_width == 0 || grid_height == 0 || grid_width > width || grid_height > height)
+    throw std::invalid_argument("bad facet grid");
+  const size_t avg_w = width / grid_width, avg_h = height / grid_height;
+  std::vector<float> dividers(width * height, 0.0f);
+  std::vector<uint8_t> scratch_mask(width * height);
+
+  struct Column {
+    std::vector<uint8_t> mask;
+    size_t x = 0, width = 0;
+  };
+  std::vector<Column> columns(grid_width);
+  // vertical dividers: each searched inside the middle half of the strip between two facets;
+  // the strips are disjoint, so the dividers can be computed concurrently in one image
+  RunOnThreads(1, grid_width, [&](size_t d) {
+    const size_t mid = width * d / grid_width;
+    DividingPath(image, dividers.data(), width, height, mid - avg_w / 4, mid + avg_w / 4, true);
+  });
+  for (size_t d = 0; d != grid_width; ++d) {
+    Column& c = columns[d];
+    FloodArea(dividers.data(), width, height, d * width / grid_width + avg_w / 2, true,
+              scratch_mask.data(), c.x, c.width);
+    c.mask.resize(c.width * height);
+    CropBox(c.mask.data(), c.x, 0, c.width, height, scratch_mask.data(), width);
+  }
+  std::fill(dividers.begin(), dividers.end(), 0.0f);
+  RunOnThreads(1, grid_height, [&](size_t d) {
+    const size_t mid = height * d / grid_height;
+    DividingPath(image, dividers.data(), width, height, mid - avg_h / 4, mid + avg_h / 4, false);
+  });
+
+  std::vector<uint8_t> bounding(width * height);
+  std::vector<Facet> facets;
+  facets.reserve(grid_width * grid_height);
+  for (size_t gy = 0; gy != grid_height; ++gy) {
+    size_t row_y, row_h;
+    FloodArea(dividers.data(), width, height, gy * height / grid_height + avg_h / 2, false,
+              scratch_mask.data(), row_y, row_h);
+    for (size_t gx = 0; gx != grid_width; ++gx) {
+      Facet f;
+      f.index = facets.size();
+      const Column& c = columns[gx];
+      BoundingMask(c.mask.data(), c.x, c.width, scratch_mask.data(), bounding.data(), width,
+                   height, f.x, f.y, f.width, f.height);
+      f.mask.resize(f.width * f.height);
+      CropBox(f.mask.data(), f.x, f.y, f.width, f.height, bounding.data(), width);
+      f.boundary_mask = f.mask;
+      if (user_mask) {
+        for (size_t row = 0; row != f.height; ++row)
+          for (size_t col = 0; col != f.width; ++col)
+            f.mask[row * f.width + col] &= user_mask[(f.y + row) * width + f.x + col] ? 1 : 0;
+      }
+      facets.push_back(std::move(f));
+    }
+  }
+  return facets;
+}
+
+}  // namespace rdl
