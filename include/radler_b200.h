@@ -169,6 +169,50 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* cube,
                                        float* const* residual, float* const* model,
                                        const float* const* psfs, void* stream, rdl_result* out);
 
+/* ---- facets: ParallelDeconvolution::ExecuteMajorIteration ------------------------------------
+ * (cpp/algorithms/parallel_deconvolution.cc:494-654) over a grid_width x grid_height grid of
+ * sub-images (Settings::Parallel::grid_width/height, settings.h). The handle is the prototype
+ * algorithm (SetAlgorithm clones it once per facet; the clones and their iteration counters live
+ * in the handle across calls); its setters reach every facet like ParallelDeconvolution's
+ * (:244-292). Dividing paths are computed on the host from the integrated residual
+ * (math/dijkstra_splitter.cc), everything else runs on the device: per-facet trims, the
+ * peak-only pass, the common major-iteration threshold start_peak * (1 - mgain), deconvolution,
+ * divergence rollback, masked copy-back and model accumulation. A 1 x 1 grid is
+ * ExecuteSingleThreadedRun. Facets run in index order (the reference with one thread). */
+rdl_status rdl_parallel_execute_major_iteration(rdl_handle* h, uint64_t grid_width,
+                                                uint64_t grid_height, const rdl_cube_desc* cube,
+                                                float* const* residual, float* const* model,
+                                                const float* const* psfs, void* stream,
+                                                rdl_result* out);
+/* SubImage of the last facet run (parallel_deconvolution.h:22-35) */
+typedef struct {
+  uint64_t x, y, width, height;
+  double peak;
+  int32_t reached_major_threshold;
+  uint64_t iteration_number; /* of this facet's algorithm clone */
+} rdl_facet_info;
+uint64_t rdl_parallel_facet_count(const rdl_handle* h);
+/* boundary_mask (optional): width*height bytes, the pixels this facet owns */
+rdl_status rdl_parallel_facet_get(const rdl_handle* h, uint64_t i, rdl_facet_info* out,
+                                  uint8_t* boundary_mask);
+
+/* Facet geometry on the host (no device needed): radler::math::DijkstraSplitter
+ * (cpp/math/dijkstra_splitter.h:40-110) and MakeSubImages (parallel_deconvolution.cc:69-168).
+ * dividing_path = DivideVertically (vertical != 0; [lo,hi) are columns) / DivideHorizontally;
+ * flood_area = FloodVerticalArea / FloodHorizontalArea; bounding_mask = GetBoundingMask with
+ * box = {x, y, width, height}; facet_grid fills grid_width*grid_height boxes, row-major. */
+rdl_status rdl_facet_dividing_path(const float* image, float* output, uint64_t width,
+                                   uint64_t height, uint64_t lo, uint64_t hi, int32_t vertical);
+rdl_status rdl_facet_flood_area(const float* dividers, uint64_t width, uint64_t height,
+                                uint64_t inside, int32_t vertical, uint8_t* mask, uint64_t* start,
+                                uint64_t* extent);
+rdl_status rdl_facet_bounding_mask(const uint8_t* vertical_mask, uint64_t vertical_mask_x,
+                                   uint64_t vertical_mask_width, const uint8_t* horizontal_mask,
+                                   uint8_t* mask, uint64_t width, uint64_t height, uint64_t* box);
+rdl_status rdl_facet_grid(const float* image, uint64_t width, uint64_t height,
+                          const uint8_t* user_mask, uint64_t grid_width, uint64_t grid_height,
+                          rdl_facet_info* out);
+
 /* ---- kernel-level entry points (device pointers; used by tests and the roofline
  * harness, and what a host-side caller can compose itself) ------------------------ */
 

@@ -71,6 +71,12 @@ class _ScaleInfo(C.Structure):
                 ("n_components_cleaned", C.c_uint64), ("total_flux_cleaned", C.c_float)]
 
 
+class _FacetInfo(C.Structure):
+    _fields_ = [("x", C.c_uint64), ("y", C.c_uint64), ("width", C.c_uint64),
+                ("height", C.c_uint64), ("peak", C.c_double),
+                ("reached_major_threshold", C.c_int32), ("iteration_number", C.c_uint64)]
+
+
 TRACE_DTYPE = np.dtype([("iteration", "<u4"), ("scale", "<u4"), ("x", "<u4"), ("y", "<u4"),
                         ("value", "<f4")])
 
@@ -87,6 +93,8 @@ EXPORTED_SYMBOLS = [
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
+    "rdl_facet_dividing_path", "rdl_facet_flood_area", "rdl_facet_bounding_mask", "rdl_facet_grid",
     "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
     "rdl_dist_finalize",
     "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
@@ -151,6 +159,15 @@ def lib():
     L.rdl_multiscale_transform.argtypes = [vp, vp, u64, u64, u64, f32, i32, vp]
     L.rdl_good_fft_size.argtypes = [u64]
     L.rdl_good_fft_size.restype = u64
+    L.rdl_parallel_execute_major_iteration.argtypes = [vp, u64, u64, C.POINTER(_CubeDesc), vp, vp,
+                                                       vp, vp, C.POINTER(_Result)]
+    L.rdl_parallel_facet_count.argtypes = [vp]
+    L.rdl_parallel_facet_count.restype = u64
+    L.rdl_parallel_facet_get.argtypes = [vp, u64, C.POINTER(_FacetInfo), vp]
+    L.rdl_facet_dividing_path.argtypes = [vp, vp, u64, u64, u64, u64, i32]
+    L.rdl_facet_flood_area.argtypes = [vp, u64, u64, u64, i32, vp, C.POINTER(u64), C.POINTER(u64)]
+    L.rdl_facet_bounding_mask.argtypes = [vp, u64, u64, vp, vp, u64, u64, vp]
+    L.rdl_facet_grid.argtypes = [vp, u64, u64, vp, u64, u64, vp]
     L.rdl_dist_unique_id.argtypes = [vp]
     L.rdl_dist_init.argtypes = [vp, vp, i32, i32]
     L.rdl_dist_set_row_band.argtypes = [vp, u64, u64]
@@ -380,6 +397,37 @@ class DeconvolutionAlgorithm:
                       out.final_peak_value, bool(out.another_iteration_required),
                       bool(out.is_diverging), out.iteration_number)
 
+    # -- facets: ParallelDeconvolution (parallel_deconvolution.cc:494-654) ----------------
+    def parallel_execute_major_iteration(self, grid_width: int, grid_height: int, cube: Cube,
+                                         residual, model, psfs, stream=None) -> Result:
+        n = cube.width * cube.height
+        rt, s0 = _plane_pointers(residual, cube.n_images, n)
+        mt, s1 = _plane_pointers(model, cube.n_images, n)
+        pt, s2 = _plane_pointers(psfs, cube.n_channels, n)
+        if not (s0 == s1 == s2):
+            raise ValueError("residual, model and psfs must live in the same memory space")
+        d = cube.desc(s0)
+        out = _Result()
+        self._check(lib().rdl_parallel_execute_major_iteration(
+            self._h, grid_width, grid_height, C.byref(d), rt, mt, pt, stream, C.byref(out)))
+        return Result(out.starting_peak_value if out.has_starting_peak else None,
+                      out.final_peak_value, bool(out.another_iteration_required),
+                      bool(out.is_diverging), out.iteration_number)
+
+    def facets(self, with_masks: bool = False):
+        """SubImage records of the last facet run."""
+        out = []
+        for i in range(lib().rdl_parallel_facet_count(self._h)):
+            f = _FacetInfo()
+            self._check(lib().rdl_parallel_facet_get(self._h, i, C.byref(f), None))
+            rec = {k: getattr(f, k) for k, _ in _FacetInfo._fields_}
+            if with_masks:
+                m = np.zeros((f.height, f.width), np.uint8)
+                self._check(lib().rdl_parallel_facet_get(self._h, i, C.byref(f), m.ctypes.data))
+                rec["boundary_mask"] = m
+            out.append(rec)
+        return out
+
     # -- kernel-level entry points (device tensors) -----------------------------------
     def find_peak(self, cube: Cube, images, *, square=False, allow_negative=True, start_y=0,
                   end_y=None, h_border=0, v_border=0, mask=None, rms_factor=None, stream=None):
@@ -473,6 +521,51 @@ def GenericClean(use_sub_minor_optimization: bool = True, **kw) -> Deconvolution
 def MultiScaleAlgorithm(beam_size: float, pixel_scale: float = 1.0, **kw) -> DeconvolutionAlgorithm:
     """MultiScaleAlgorithm (cpp/algorithms/multiscale_algorithm.h)."""
     return DeconvolutionAlgorithm(MULTISCALE, beam_size=beam_size, pixel_scale=pixel_scale, **kw)
+
+
+# ---- facet geometry on the host (math/dijkstra_splitter.h; no GPU needed) ---------------------
+def _host_status(st):
+    if st != RDL_OK:
+        raise RadlerError(st, lib().rdl_last_error(None).decode())
+
+
+def facet_dividing_path(image, lo, hi, vertical=True):
+    img = np.ascontiguousarray(image, np.float32)
+    out = np.zeros_like(img)
+    _host_status(lib().rdl_facet_dividing_path(img.ctypes.data, out.ctypes.data, img.shape[1],
+                                               img.shape[0], lo, hi, int(vertical)))
+    return out
+
+
+def facet_flood_area(dividers, inside, vertical=True):
+    d = np.ascontiguousarray(dividers, np.float32)
+    mask = np.zeros(d.shape, np.uint8)
+    start, extent = C.c_uint64(), C.c_uint64()
+    _host_status(lib().rdl_facet_flood_area(d.ctypes.data, d.shape[1], d.shape[0], inside,
+                                            int(vertical), mask.ctypes.data, C.byref(start),
+                                            C.byref(extent)))
+    return mask, start.value, extent.value
+
+
+def facet_bounding_mask(vertical_mask, vertical_mask_x, horizontal_mask, mask=None):
+    v = np.ascontiguousarray(vertical_mask, np.uint8)
+    hm = np.ascontiguousarray(horizontal_mask, np.uint8)
+    mask = np.zeros(hm.shape, np.uint8) if mask is None else mask
+    box = (C.c_uint64 * 4)()
+    _host_status(lib().rdl_facet_bounding_mask(v.ctypes.data, vertical_mask_x, v.shape[1],
+                                               hm.ctypes.data, mask.ctypes.data, hm.shape[1],
+                                               hm.shape[0], box))
+    return mask, tuple(box)
+
+
+def facet_grid(image, grid_width, grid_height, user_mask=None):
+    img = np.ascontiguousarray(image, np.float32)
+    m = None if user_mask is None else np.ascontiguousarray(user_mask, np.uint8)
+    out = (_FacetInfo * (grid_width * grid_height))()
+    _host_status(lib().rdl_facet_grid(img.ctypes.data, img.shape[1], img.shape[0],
+                                      None if m is None else m.ctypes.data, grid_width,
+                                      grid_height, out))
+    return [(f.x, f.y, f.width, f.height) for f in out]
 
 
 def dist_unique_id() -> bytes:

@@ -7,6 +7,8 @@
 
 #include "fft.cuh"
 #include "iuwt.cuh"
+#include "facets.h"
+#include "parallel.cuh"
 #include "handle.h"
 #include "multiscale.cuh"
 
@@ -330,9 +332,11 @@ rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out) {
   });
 }
 
-rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
-                                       float* const* residual, float* const* model,
-                                       const float* const* psfs, void* stream_v, rdl_result* out) {
+namespace {
+// grid_width = 0: the algorithm itself; otherwise ParallelDeconvolution over a facet grid
+rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* residual,
+                       float* const* model, const float* const* psfs, void* stream_v,
+                       rdl_result* out, uint64_t grid_width, uint64_t grid_height) {
   if (!h || !out) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
     CheckCube(c);
@@ -384,12 +388,16 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
     }
     SetVec(cube);
     rdl_result r{};
+    if (grid_width != 0) {
+      r = RunParallel(*h, cube, grid_width, grid_height, stream);
+    } else {
     if (h->config.algorithm == RDL_GENERIC_CLEAN)
       r = RunGenericClean(*h, cube, stream);
     else if (h->config.algorithm == RDL_MULTISCALE)
       r = RunMultiScale(*h, cube, stream);
     else
       r = RunIuwt(*h, cube, stream);
+    }
     if (host) {
       for (size_t i = 0; i != cube.n_images; ++i) {
         RDL_CUDA(cudaMemcpyAsync(residual[i], cube.residual.p[i], bytes, cudaMemcpyDeviceToHost, stream));
@@ -398,6 +406,93 @@ rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
     }
     RDL_CUDA(cudaStreamSynchronize(stream));
     *out = r;
+  });
+}
+}  // namespace
+
+rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* c,
+                                       float* const* residual, float* const* model,
+                                       const float* const* psfs, void* stream_v, rdl_result* out) {
+  return ExecuteImpl(h, c, residual, model, psfs, stream_v, out, 0, 0);
+}
+
+rdl_status rdl_parallel_execute_major_iteration(rdl_handle* h, uint64_t grid_width,
+                                                uint64_t grid_height, const rdl_cube_desc* c,
+                                                float* const* residual, float* const* model,
+                                                const float* const* psfs, void* stream_v,
+                                                rdl_result* out) {
+  if (grid_width == 0 || grid_height == 0) return RDL_ERR_INVALID_ARGUMENT;
+  return ExecuteImpl(h, c, residual, model, psfs, stream_v, out, grid_width, grid_height);
+}
+
+// ---- facet geometry (host only; math/dijkstra_splitter.h) -----------------------------------
+rdl_status rdl_facet_dividing_path(const float* image, float* output, uint64_t width,
+                                   uint64_t height, uint64_t lo, uint64_t hi, int32_t vertical) {
+  if (!image || !output) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(nullptr, [&] { DividingPath(image, output, width, height, lo, hi, vertical != 0); });
+}
+
+rdl_status rdl_facet_flood_area(const float* dividers, uint64_t width, uint64_t height,
+                                uint64_t inside, int32_t vertical, uint8_t* mask, uint64_t* start,
+                                uint64_t* extent) {
+  if (!dividers || !mask || !start || !extent) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(nullptr, [&] {
+    size_t s = 0, e = 0;
+    FloodArea(dividers, width, height, inside, vertical != 0, mask, s, e);
+    *start = s;
+    *extent = e;
+  });
+}
+
+rdl_status rdl_facet_bounding_mask(const uint8_t* vertical_mask, uint64_t vertical_mask_x,
+                                   uint64_t vertical_mask_width, const uint8_t* horizontal_mask,
+                                   uint8_t* mask, uint64_t width, uint64_t height, uint64_t* box) {
+  if (!vertical_mask || !horizontal_mask || !mask || !box) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(nullptr, [&] {
+    size_t x, y, w, h;
+    BoundingMask(vertical_mask, vertical_mask_x, vertical_mask_width, horizontal_mask, mask, width,
+                 height, x, y, w, h);
+    box[0] = x;
+    box[1] = y;
+    box[2] = w;
+    box[3] = h;
+  });
+}
+
+rdl_status rdl_facet_grid(const float* image, uint64_t width, uint64_t height,
+                          const uint8_t* user_mask, uint64_t grid_width, uint64_t grid_height,
+                          rdl_facet_info* out) {
+  if (!image || !out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(nullptr, [&] {
+    const std::vector<Facet> f = MakeFacets(image, width, height, user_mask, grid_width, grid_height);
+    for (size_t i = 0; i != f.size(); ++i) {
+      out[i] = rdl_facet_info{};
+      out[i].x = f[i].x;
+      out[i].y = f[i].y;
+      out[i].width = f[i].width;
+      out[i].height = f[i].height;
+    }
+  });
+}
+
+uint64_t rdl_parallel_facet_count(const rdl_handle* h) { return h ? ParallelFacetCount(*h) : 0; }
+
+rdl_status rdl_parallel_facet_get(const rdl_handle* h, uint64_t i, rdl_facet_info* out,
+                                  uint8_t* boundary_mask) {
+  if (!h || !out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(const_cast<rdl_handle*>(h), [&] {
+    const FacetInfo f = ParallelFacet(*h, i);
+    out->x = f.x;
+    out->y = f.y;
+    out->width = f.width;
+    out->height = f.height;
+    out->peak = f.peak;
+    out->reached_major_threshold = f.reached_major_threshold;
+    out->iteration_number = f.iteration_number;
+    if (boundary_mask) {
+      const std::vector<uint8_t>& m = ParallelFacetBoundaryMask(*h, i);
+      std::copy(m.begin(), m.end(), boundary_mask);
+    }
   });
 }
 

@@ -105,6 +105,10 @@ struct Settings {  // deconvolution_algorithm.h:189-202
 
 class MultiScaleState;
 class FftConvolver;
+struct ParallelState;  // facets (parallel.cu)
+struct ParallelStateDeleter {
+  void operator()(ParallelState* p) const;
+};
 
 // Device buffers of the sub-minor loop (grow-only, reused between runs).
 struct SubMinorBuffers {
@@ -166,6 +170,8 @@ struct rdl_handle {
   rdl::DeviceBuffer<float> fft_scratch, small_kernel;
   rdl::DeviceBuffer<float2> fft_spectrum;
   rdl::DeviceBuffer<float> iuwt_a, iuwt_b;  // IUWT ping-pong planes
+  // facet run state: per-facet clones and geometry (not cloned)
+  std::unique_ptr<rdl::ParallelState, rdl::ParallelStateDeleter> parallel;
   // row-sharded multi-GPU loop (not cloned)
   rdl::DistContext dist;
   rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;

@@ -1,0 +1,285 @@
+// ParallelDeconvolution on the device (cpp/algorithms/parallel_deconvolution.cc):
+//   SetAlgorithm :227-242 (one clone per facet), RunSubImage :294-492 (trim, masked model trim,
+//   centre-cropped PSFs, peak-only probe, deconvolve, divergence rollback, masked copy-back,
+//   model add), ExecuteParallelRun :548-654 (two passes, global start peak, major-iteration
+//   threshold, result bookkeeping). The facet geometry is computed on the host (facets.cc);
+//   every pixel operation — trims, masked copies, model accumulation and the per-facet
+//   ExecuteMajorIteration — runs on the device, so the cube never leaves HBM.
+// Facets run one after the other on the handle's stream, in index order: the reference's result
+// depends on the order in which facets copy their residual back (a facet's bounding box overlaps
+// its neighbours' pixels); index order is what the reference does with one thread.
+#include "parallel.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <stdexcept>
+
+#include "clean_kernels.cuh"
+#include "facets.h"
+
+namespace rdl {
+namespace {
+
+constexpr int kThreads = 256;
+
+// dst (w x h) = src box at (x, y), zeroed where mask == 0  (ImageSet::TrimMasked, image_set.h:230)
+__global__ void TrimMaskedKernel(float* dst, const float* src, size_t src_width, size_t x, size_t y,
+                                 size_t w, size_t h, const uint8_t* mask) {
+  const size_t n = w * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t row = i / w, col = i - row * w;
+    dst[i] = (mask == nullptr || mask[i]) ? src[(y + row) * src_width + x + col] : 0.0f;
+  }
+}
+
+// frame box at (x, y) = sub where mask (Image::CopyMasked) / += sub (Image::AddSubImage)
+template <bool ADD>
+__global__ void PlaceKernel(float* frame, size_t frame_width, size_t x, size_t y, const float* sub,
+                            size_t w, size_t h, const uint8_t* mask) {
+  const size_t n = w * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t row = i / w, col = i - row * w;
+    float* d = frame + (y + row) * frame_width + x + col;
+    if (ADD)
+      *d = __fadd_rn(*d, sub[i]);
+    else if (mask[i])
+      *d = sub[i];
+  }
+}
+
+int GridFor(size_t n) { return int(std::min<size_t>((n + kThreads - 1) / kThreads, kSmCount * 8)); }
+
+}  // namespace
+
+struct ParallelState {
+  size_t grid_width = 0, grid_height = 0;
+  std::vector<rdl_handle*> algorithms;  // one clone per facet
+  std::vector<Facet> facets;            // geometry + results of the last call
+  DeviceBuffer<float> integrated, result_model, sub_residual, sub_model, sub_model_start, sub_psf;
+  DeviceBuffer<uint8_t> boundary_mask;
+  ~ParallelState() {
+    for (rdl_handle* a : algorithms) rdl_destroy(a);
+  }
+};
+
+void ParallelStateDeleter::operator()(ParallelState* p) const { delete p; }
+
+namespace {
+
+void EnsureAlgorithms(rdl_handle& h, ParallelState& st, size_t n) {
+  if (st.algorithms.size() == n) return;
+  for (rdl_handle* a : st.algorithms) rdl_destroy(a);
+  st.algorithms.clear();
+  for (size_t i = 0; i != n; ++i) {  // SetAlgorithm: algorithms_[i] = front()->Clone()
+    rdl_handle* c = nullptr;
+    if (rdl_clone(&h, &c) != RDL_OK) throw std::runtime_error("cloning the facet algorithm failed");
+    st.algorithms.push_back(c);
+  }
+}
+
+rdl_result RunAlgorithm(rdl_handle& a, DeviceCube& cube, cudaStream_t stream) {
+  switch (a.config.algorithm) {
+    case RDL_GENERIC_CLEAN: return RunGenericClean(a, cube, stream);
+    case RDL_MULTISCALE: return RunMultiScale(a, cube, stream);
+    default: return RunIuwt(a, cube, stream);
+  }
+}
+
+// RunSubImage (parallel_deconvolution.cc:294-492) for one facet.
+void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
+              double major_iteration_threshold, bool find_peak_only, cudaStream_t stream) {
+  rdl_handle& a = *st.algorithms[f.index];
+  const size_t W = cube.width, w = f.width, fh = f.height, n = w * fh;
+  st.sub_residual.Reserve(cube.n_images * n);
+  st.sub_model.Reserve(cube.n_images * n);
+  st.sub_model_start.Reserve(cube.n_images * n);
+  st.sub_psf.Reserve(cube.n_channels * n);
+  st.boundary_mask.Reserve(n);
+  RDL_CUDA(cudaMemcpyAsync(st.boundary_mask.get(), f.boundary_mask.data(), n, cudaMemcpyHostToDevice,
+                           stream));
+  DeviceCube sub = cube;
+  sub.width = w;
+  sub.height = fh;
+  for (size_t i = 0; i != cube.n_images; ++i) {
+    sub.residual.p[i] = st.sub_residual.get() + i * n;
+    sub.model.p[i] = st.sub_model.get() + i * n;
+    // data_image.Trim(...)
+    RDL_CUDA(cudaMemcpy2DAsync(sub.residual.p[i], w * sizeof(float),
+                               cube.residual.p[i] + f.y * W + f.x, W * sizeof(float),
+                               w * sizeof(float), fh, cudaMemcpyDeviceToDevice, stream));
+    // model_image.TrimMasked(..., boundary_mask): pixels other facets own start at zero
+    TrimMaskedKernel<<<GridFor(n), kThreads, 0, stream>>>(sub.model.p[i], cube.model.p[i], W, f.x,
+                                                          f.y, w, fh, st.boundary_mask.get());
+    ++h.launches;
+  }
+  // the model as it was, to undo a diverging facet
+  RDL_CUDA(cudaMemcpyAsync(st.sub_model_start.get(), st.sub_model.get(),
+                           cube.n_images * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  // psf_image.Resize(sub width, sub height): centred crop (a facet is never larger than the frame)
+  const size_t px = (W - w) / 2, py = (cube.height - fh) / 2;
+  for (size_t c = 0; c != cube.n_channels; ++c) {
+    float* dst = st.sub_psf.get() + c * n;
+    RDL_CUDA(cudaMemcpy2DAsync(dst, w * sizeof(float), cube.psf.p[c] + py * W + px,
+                               W * sizeof(float), w * sizeof(float), fh, cudaMemcpyDeviceToDevice,
+                               stream));
+    sub.psf.p[c] = dst;
+  }
+  sub.vec = (w % 4 == 0) ? 4 : 1;  // the sub buffers are cudaMalloc-aligned, planes are n floats
+  if ((n % 4) != 0) sub.vec = 1;
+
+  if (rdl_set_clean_mask(&a, f.mask.data(), w, fh) != RDL_OK) throw std::runtime_error(a.error);
+  if (!h.rms_host.empty()) {  // rms_image_.TrimBox(...)
+    std::vector<float> crop(n);
+    for (size_t row = 0; row != fh; ++row)
+      std::copy_n(h.rms_host.data() + (f.y + row) * W + f.x, w, crop.data() + row * w);
+    if (rdl_set_rms_factor_image(&a, crop.data(), w, fh) != RDL_OK) throw std::runtime_error(a.error);
+  }
+  const uint64_t max_iterations = a.settings.max_iterations;
+  if (find_peak_only)
+    a.settings.max_iterations = 0;
+  else
+    a.settings.major_iteration_threshold = float(major_iteration_threshold);
+
+  const double peak_at_start = std::fabs(f.peak);
+  const rdl_result r = RunAlgorithm(a, sub, stream);
+  h.launches += a.launches;
+  a.launches = 0;
+  f.peak = r.final_peak_value;
+  f.reached_major_threshold = r.another_iteration_required != 0;
+  const double limit = h.settings.divergence_limit;
+  const bool converging = (limit == 0.0 || std::fabs(f.peak) <= peak_at_start * limit) &&
+                          std::isfinite(f.peak) && !r.is_diverging;
+  if (!converging && !find_peak_only) f.reached_major_threshold = false;
+  if (!h.rms_host.empty()) rdl_set_rms_factor_image(&a, nullptr, 0, 0);
+
+  if (find_peak_only) {
+    a.settings.max_iterations = max_iterations;
+    return;
+  }
+  for (size_t i = 0; i != cube.n_images; ++i) {
+    if (converging) {
+      // data_image.CopyMasked(*sub_data, x, y, boundary_mask)
+      PlaceKernel<false><<<GridFor(n), kThreads, 0, stream>>>(
+          cube.residual.p[i], W, f.x, f.y, sub.residual.p[i], w, fh, st.boundary_mask.get());
+      ++h.launches;
+    }
+    // result_model.AddSubImage(*sub_model, x, y); a diverged facet contributes its old model
+    const float* m = converging ? sub.model.p[i] : st.sub_model_start.get() + i * n;
+    PlaceKernel<true><<<GridFor(n), kThreads, 0, stream>>>(
+        st.result_model.get() + i * cube.Pixels(), W, f.x, f.y, m, w, fh, nullptr);
+    ++h.launches;
+  }
+  RDL_CUDA(cudaGetLastError());
+}
+
+}  // namespace
+
+rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_t grid_height,
+                       cudaStream_t stream) {
+  if (grid_width == 0 || grid_height == 0) throw std::invalid_argument("empty facet grid");
+  if (h.dist.band_set) throw std::domain_error("facets of a row-sharded cube are not supported");
+  if (!h.parallel) h.parallel.reset(new ParallelState);
+  ParallelState& st = *h.parallel;
+  const size_t n_facets = grid_width * grid_height;
+  if (st.grid_width != grid_width || st.grid_height != grid_height) {
+    for (rdl_handle* a : st.algorithms) rdl_destroy(a);
+    st.algorithms.clear();
+    st.grid_width = grid_width;
+    st.grid_height = grid_height;
+  }
+  EnsureAlgorithms(h, st, n_facets);
+  // ParallelDeconvolution::SetThreshold / SetMinorLoopGain / SetAutoMaskMode / ... reach every
+  // facet algorithm (parallel_deconvolution.cc:244-292); the iteration counters stay per facet
+  for (rdl_handle* a : st.algorithms) {
+    a->settings = h.settings;
+    a->track_per_scale_masks = h.track_per_scale_masks;
+    a->use_per_scale_masks = h.use_per_scale_masks;
+    a->trace_capacity = 0;
+  }
+  if (n_facets == 1) {
+    // ExecuteSingleThreadedRun (:505-546): the algorithm on the whole frame, user mask and all
+    rdl_handle& a = *st.algorithms.front();
+    if (!h.mask_host.empty()) rdl_set_clean_mask(&a, h.mask_host.data(), h.mask_w, h.mask_h);
+    const rdl_result r = RunAlgorithm(a, cube, stream);
+    h.launches += a.launches;
+    a.launches = 0;
+    h.iteration_number = a.iteration_number;
+    st.facets.assign(1, Facet{});
+    st.facets[0].width = cube.width;
+    st.facets[0].height = cube.height;
+    st.facets[0].peak = r.final_peak_value;
+    return r;
+  }
+  if (h.track_per_scale_masks || h.use_per_scale_masks)
+    throw std::domain_error("per-scale masks under facets are not supported yet");
+
+  const size_t W = cube.width, H = cube.height, A = cube.Pixels();
+  // image = data_image.GetLinearIntegrated(); the dividers follow its minimum-power paths
+  st.integrated.Reserve(A);
+  const IntegSpec spec = MakeLinearSpec(cube);
+  LaunchIntegrate(spec, reinterpret_cast<const ConstPtrTable&>(cube.residual), A,
+                  st.integrated.get(), cube.vec, stream);
+  ++h.launches;
+  std::vector<float> integrated(A);
+  RDL_CUDA(cudaMemcpyAsync(integrated.data(), st.integrated.get(), A * sizeof(float),
+                           cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+  st.facets = MakeFacets(integrated.data(), W, H,
+                         h.mask_host.empty() ? nullptr : h.mask_host.data(), grid_width,
+                         grid_height);
+  std::vector<float>().swap(integrated);
+
+  st.result_model.Reserve(cube.n_images * A);
+  RDL_CUDA(cudaMemsetAsync(st.result_model.get(), 0, cube.n_images * A * sizeof(float), stream));
+  // pass 1: every facet reports its peak (max_iterations = 0)
+  for (Facet& f : st.facets) RunFacet(h, st, f, cube, 0.0, true, stream);
+  double start_peak = 0.0;
+  for (const Facet& f : st.facets)
+    if (f.peak > start_peak) start_peak = f.peak;  // signed, like the reference (:592-599)
+  const double threshold = start_peak * (1.0 - double(h.settings.major_loop_gain));
+  // pass 2: deconvolve every facet down to the common major-iteration threshold
+  for (Facet& f : st.facets) RunFacet(h, st, f, cube, threshold, false, stream);
+  // model_image.SetImages(resultModel)
+  for (size_t i = 0; i != cube.n_images; ++i)
+    RDL_CUDA(cudaMemcpyAsync(cube.model.p[i], st.result_model.get() + i * A, A * sizeof(float),
+                             cudaMemcpyDeviceToDevice, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+
+  size_t finished = 0;
+  bool reached_max_iterations = false;
+  double end_peak = 0.0;
+  for (const Facet& f : st.facets) {
+    if (!f.reached_major_threshold) ++finished;
+    const rdl_handle& a = *st.algorithms[f.index];
+    if (a.iteration_number >= a.settings.max_iterations) reached_max_iterations = true;
+    end_peak = std::max(end_peak, f.peak);
+  }
+  rdl_result r{};
+  r.has_starting_peak = 1;
+  r.starting_peak_value = float(start_peak);
+  r.final_peak_value = float(end_peak);
+  r.another_iteration_required = (finished != st.facets.size()) && !reached_max_iterations;
+  r.is_diverging = 0;
+  h.iteration_number = st.algorithms.front()->iteration_number;
+  r.iteration_number = h.iteration_number;
+  return r;
+}
+
+size_t ParallelFacetCount(const rdl_handle& h) { return h.parallel ? h.parallel->facets.size() : 0; }
+
+FacetInfo ParallelFacet(const rdl_handle& h, size_t i) {
+  if (!h.parallel || i >= h.parallel->facets.size()) throw std::invalid_argument("no such facet");
+  const Facet& f = h.parallel->facets[i];
+  const uint64_t it =
+      i < h.parallel->algorithms.size() ? h.parallel->algorithms[i]->iteration_number : 0;
+  return FacetInfo{f.x, f.y, f.width, f.height, f.peak, f.reached_major_threshold ? 1 : 0, it};
+}
+
+const std::vector<uint8_t>& ParallelFacetBoundaryMask(const rdl_handle& h, size_t i) {
+  if (!h.parallel || i >= h.parallel->facets.size()) throw std::invalid_argument("no such facet");
+  return h.parallel->facets[i].boundary_mask;
+}
+
+}  // namespace rdl
