@@ -1,0 +1,73 @@
+"""GPU parity of ParallelDeconvolution over a facet grid (csrc/parallel.cu) against the
+reference's OWN parallel_deconvolution.cc + generic_clean.cc (oracle/_ref, one thread so that
+the facet order is defined): facet boxes, per-call result, residual and model."""
+import numpy as np
+import pytest
+
+from helpers import hogbom_case
+
+pytestmark = pytest.mark.gpu
+
+
+def run_reference(oracle, res, psfs, weights, grid, sub_minor, calls=2, **kw):
+    c, n, _ = res.shape
+    ref = oracle.Reference("generic", n, n, c, weights=weights, use_sub_minor_optimization=sub_minor,
+                           grid=grid, threads=1, **kw)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    out = [ref.execute(r_res, r_model, psfs) for _ in range(calls)]
+    return out, r_res, r_model
+
+
+@pytest.mark.parametrize("n,c,grid,sub_minor", [(128, 1, (2, 2), False), (192, 2, (3, 2), False),
+                                                (128, 1, (2, 2), True), (160, 1, (1, 1), False)])
+def test_facet_run_matches_reference_sources(rdl, oracle, torch_cuda, n, c, grid, sub_minor):
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    res, psfs, weights, _ = hogbom_case(n, c)
+    kw = dict(max_iterations=150, minor_loop_gain=0.1, major_loop_gain=0.7, clean_border_ratio=0.0)
+    want, r_res, r_model = run_reference(oracle, res, psfs, weights, grid, sub_minor, **kw)
+    alg = rdl.GenericClean(use_sub_minor_optimization=sub_minor)
+    alg.apply(max_iterations=150, minor_loop_gain=0.1, major_loop_gain=0.7, clean_border_ratio=0.0)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, n, n), device="cuda")
+    d_psf = torch.from_numpy(psfs).cuda()
+    cube = rdl.Cube(n, n, c, 1, weights)
+    for call, w in enumerate(want):
+        g = alg.parallel_execute_major_iteration(grid[0], grid[1], cube, d_res, d_model, d_psf)
+        assert g.another_iteration_required == w.another_iteration_required, call
+        assert np.float32(g.final_peak_value) == np.float32(w.final_peak_value), call
+        if w.starting_peak_value is not None:
+            assert np.float32(g.starting_peak_value) == np.float32(w.starting_peak_value), call
+    facets = alg.facets(with_masks=True)
+    assert len(facets) == grid[0] * grid[1]
+    owned = np.zeros((n, n), np.int32)
+    for f in facets:
+        if "boundary_mask" in f and grid != (1, 1):
+            owned[f["y"]:f["y"] + f["height"], f["x"]:f["x"] + f["width"]] += f["boundary_mask"]
+    if grid != (1, 1):
+        assert (owned == 1).all()  # every pixel belongs to exactly one facet
+    tol = 1e-5 * np.abs(r_res).max() if sub_minor else 0.0  # path A goes through FFTs
+    assert np.abs(d_res.cpu().numpy() - r_res).max() <= tol
+    assert np.abs(d_model.cpu().numpy() - r_model).max() <= (1e-5 * max(np.abs(r_model).max(), 1e-30) if sub_minor else 0.0)
+
+
+def test_facet_run_with_host_buffers_and_mask(rdl, oracle, torch_cuda):
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, c, grid = 128, 1, (2, 2)
+    res, psfs, weights, _ = hogbom_case(n, c)
+    mask = np.zeros((n, n), np.uint8)
+    mask[10:100, 20:120] = 1
+    c_, n_ = res.shape[0], n
+    ref = oracle.Reference("generic", n, n, c, weights=weights, use_sub_minor_optimization=False,
+                           grid=grid, threads=1, max_iterations=100, major_loop_gain=0.8)
+    ref.set_clean_mask(mask)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    w = ref.execute(r_res, r_model, psfs)
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    alg.apply(max_iterations=100, major_loop_gain=0.8, clean_border_ratio=0.0)
+    alg.set_clean_mask(mask)
+    g_res, g_model = res.copy(), np.zeros_like(res)
+    g = alg.parallel_execute_major_iteration(2, 2, rdl.Cube(n, n, c, 1, weights), g_res, g_model, psfs)
+    assert g.another_iteration_required == w.another_iteration_required
+    assert np.array_equal(g_res, r_res) and np.array_equal(g_model, r_model)
