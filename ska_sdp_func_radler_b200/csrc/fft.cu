@@ -4,17 +4,22 @@
 //
 //   out = irfft2( rfft2(in) * rfft2(kernel) ) / (W*H)          (circular, in place)
 //
-// Three HBM passes per convolution, every 1-D transform done entirely in shared memory:
-//   RowForwardKernel   real rows -> half spectrum   (R2C through a length-W/2 complex FFT)
-//   ColumnKernel       column FFT, * kernel spectrum, inverse column FFT   (one pass)
-//   RowInverseKernel   half spectrum -> real rows, fused with the caller's epilogue
+// Every 1-D transform is done entirely in shared memory:
+//   RowForwardKernel      real rows -> half spectrum (R2C through a length-W/2 complex FFT)
+//   ColumnStridedKernel   four-step column transform, step 1: H2-point transforms over rows at
+//                         stride H1 + step twiddles, on 16-column (128-byte) tiles
+//   ColumnBlockKernel     step 2 on H1 contiguous rows: forward FFT, * kernel spectrum, inverse
+//                         FFT in one pass (the whole column transform when H <= 512)
+//   ColumnStridedKernel   step 1 undone (inverse)
+//   RowInverseKernel      half spectrum -> real rows, fused with the caller's epilogue
 //                      (store / residual -= result / model += result) and with the
 //                      reference's Untrim/Trim (centred zero-pad and crop).
 // The 1-D transforms are in-place decimation-in-frequency forward and decimation-in-time
 // inverse passes (radix 8/4/2/3/5/7, generic prime radix <= 127), so no bit-reversal pass is
 // ever needed: the column spectra stay in digit-reversed order (the kernel spectrum is
 // produced by the same forward pass), only the row split step looks frequencies up through a
-// small permutation table. Algorithmic HBM traffic: 28 bytes per padded pixel.
+// small permutation table. Algorithmic HBM traffic: 28 bytes per padded pixel;
+// the four-step column transform moves 44.
 // Results are not bit-comparable with FFTW or the CPU checker; parity is by tolerance.
 #include "fft.cuh"
 
@@ -323,12 +328,12 @@ __device__ __forceinline__ void TileStage(float2* s, int n, int L, const float2*
     for (int q = 0; q < R; ++q) v[q] = p[q * m * TC];
     if (INV && m > 1) {
 #pragma unroll
-      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], Conj(__ldg(tw + j * q * tw_step)));
+      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], Conj(tw[j * q * tw_step]));
     }
     Dft<R, INV>::Run(v);
     if (!INV && m > 1) {
 #pragma unroll
-      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], __ldg(tw + j * q * tw_step));
+      for (int q = 1; q < R; ++q) v[q] = CMul(v[q], tw[j * q * tw_step]);
     }
 #pragma unroll
     for (int q = 0; q < R; ++q) p[q * m * TC] = v[q];
@@ -348,7 +353,7 @@ __device__ void TileGenericStage(float2* s, int n, int L, int p, const float2* _
     float2 x[kMaxGenericRadix];
     for (int q = 0; q < p; ++q) {
       float2 v = ptr[q * m * TC];
-      if (INV && m > 1) v = CMul(v, Conj(__ldg(tw + j * q * tw_step)));
+      if (INV && m > 1) v = CMul(v, Conj(tw[j * q * tw_step]));
       x[q] = v;
     }
     for (int q = 0; q < p; ++q) {
@@ -357,11 +362,11 @@ __device__ void TileGenericStage(float2* s, int n, int L, int p, const float2* _
       for (int k = 1; k < p; ++k) {
         idx += q;
         if (idx >= p) idx -= p;
-        float2 r = __ldg(tw + idx * root_step);
+        float2 r = tw[idx * root_step];
         if (INV) r.y = -r.y;
         acc = acc + CMul(x[k], r);
       }
-      if (!INV && m > 1) acc = CMul(acc, __ldg(tw + j * q * tw_step));
+      if (!INV && m > 1) acc = CMul(acc, tw[j * q * tw_step]);
       ptr[q * m * TC] = acc;
     }
   }
@@ -369,22 +374,27 @@ __device__ void TileGenericStage(float2* s, int n, int L, int p, const float2* _
 
 // Forward: natural order in, digit-reversed out; inverse the other way. Leaves the block
 // synchronised.
+// `tw`: the plan's twiddle table, staged in shared memory by the caller (n entries).
 template <bool INV, int TC>
-__device__ __forceinline__ void RunTileFft(float2* s, const Plan& plan) {
+__device__ __forceinline__ void RunTileFft(float2* s, const Plan& plan, const float2* tw) {
   for (int k = 0; k < plan.n_stages; ++k) {
     const int st = INV ? plan.n_stages - 1 - k : k;
     const int n = plan.n, L = plan.len[st];
     switch (plan.radix[st]) {
-      case 8: TileStage<8, INV, TC>(s, n, L, plan.tw); break;
-      case 4: TileStage<4, INV, TC>(s, n, L, plan.tw); break;
-      case 2: TileStage<2, INV, TC>(s, n, L, plan.tw); break;
-      case 3: TileStage<3, INV, TC>(s, n, L, plan.tw); break;
-      case 5: TileStage<5, INV, TC>(s, n, L, plan.tw); break;
-      case 7: TileStage<7, INV, TC>(s, n, L, plan.tw); break;
-      default: TileGenericStage<INV, TC>(s, n, L, plan.radix[st], plan.tw); break;
+      case 8: TileStage<8, INV, TC>(s, n, L, tw); break;
+      case 4: TileStage<4, INV, TC>(s, n, L, tw); break;
+      case 2: TileStage<2, INV, TC>(s, n, L, tw); break;
+      case 3: TileStage<3, INV, TC>(s, n, L, tw); break;
+      case 5: TileStage<5, INV, TC>(s, n, L, tw); break;
+      case 7: TileStage<7, INV, TC>(s, n, L, tw); break;
+      default: TileGenericStage<INV, TC>(s, n, L, plan.radix[st], tw); break;
     }
     __syncthreads();
   }
+}
+
+__device__ __forceinline__ void StageTwiddles(float2* dst, const Plan& plan) {
+  for (int i = threadIdx.x; i < plan.n; i += blockDim.x) dst[i] = __ldg(plan.tw + i);
 }
 
 struct RowParams {
@@ -409,13 +419,26 @@ __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant
   const int n = p.plan.n;
   const int row0 = blockIdx.x * p.rows_per_cta;
   const int n_seq = min(p.rows_per_cta, p.sh - row0);
+  // 128-bit loads when the row, its offset in the frame and the source are 16-byte aligned
+  const bool vec = ((p.ox | p.sw | p.W) & 3) == 0 && (reinterpret_cast<uintptr_t>(p.src) & 15) == 0;
   for (int c = 0; c < n_seq; ++c) {
-    float* s = reinterpret_cast<float*>(smem + c * p.seq_stride);
     const float* src = p.src + size_t(row0 + c) * p.sw;
-    for (int x = threadIdx.x; x < p.W; x += blockDim.x) {
-      const int xs = x - p.ox;
-      const float v = (xs >= 0 && xs < p.sw) ? __ldg(src + xs) : 0.0f;
-      s[2 * Pad(x >> 1) + (x & 1)] = v;
+    if (vec) {
+      float2* s2 = smem + c * p.seq_stride;
+      for (int x = 4 * threadIdx.x; x < p.W; x += 4 * blockDim.x) {
+        const int xs = x - p.ox;
+        const float4 v = (xs >= 0 && xs < p.sw) ? __ldg(reinterpret_cast<const float4*>(src + xs))
+                                                : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        s2[Pad(x >> 1)] = make_float2(v.x, v.y);
+        s2[Pad((x >> 1) + 1)] = make_float2(v.z, v.w);
+      }
+    } else {
+      float* s = reinterpret_cast<float*>(smem + c * p.seq_stride);
+      for (int x = threadIdx.x; x < p.W; x += blockDim.x) {
+        const int xs = x - p.ox;
+        const float v = (xs >= 0 && xs < p.sw) ? __ldg(src + xs) : 0.0f;
+        s[2 * Pad(x >> 1) + (x & 1)] = v;
+      }
     }
   }
   __syncthreads();
@@ -454,9 +477,26 @@ __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant
   }
   __syncthreads();
   RunFft<true>(smem, n_seq, p.seq_stride, p.plan);
+  const bool vec = ((p.ox | p.sw) & 3) == 0 && (reinterpret_cast<uintptr_t>(p.dst) & 15) == 0;
   for (int c = 0; c < n_seq; ++c) {
     const float* s = reinterpret_cast<const float*>(smem + c * p.seq_stride);
     float* dst = p.dst + size_t(row0 + c) * p.sw;
+    if (vec) {
+      const float2* s2 = smem + c * p.seq_stride;
+      for (int xs = 4 * threadIdx.x; xs < p.sw; xs += 4 * blockDim.x) {
+        const int x = xs + p.ox;
+        const float2 a = s2[Pad(x >> 1)], b = s2[Pad((x >> 1) + 1)];
+        float4* d4 = reinterpret_cast<float4*>(dst + xs);
+        float4 v = make_float4(a.x, a.y, b.x, b.y);
+        if (p.mode != 0) {
+          const float4 o = *d4;
+          v = p.mode == 1 ? make_float4(o.x - v.x, o.y - v.y, o.z - v.z, o.w - v.w)
+                          : make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w);
+        }
+        *d4 = v;
+      }
+      continue;
+    }
     for (int xs = threadIdx.x; xs < p.sw; xs += blockDim.x) {
       const int x = xs + p.ox;
       const float v = s[2 * Pad(x >> 1) + (x & 1)];
@@ -499,6 +539,8 @@ __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant
   const int H1 = p.H1, H2 = p.H2;
   float2* base = p.spec + size_t(r) * p.pitch + c0;
   const size_t step = size_t(H1) * p.pitch;
+  float2* tw = smem + H2 * TC;
+  StageTwiddles(tw, p.plan2);
   for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
     const int j = i / TC, c = i - j * TC;
     float2 v;
@@ -511,7 +553,7 @@ __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant
     smem[i] = v;
   }
   __syncthreads();
-  RunTileFft<INV, TC>(smem, p.plan2);
+  RunTileFft<INV, TC>(smem, p.plan2, tw);
   for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
     const int j = i / TC, c = i - j * TC;
     if (!INV) {
@@ -534,13 +576,15 @@ __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__
   const size_t row0 = size_t(blockIdx.y) * H1;
   float2* base = p.spec + row0 * p.pitch + c0;
   const bool whole = p.H2 == 1;
+  float2* tw = smem + H1 * TC;
+  StageTwiddles(tw, p.plan1);
   for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
     const int y = i / TC, c = i - y * TC;
     smem[i] = (!whole || (y >= p.y0 && y < p.y1)) ? base[size_t(y) * p.pitch + c]
                                                     : make_float2(0.0f, 0.0f);
   }
   __syncthreads();
-  RunTileFft<false, TC>(smem, p.plan1);
+  RunTileFft<false, TC>(smem, p.plan1, tw);
   if (!CONVOLVE) {
     float2* out = p.kspec_out + row0 * p.pitch + c0;
     for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
@@ -555,7 +599,7 @@ __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__
     smem[i] = CMul(smem[i], __ldg(k + size_t(y) * p.pitch + c));
   }
   __syncthreads();
-  RunTileFft<true, TC>(smem, p.plan1);
+  RunTileFft<true, TC>(smem, p.plan1, tw);
   for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
     const int y = i / TC, c = i - y * TC;
     if (!whole || (y >= p.out_y0 && y < p.out_y1)) base[size_t(y) * p.pitch + c] = smem[i];
@@ -720,7 +764,7 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     d.row_stride = PaddedLength(d.n);
     const size_t row_bytes = size_t(d.row_stride) * sizeof(float2);
     if (row_bytes > kMaxSmemBytes) throw std::domain_error("image row does not fit in shared memory");
-    d.rows_per_cta = int(std::clamp<size_t>(size_t(56 * 1024) / row_bytes, 1, 8));
+    d.rows_per_cta = int(std::clamp<size_t>(size_t(75 * 1024) / row_bytes, 1, 8));
     d.row_smem = row_bytes * d.rows_per_cta;
     d.row_threads = d.n * d.rows_per_cta >= 4096 ? 256 : 128;
 
@@ -737,7 +781,7 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
       d.H2 = best;
       d.H1 = d.H / best;
     }
-    if (size_t(d.H1) * tile_row_bytes > kMaxSmemBytes)
+    if (size_t(d.H1) * (tile_row_bytes + sizeof(float2)) > kMaxSmemBytes)
       throw std::domain_error("image height " + std::to_string(d.H) +
                               " has no factorisation that fits in shared memory");
     d.col1.Build(d.H1);
@@ -746,8 +790,9 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     for (int k = 0; k < d.H2; ++k) freq2[d.col2.Slot(uint32_t(k))] = uint32_t(k);
     d.freq2.Resize(d.H2);
     RDL_CUDA(cudaMemcpy(d.freq2.get(), freq2.data(), d.H2 * sizeof(uint32_t), cudaMemcpyHostToDevice));
-    d.smem1 = size_t(d.H1) * tile_row_bytes;
-    d.smem2 = size_t(d.H2) * tile_row_bytes;
+    // tile + the transform's twiddle table
+    d.smem1 = size_t(d.H1) * (tile_row_bytes + sizeof(float2));
+    d.smem2 = size_t(d.H2) * (tile_row_bytes + sizeof(float2));
     d.threads1 = std::min(2 * TileThreads(d.H1), 512);
     d.threads2 = TileThreads(d.H2);
 
