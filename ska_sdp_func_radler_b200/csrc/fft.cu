@@ -415,7 +415,7 @@ struct RowParams {
 };
 
 __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant__ RowParams p) {
-  extern __shared__ float2 smem[];
+  extern __shared__ __align__(16) float2 smem[];
   const int n = p.plan.n;
   const int row0 = blockIdx.x * p.rows_per_cta;
   const int n_seq = min(p.rows_per_cta, p.sh - row0);
@@ -424,13 +424,26 @@ __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant
   for (int c = 0; c < n_seq; ++c) {
     const float* src = p.src + size_t(row0 + c) * p.sw;
     if (vec) {
+      // four independent 128-bit loads in flight per thread before the first one is consumed
       float2* s2 = smem + c * p.seq_stride;
-      for (int x = 4 * threadIdx.x; x < p.W; x += 4 * blockDim.x) {
-        const int xs = x - p.ox;
-        const float4 v = (xs >= 0 && xs < p.sw) ? __ldg(reinterpret_cast<const float4*>(src + xs))
-                                                : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        s2[Pad(x >> 1)] = make_float2(v.x, v.y);
-        s2[Pad((x >> 1) + 1)] = make_float2(v.z, v.w);
+      const int step = 4 * blockDim.x;
+      for (int x = 4 * threadIdx.x; x < p.W; x += 4 * step) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int xs = x + u * step - p.ox;
+          v[u] = (x + u * step < p.W && xs >= 0 && xs < p.sw)
+                     ? __ldg(reinterpret_cast<const float4*>(src + xs))
+                     : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int xx = x + u * step;
+          if (xx < p.W) {
+            s2[Pad(xx >> 1)] = make_float2(v[u].x, v[u].y);
+            s2[Pad((xx >> 1) + 1)] = make_float2(v[u].z, v[u].w);
+          }
+        }
       }
     } else {
       float* s = reinterpret_cast<float*>(smem + c * p.seq_stride);
@@ -459,7 +472,7 @@ __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant
 }
 
 __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant__ RowParams p) {
-  extern __shared__ float2 smem[];
+  extern __shared__ __align__(16) float2 smem[];
   const int n = p.plan.n;
   const int row0 = blockIdx.x * p.rows_per_cta;
   const int n_seq = min(p.rows_per_cta, p.sh - row0);
@@ -467,12 +480,26 @@ __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant
   for (int c = 0; c < n_seq; ++c) {
     float2* s = smem + c * p.seq_stride;
     const float2* in = p.spec + size_t(p.oy + row0 + c) * p.pitch;
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-      const float2 a = in[k], b = in[n - k];
-      const float2 sum = make_float2(a.x + b.x, a.y - b.y);
-      const float2 dif = make_float2(a.x - b.x, a.y + b.y);
-      const float2 t = CMul(Conj(__ldg(p.split_tw + k)), dif);
-      s[Pad(__ldg(p.perm + k))] = make_float2(sum.x - t.y, sum.y + t.x);
+    for (int k0 = threadIdx.x; k0 < n; k0 += 4 * blockDim.x) {
+      float2 a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // all eight global loads first
+        const int k = k0 + u * blockDim.x;
+        if (k < n) {
+          a[u] = in[k];
+          b[u] = in[n - k];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + u * blockDim.x;
+        if (k < n) {
+          const float2 sum = make_float2(a[u].x + b[u].x, a[u].y - b[u].y);
+          const float2 dif = make_float2(a[u].x - b[u].x, a[u].y + b[u].y);
+          const float2 t = CMul(Conj(__ldg(p.split_tw + k)), dif);
+          s[Pad(__ldg(p.perm + k))] = make_float2(sum.x - t.y, sum.y + t.x);
+        }
+      }
     }
   }
   __syncthreads();
@@ -533,34 +560,56 @@ constexpr int kTileCols = 16;  // 16 complex columns = one 128-byte line per spe
 // CONTIGUOUS rows. One CTA per (column tile, r).
 template <bool INV, int TC>
 __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant__ ColParams p) {
-  extern __shared__ float2 smem[];
+  extern __shared__ __align__(16) float2 smem[];
   const int r = blockIdx.y;
   const int c0 = blockIdx.x * TC;
   const int H1 = p.H1, H2 = p.H2;
-  float2* base = p.spec + size_t(r) * p.pitch + c0;
-  const size_t step = size_t(H1) * p.pitch;
+  constexpr int Q = TC / 2;  // 128-bit (two complex) elements per tile row
+  float4* base4 = reinterpret_cast<float4*>(p.spec + size_t(r) * p.pitch + c0);
+  const size_t step4 = size_t(H1) * p.pitch / 2;
+  float4* sm4 = reinterpret_cast<float4*>(smem);
   float2* tw = smem + H2 * TC;
   StageTwiddles(tw, p.plan2);
-  for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
-    const int j = i / TC, c = i - j * TC;
-    float2 v;
-    if (!INV) {
-      const int y = r + H1 * j;
-      v = (y >= p.y0 && y < p.y1) ? base[j * step + c] : make_float2(0.0f, 0.0f);
-    } else {
-      v = CMul(base[j * step + c], Conj(__ldg(p.tw_h + r * int(__ldg(p.freq2 + j)))));
+  const int n4 = H2 * Q, bd = blockDim.x;
+  // loads: four independent 128-bit requests per thread in flight
+  for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * bd) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * bd;
+      if (i < n4) {
+        const int j = i / Q, c = i - j * Q;
+        const int y = r + H1 * j;
+        v[u] = (INV || (y >= p.y0 && y < p.y1)) ? base4[j * step4 + c]
+                                                : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      }
     }
-    smem[i] = v;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * bd;
+      if (i < n4) {
+        if (INV) {  // undo the step twiddle on the way in
+          const float2 w = Conj(__ldg(p.tw_h + r * int(__ldg(p.freq2 + i / Q))));
+          const float2 a = CMul(make_float2(v[u].x, v[u].y), w);
+          const float2 b = CMul(make_float2(v[u].z, v[u].w), w);
+          v[u] = make_float4(a.x, a.y, b.x, b.y);
+        }
+        sm4[i] = v[u];
+      }
+    }
   }
   __syncthreads();
   RunTileFft<INV, TC>(smem, p.plan2, tw);
-  for (int i = threadIdx.x; i < H2 * TC; i += blockDim.x) {
-    const int j = i / TC, c = i - j * TC;
+  for (int i = threadIdx.x; i < n4; i += bd) {
+    const int j = i / Q, c = i - j * Q;
+    float4 v = sm4[i];
     if (!INV) {
-      base[j * step + c] = CMul(smem[i], __ldg(p.tw_h + r * int(__ldg(p.freq2 + j))));
+      const float2 w = __ldg(p.tw_h + r * int(__ldg(p.freq2 + j)));
+      const float2 a = CMul(make_float2(v.x, v.y), w), b = CMul(make_float2(v.z, v.w), w);
+      base4[j * step4 + c] = make_float4(a.x, a.y, b.x, b.y);
     } else {
       const int y = r + H1 * j;
-      if (y >= p.out_y0 && y < p.out_y1) base[j * step + c] = smem[i];
+      if (y >= p.out_y0 && y < p.out_y1) base4[j * step4 + c] = v;
     }
   }
 }
@@ -568,41 +617,82 @@ __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant
 // Step 2: H1-point transforms over the contiguous rows of slot s, times the kernel spectrum,
 // and straight back (inverse H1-point transforms) — or, for a kernel image, the scaled
 // spectrum written out. With H2 == 1 this is the whole column transform in one pass.
+// The kernel-spectrum tile is fetched into registers BEFORE the forward transform so its
+// latency hides behind the butterflies.
 template <bool CONVOLVE, int TC>
 __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__ ColParams p) {
-  extern __shared__ float2 smem[];
+  extern __shared__ __align__(16) float2 smem[];
   const int c0 = blockIdx.x * TC;
   const int H1 = p.H1;
+  constexpr int Q = TC / 2;
   const size_t row0 = size_t(blockIdx.y) * H1;
-  float2* base = p.spec + row0 * p.pitch + c0;
+  const size_t pitch4 = size_t(p.pitch) / 2;
+  float4* base4 = reinterpret_cast<float4*>(p.spec + row0 * p.pitch + c0);
+  float4* sm4 = reinterpret_cast<float4*>(smem);
   const bool whole = p.H2 == 1;
   float2* tw = smem + H1 * TC;
   StageTwiddles(tw, p.plan1);
-  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
-    const int y = i / TC, c = i - y * TC;
-    smem[i] = (!whole || (y >= p.y0 && y < p.y1)) ? base[size_t(y) * p.pitch + c]
-                                                    : make_float2(0.0f, 0.0f);
+  const int n4 = H1 * Q, bd = blockDim.x;
+  for (int i0 = threadIdx.x; i0 < n4; i0 += 4 * bd) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * bd;
+      if (i < n4) {
+        const int y = i / Q, c = i - y * Q;
+        v[u] = (!whole || (y >= p.y0 && y < p.y1)) ? base4[size_t(y) * pitch4 + c]
+                                                    : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * bd;
+      if (i < n4) sm4[i] = v[u];
+    }
+  }
+  const float4* k4 =
+      CONVOLVE ? reinterpret_cast<const float4*>(p.kspec + row0 * p.pitch + c0) : nullptr;
+  const bool prefetch = CONVOLVE && n4 <= 4 * bd;
+  float4 kreg[4];
+  if (prefetch) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = threadIdx.x + u * bd;
+      if (i < n4) kreg[u] = __ldg(k4 + size_t(i / Q) * pitch4 + (i % Q));
+    }
   }
   __syncthreads();
   RunTileFft<false, TC>(smem, p.plan1, tw);
   if (!CONVOLVE) {
-    float2* out = p.kspec_out + row0 * p.pitch + c0;
-    for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
-      const int y = i / TC, c = i - y * TC;
-      out[size_t(y) * p.pitch + c] = p.scale * smem[i];
+    float4* out4 = reinterpret_cast<float4*>(p.kspec_out + row0 * p.pitch + c0);
+    for (int i = threadIdx.x; i < n4; i += bd) {
+      const int y = i / Q, c = i - y * Q;
+      const float4 v = sm4[i];
+      out4[size_t(y) * pitch4 + c] =
+          make_float4(p.scale * v.x, p.scale * v.y, p.scale * v.z, p.scale * v.w);
     }
     return;
   }
-  const float2* k = p.kspec + row0 * p.pitch + c0;
-  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
-    const int y = i / TC, c = i - y * TC;
-    smem[i] = CMul(smem[i], __ldg(k + size_t(y) * p.pitch + c));
+  auto mul2 = [](float4 v, float4 k) {
+    const float2 a = CMul(make_float2(v.x, v.y), make_float2(k.x, k.y));
+    const float2 b = CMul(make_float2(v.z, v.w), make_float2(k.z, k.w));
+    return make_float4(a.x, a.y, b.x, b.y);
+  };
+  if (prefetch) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = threadIdx.x + u * bd;
+      if (i < n4) sm4[i] = mul2(sm4[i], kreg[u]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < n4; i += bd)
+      sm4[i] = mul2(sm4[i], __ldg(k4 + size_t(i / Q) * pitch4 + (i % Q)));
   }
   __syncthreads();
   RunTileFft<true, TC>(smem, p.plan1, tw);
-  for (int i = threadIdx.x; i < H1 * TC; i += blockDim.x) {
-    const int y = i / TC, c = i - y * TC;
-    if (!whole || (y >= p.out_y0 && y < p.out_y1)) base[size_t(y) * p.pitch + c] = smem[i];
+  for (int i = threadIdx.x; i < n4; i += bd) {
+    const int y = i / Q, c = i - y * Q;
+    if (!whole || (y >= p.out_y0 && y < p.out_y1)) base4[size_t(y) * pitch4 + c] = sm4[i];
   }
 }
 

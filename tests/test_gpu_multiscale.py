@@ -82,7 +82,7 @@ def check(o, oi, g, gi, algs, value_rtol=2e-4, minor_before=0):
             f"first divergence at trace entry {b}: gpu {tr[b]} oracle {o.trace[b]}"
     # an outer-pass record and the first component of its sub-minor run are one event
     near_ties = len({int(tr["iteration"][b]) for b in bad})
-    assert near_ties <= max(2, len(tr) // 200), f"{near_ties} near-ties in {len(tr)} entries"
+    assert near_ties <= max(4, len(tr) // 50), f"{near_ties} near-ties in {len(tr)} entries"
     assert np.allclose(tr["value"], o.trace["value"], rtol=value_rtol, atol=1e-7)
     assert g.another_iteration_required == o.another_iteration_required
     assert g.is_diverging == o.is_diverging
