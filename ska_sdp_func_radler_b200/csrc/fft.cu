@@ -278,7 +278,8 @@ __device__ void GenericStage(float2* s, int n_seq, int seq_stride, int n, int L,
   }
 }
 
-template <bool INV>
+// GENERIC = false compiles the generic-prime stage (and its 1 KB local array) out of the kernel.
+template <bool INV, bool GENERIC>
 __device__ __forceinline__ void RunStage(float2* s, int n_seq, int seq_stride, const Plan& plan,
                                          int st) {
   const int n = plan.n, L = plan.len[st];
@@ -289,22 +290,24 @@ __device__ __forceinline__ void RunStage(float2* s, int n_seq, int seq_stride, c
     case 3: Stage<3, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
     case 5: Stage<5, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
     case 7: Stage<7, INV>(s, n_seq, seq_stride, n, L, plan.tw); break;
-    default: GenericStage<INV>(s, n_seq, seq_stride, n, L, plan.radix[st], plan.tw); break;
+    default:
+      if (GENERIC) GenericStage<INV>(s, n_seq, seq_stride, n, L, plan.radix[st], plan.tw);
+      break;
   }
 }
 
 // Forward: natural order in, digit-reversed out. Inverse: digit-reversed in, natural out.
 // Both leave the block synchronised.
-template <bool INV>
+template <bool INV, bool GENERIC>
 __device__ __forceinline__ void RunFft(float2* s, int n_seq, int seq_stride, const Plan& plan) {
   if (!INV) {
     for (int st = 0; st < plan.n_stages; ++st) {
-      RunStage<false>(s, n_seq, seq_stride, plan, st);
+      RunStage<false, GENERIC>(s, n_seq, seq_stride, plan, st);
       __syncthreads();
     }
   } else {
     for (int st = plan.n_stages - 1; st >= 0; --st) {
-      RunStage<true>(s, n_seq, seq_stride, plan, st);
+      RunStage<true, GENERIC>(s, n_seq, seq_stride, plan, st);
       __syncthreads();
     }
   }
@@ -375,7 +378,7 @@ __device__ void TileGenericStage(float2* s, int n, int L, int p, const float2* _
 // Forward: natural order in, digit-reversed out; inverse the other way. Leaves the block
 // synchronised.
 // `tw`: the plan's twiddle table, staged in shared memory by the caller (n entries).
-template <bool INV, int TC>
+template <bool INV, int TC, bool GENERIC>
 __device__ __forceinline__ void RunTileFft(float2* s, const Plan& plan, const float2* tw) {
   for (int k = 0; k < plan.n_stages; ++k) {
     const int st = INV ? plan.n_stages - 1 - k : k;
@@ -387,7 +390,9 @@ __device__ __forceinline__ void RunTileFft(float2* s, const Plan& plan, const fl
       case 3: TileStage<3, INV, TC>(s, n, L, tw); break;
       case 5: TileStage<5, INV, TC>(s, n, L, tw); break;
       case 7: TileStage<7, INV, TC>(s, n, L, tw); break;
-      default: TileGenericStage<INV, TC>(s, n, L, plan.radix[st], tw); break;
+      default:
+        if (GENERIC) TileGenericStage<INV, TC>(s, n, L, plan.radix[st], tw);
+        break;
     }
     __syncthreads();
   }
@@ -414,6 +419,7 @@ struct RowParams {
   int mode;          // inverse epilogue: 0 store, 1 dst -= v, 2 dst += v
 };
 
+template <bool GENERIC>
 __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant__ RowParams p) {
   extern __shared__ __align__(16) float2 smem[];
   const int n = p.plan.n;
@@ -455,22 +461,39 @@ __global__ void __launch_bounds__(256, 3) RowForwardKernel(const __grid_constant
     }
   }
   __syncthreads();
-  RunFft<false>(smem, n_seq, p.seq_stride, p.plan);
+  RunFft<false, GENERIC>(smem, n_seq, p.seq_stride, p.plan);
   // split: 2 X[k] = (Z[k] + conj Z[n-k]) - i w^k (Z[k] - conj Z[n-k]),  k = 0..n
   for (int c = 0; c < n_seq; ++c) {
     const float2* s = smem + c * p.seq_stride;
     float2* out = p.spec + size_t(p.oy + row0 + c) * p.pitch;
-    for (int k = threadIdx.x; k <= n; k += blockDim.x) {
-      const int ka = k == n ? 0 : k, kb = k == 0 ? 0 : n - k;
-      const float2 a = s[Pad(__ldg(p.perm + ka))], b = s[Pad(__ldg(p.perm + kb))];
-      const float2 sum = make_float2(a.x + b.x, a.y - b.y);
-      const float2 dif = make_float2(a.x - b.x, a.y + b.y);
-      const float2 t = CMul(__ldg(p.split_tw + k), dif);
-      out[k] = make_float2(sum.x + t.y, sum.y - t.x);
+    for (int k0 = threadIdx.x; k0 <= n; k0 += 4 * blockDim.x) {
+      uint32_t pa[4], pb[4];
+      float2 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // table lookups of four outputs in flight together
+        const int k = k0 + u * blockDim.x;
+        if (k <= n) {
+          pa[u] = __ldg(p.perm + (k == n ? 0 : k));
+          pb[u] = __ldg(p.perm + (k == 0 ? 0 : n - k));
+          w[u] = __ldg(p.split_tw + k);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + u * blockDim.x;
+        if (k <= n) {
+          const float2 a = s[Pad(pa[u])], b = s[Pad(pb[u])];
+          const float2 sum = make_float2(a.x + b.x, a.y - b.y);
+          const float2 dif = make_float2(a.x - b.x, a.y + b.y);
+          const float2 t = CMul(w[u], dif);
+          out[k] = make_float2(sum.x + t.y, sum.y - t.x);
+        }
+      }
     }
   }
 }
 
+template <bool GENERIC>
 __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant__ RowParams p) {
   extern __shared__ __align__(16) float2 smem[];
   const int n = p.plan.n;
@@ -481,13 +504,16 @@ __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant
     float2* s = smem + c * p.seq_stride;
     const float2* in = p.spec + size_t(p.oy + row0 + c) * p.pitch;
     for (int k0 = threadIdx.x; k0 < n; k0 += 4 * blockDim.x) {
-      float2 a[4], b[4];
+      float2 a[4], b[4], w[4];
+      uint32_t slot[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // all eight global loads first
+      for (int u = 0; u < 4; ++u) {  // all global loads first
         const int k = k0 + u * blockDim.x;
         if (k < n) {
           a[u] = in[k];
           b[u] = in[n - k];
+          w[u] = __ldg(p.split_tw + k);
+          slot[u] = __ldg(p.perm + k);
         }
       }
 #pragma unroll
@@ -496,14 +522,14 @@ __global__ void __launch_bounds__(256, 3) RowInverseKernel(const __grid_constant
         if (k < n) {
           const float2 sum = make_float2(a[u].x + b[u].x, a[u].y - b[u].y);
           const float2 dif = make_float2(a[u].x - b[u].x, a[u].y + b[u].y);
-          const float2 t = CMul(Conj(__ldg(p.split_tw + k)), dif);
-          s[Pad(__ldg(p.perm + k))] = make_float2(sum.x - t.y, sum.y + t.x);
+          const float2 t = CMul(Conj(w[u]), dif);
+          s[Pad(slot[u])] = make_float2(sum.x - t.y, sum.y + t.x);
         }
       }
     }
   }
   __syncthreads();
-  RunFft<true>(smem, n_seq, p.seq_stride, p.plan);
+  RunFft<true, GENERIC>(smem, n_seq, p.seq_stride, p.plan);
   const bool vec = ((p.ox | p.sw) & 3) == 0 && (reinterpret_cast<uintptr_t>(p.dst) & 15) == 0;
   for (int c = 0; c < n_seq; ++c) {
     const float* s = reinterpret_cast<const float*>(smem + c * p.seq_stride);
@@ -558,7 +584,7 @@ constexpr int kTileCols = 16;  // 16 complex columns = one 128-byte line per spe
 // over rows r, r + H1, r + 2 H1, ... of one column tile, fused with the step twiddle
 // w_H^(r k2). Forward leaves frequency k2 in the row block of its slot, so step 2 works on H1
 // CONTIGUOUS rows. One CTA per (column tile, r).
-template <bool INV, int TC>
+template <bool INV, int TC, bool GENERIC>
 __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant__ ColParams p) {
   extern __shared__ __align__(16) float2 smem[];
   const int r = blockIdx.y;
@@ -599,7 +625,7 @@ __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant
     }
   }
   __syncthreads();
-  RunTileFft<INV, TC>(smem, p.plan2, tw);
+  RunTileFft<INV, TC, GENERIC>(smem, p.plan2, tw);
   for (int i = threadIdx.x; i < n4; i += bd) {
     const int j = i / Q, c = i - j * Q;
     float4 v = sm4[i];
@@ -619,7 +645,7 @@ __global__ void __launch_bounds__(256) ColumnStridedKernel(const __grid_constant
 // spectrum written out. With H2 == 1 this is the whole column transform in one pass.
 // The kernel-spectrum tile is fetched into registers BEFORE the forward transform so its
 // latency hides behind the butterflies.
-template <bool CONVOLVE, int TC>
+template <bool CONVOLVE, int TC, bool GENERIC>
 __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__ ColParams p) {
   extern __shared__ __align__(16) float2 smem[];
   const int c0 = blockIdx.x * TC;
@@ -662,7 +688,7 @@ __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__
     }
   }
   __syncthreads();
-  RunTileFft<false, TC>(smem, p.plan1, tw);
+  RunTileFft<false, TC, GENERIC>(smem, p.plan1, tw);
   if (!CONVOLVE) {
     float4* out4 = reinterpret_cast<float4*>(p.kspec_out + row0 * p.pitch + c0);
     for (int i = threadIdx.x; i < n4; i += bd) {
@@ -689,7 +715,7 @@ __global__ void __launch_bounds__(512) ColumnBlockKernel(const __grid_constant__
       sm4[i] = mul2(sm4[i], __ldg(k4 + size_t(i / Q) * pitch4 + (i % Q)));
   }
   __syncthreads();
-  RunTileFft<true, TC>(smem, p.plan1, tw);
+  RunTileFft<true, TC, GENERIC>(smem, p.plan1, tw);
   for (int i = threadIdx.x; i < n4; i += bd) {
     const int y = i / Q, c = i - y * Q;
     if (!whole || (y >= p.out_y0 && y < p.out_y1)) base4[size_t(y) * pitch4 + c] = sm4[i];
@@ -790,6 +816,7 @@ struct HostPlan {
 struct FftConvolver::Impl {
   int W, H, n, pitch;
   int H1 = 1, H2 = 1;
+  bool row_generic = false, col_generic = false;  // a prime radix > 7 somewhere in the plans
   HostPlan row, col, col1, col2;
   DeviceBuffer<uint32_t> perm, freq2;
   DeviceBuffer<float2> split_tw;
@@ -886,12 +913,25 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     d.threads1 = std::min(2 * TileThreads(d.H1), 512);
     d.threads2 = TileThreads(d.H2);
 
-    RDL_CUDA(cudaFuncSetAttribute(RowForwardKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(RowInverseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<true, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<false, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<true, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
-    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<false, kTileCols>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxSmemBytes)));
+    auto has_generic = [](const HostPlan& hp) {
+      return std::any_of(hp.radices.begin(), hp.radices.end(), [](int r) { return r > 8; });
+    };
+    d.row_generic = has_generic(d.row);
+    d.col_generic = has_generic(d.col1) || has_generic(d.col2);
+    const int smem_max = int(kMaxSmemBytes);
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    RDL_CUDA(cudaFuncSetAttribute(RowForwardKernel<false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(RowForwardKernel<true>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(RowInverseKernel<false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(RowInverseKernel<true>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<true, kTileCols, false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<true, kTileCols, true>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<false, kTileCols, false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnBlockKernel<false, kTileCols, true>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<true, kTileCols, false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<true, kTileCols, true>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<false, kTileCols, false>, attr, smem_max));
+    RDL_CUDA(cudaFuncSetAttribute(ColumnStridedKernel<false, kTileCols, true>, attr, smem_max));
     d.work.Resize(size_t(d.H) * d.pitch);
     // columns n+1 .. pitch-1 ride along in the column tiles: keep them finite
     RDL_CUDA(cudaMemset(d.work.get(), 0, size_t(d.H) * d.pitch * sizeof(float2)));
@@ -925,7 +965,10 @@ void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, cudaStrea
   p.rows_per_cta = d.rows_per_cta;
   p.seq_stride = d.row_stride;
   const int grid = (int(sh) + d.rows_per_cta - 1) / d.rows_per_cta;
-  RowForwardKernel<<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  if (d.row_generic)
+    RowForwardKernel<true><<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  else
+    RowForwardKernel<false><<<grid, d.row_threads, d.row_smem, stream>>>(p);
   ++launches_;
 }
 
@@ -937,10 +980,16 @@ void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectru
   c.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
   const int tiles = d.pitch / kTileCols;
   if (d.H2 > 1) {
-    ColumnStridedKernel<false, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    if (d.col_generic)
+      ColumnStridedKernel<false, kTileCols, true><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    else
+      ColumnStridedKernel<false, kTileCols, false><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
     ++launches_;
   }
-  ColumnBlockKernel<false, kTileCols><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
+  if (d.col_generic)
+    ColumnBlockKernel<false, kTileCols, true><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
+  else
+    ColumnBlockKernel<false, kTileCols, false><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
   ++launches_;
 }
 
@@ -980,13 +1029,22 @@ void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const fl
   c.out_y1 = c.out_y0 + int(dh);
   const int tiles = d.pitch / kTileCols;
   if (d.H2 > 1) {
-    ColumnStridedKernel<false, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    if (d.col_generic)
+      ColumnStridedKernel<false, kTileCols, true><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    else
+      ColumnStridedKernel<false, kTileCols, false><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
     ++launches_;
   }
-  ColumnBlockKernel<true, kTileCols><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
+  if (d.col_generic)
+    ColumnBlockKernel<true, kTileCols, true><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
+  else
+    ColumnBlockKernel<true, kTileCols, false><<<dim3(tiles, d.H2), d.threads1, d.smem1, stream>>>(c);
   ++launches_;
   if (d.H2 > 1) {
-    ColumnStridedKernel<true, kTileCols><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    if (d.col_generic)
+      ColumnStridedKernel<true, kTileCols, true><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
+    else
+      ColumnStridedKernel<true, kTileCols, false><<<dim3(tiles, d.H1), d.threads2, d.smem2, stream>>>(c);
     ++launches_;
   }
   RowParams p{};
@@ -1006,7 +1064,10 @@ void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const fl
   p.seq_stride = d.row_stride;
   p.mode = mode;
   const int grid = (int(dh) + d.rows_per_cta - 1) / d.rows_per_cta;
-  RowInverseKernel<<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  if (d.row_generic)
+    RowInverseKernel<true><<<grid, d.row_threads, d.row_smem, stream>>>(p);
+  else
+    RowInverseKernel<false><<<grid, d.row_threads, d.row_smem, stream>>>(p);
   ++launches_;
 }
 
