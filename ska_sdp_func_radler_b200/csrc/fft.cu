@@ -25,6 +25,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <map>
 #include <vector>
 
@@ -881,7 +882,9 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     d.row_stride = PaddedLength(d.n);
     const size_t row_bytes = size_t(d.row_stride) * sizeof(float2);
     if (row_bytes > kMaxSmemBytes) throw std::domain_error("image row does not fit in shared memory");
-    d.rows_per_cta = int(std::clamp<size_t>(size_t(75 * 1024) / row_bytes, 1, 8));
+    size_t row_budget_kb = 75;
+    if (const char* e = std::getenv("RDL_FFT_ROW_SMEM_KB")) row_budget_kb = size_t(std::atoi(e));
+    d.rows_per_cta = int(std::clamp<size_t>(row_budget_kb * 1024 / row_bytes, 1, 8));
     d.row_smem = row_bytes * d.rows_per_cta;
     d.row_threads = d.n * d.rows_per_cta >= 4096 ? 256 : 128;
 

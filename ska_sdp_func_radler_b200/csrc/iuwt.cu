@@ -96,6 +96,7 @@ struct SmoothParams {
   const uint8_t* mask;  // EPI 2: optional ApplyMask plane
   int width, height, d;
   int blocks_per_residue;  // comb blocks per residue class
+  int rows_per_block;      // comb rows a CTA produces (<= kTY), balanced over the blocks
 };
 
 // EPI 0: out = B(in); 1: out = other - B(in); 2: out = B(in) + (mask ? other : 0)
@@ -106,31 +107,41 @@ __global__ void __launch_bounds__(kThreads) IuwtSmoothKernel(const __grid_consta
   const int x0 = blockIdx.x * kTX;
   const int r = blockIdx.y / p.blocks_per_residue;           // residue class of the comb
   const int kb = blockIdx.y - r * p.blocks_per_residue;      // comb block
-  const int k0 = kb * kTY;                                   // first comb index of the tile
-  // phase 1: horizontally smoothed comb rows k0-2 .. k0+TY+1
-  for (int i = threadIdx.x; i < (kTY + 4) * kTX; i += kThreads) {
-    const int row = i / kTX, xl = i - row * kTX;
-    const int x = x0 + xl;
-    const long y = long(r) + long(k0 + row - 2) * d;
-    float val = 0.0f;
-    if (y >= 0 && y < H && x < W) {
-      const float* src = p.in + size_t(y) * W;
-      float v[5];
-      unsigned present = 0;
+  const int k0 = kb * p.rows_per_block;                      // first comb index of the tile
+  // phase 1: horizontally smoothed comb rows k0-2 .. k0+ty+1; four outputs (20 loads) in flight
+  // per thread before the first tap sum
+  const int ty = p.rows_per_block;
+  const int n1 = (ty + 4) * kTX;
+  for (int i0 = threadIdx.x; i0 < n1; i0 += 4 * kThreads) {
+    float v[4][5];
+    unsigned present[4];
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const int xx = x + (k - 2) * d;
-        const bool ok = xx >= 0 && xx < W;
-        v[k] = ok ? __ldg(src + xx) : 0.0f;
-        present |= ok ? (1u << k) : 0u;
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * kThreads;
+      present[u] = 0;
+      const int row = i / kTX, xl = i - row * kTX;
+      const int x = x0 + xl;
+      const long y = long(r) + long(k0 + row - 2) * d;
+      if (i < n1 && y >= 0 && y < H && x < W) {
+        const float* src = p.in + size_t(y) * W;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const int xx = x + (k - 2) * d;
+          const bool ok = xx >= 0 && xx < W;
+          v[u][k] = ok ? __ldg(src + xx) : 0.0f;
+          present[u] |= ok ? (1u << k) : 0u;
+        }
       }
-      val = Taps<SIMPLE, !SIMPLE>(v, present);
     }
-    hs[row][xl] = val;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * kThreads;
+      if (i < n1) (&hs[0][0])[i] = present[u] ? Taps<SIMPLE, !SIMPLE>(v[u], present[u]) : 0.0f;
+    }
   }
   __syncthreads();
   // phase 2: vertical pass over the comb + epilogue
-  for (int i = threadIdx.x; i < kTY * kTX; i += kThreads) {
+  for (int i = threadIdx.x; i < ty * kTX; i += kThreads) {
     const int row = i / kTX, xl = i - row * kTX;
     const int x = x0 + xl;
     const long y = long(r) + long(k0 + row) * d;
@@ -176,6 +187,7 @@ void LaunchSmooth(rdl_handle& h, const float* in, float* out, const float* other
   const int residues = std::min<long>(p.d, long(height));
   const int comb_rows = (int(height) + p.d - 1) / p.d;  // rows of the longest comb
   p.blocks_per_residue = (comb_rows + kTY - 1) / kTY;
+  p.rows_per_block = (comb_rows + p.blocks_per_residue - 1) / p.blocks_per_residue;
   dim3 grid((unsigned(width) + kTX - 1) / kTX, unsigned(residues) * p.blocks_per_residue);
   IuwtSmoothKernel<SIMPLE, EPI><<<grid, kThreads, 0, stream>>>(p);
   RDL_CUDA(cudaGetLastError());
