@@ -296,6 +296,52 @@ rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, u
                               uint64_t height, int32_t n_scales, int32_t include_largest,
                               const uint8_t* device_masks, float* device_out, void* stream);
 
+/* ---- IUWT structure selection (cpp/algorithms/iuwt/image_analysis.{h,cc}); device pointers ----
+ * device_coefficients: n_scales planes of width*height floats (IuwtDecomposition);
+ * device_masks: n_scales planes of width*height bytes (IuwtMask), updated in place;
+ * thresholds: n_scales HOST floats. A negative threshold t selects v < t or v > -t
+ * (ExceedsThreshold, image_analysis.cc:9-15). clean_border in [0, 0.5). These calls return
+ * when the result is on the host (they synchronise the stream).
+ *
+ * image_analysis::SelectStructures (image_analysis.cc:208-239): marks every voxel of scales
+ * [min_scale, end_scale) that exceeds its threshold, is not marked yet, lies inside
+ * device_prior_mask (width*height bytes, NULL = everywhere) and inside the clean border;
+ * *area_size = number of voxels newly marked. */
+rdl_status rdl_iuwt_select_structures(rdl_handle* h, const float* device_coefficients,
+                                      uint8_t* device_masks, uint64_t width, uint64_t height,
+                                      int32_t n_scales, const float* thresholds, int32_t min_scale,
+                                      int32_t end_scale, float clean_border,
+                                      const uint8_t* device_prior_mask, uint64_t* area_size,
+                                      void* stream);
+/* image_analysis::Floodfill (image_analysis.cc:86-149) and, with a prior mask, MaskedFloodfill
+ * (:151-206): marks the 6-connected (x, y, scale) structure around the seed voxel;
+ * *area_size = voxels filled, the seed included. */
+rdl_status rdl_iuwt_floodfill(rdl_handle* h, const float* device_coefficients,
+                              uint8_t* device_masks, uint64_t width, uint64_t height,
+                              int32_t n_scales, const float* thresholds, int32_t min_scale,
+                              int32_t end_scale, uint64_t seed_x, uint64_t seed_y,
+                              int32_t seed_scale, float clean_border,
+                              const uint8_t* device_prior_mask, uint64_t* area_size, void* stream);
+/* image_analysis::FloodFill2D (image_analysis.cc:241-333): use_abs = 0 is the ExceedsThreshold
+ * overload that returns the area size (:241-283), use_abs = 1 the fabs(v) > threshold overload
+ * that collects the area (:285-333; its pixels are the bytes newly set in device_mask). */
+rdl_status rdl_iuwt_floodfill_2d(rdl_handle* h, const float* device_image, uint8_t* device_mask,
+                                 uint64_t width, uint64_t height, float threshold, int32_t use_abs,
+                                 uint64_t seed_x, uint64_t seed_y, uint64_t* area_size,
+                                 void* stream);
+/* IuwtDeconvolutionAlgorithm::Mad (cpp/algorithms/iuwt_deconvolution_algorithm.cc:104-110):
+ * element n/2 of the sorted |v| of a plane of n floats, divided by 0.674559. */
+rdl_status rdl_iuwt_mad(rdl_handle* h, const float* device_image, uint64_t n, float* mad,
+                        void* stream);
+/* IuwtDeconvolutionAlgorithm::GetMaxAbsWithoutMask / GetMaxAbsWithMask
+ * (iuwt_deconvolution_algorithm.cc:112-167): first row-major maximum of |v| (allow_negative)
+ * or v inside the clean border and, when given, inside device_mask (width*height bytes). When
+ * nothing qualifies *x = width, *y = height and *value = -FLT_MAX, as in the reference. */
+rdl_status rdl_iuwt_max_abs(rdl_handle* h, const float* device_image, uint64_t width,
+                            uint64_t height, float clean_border, int32_t allow_negative,
+                            const uint8_t* device_mask, float* value, uint64_t* x, uint64_t* y,
+                            void* stream);
+
 /* utils::CalculateGoodFFTSize / GetConvolutionSize (cpp/utils/fft_size_calculations.h:15-50) */
 uint64_t rdl_good_fft_size(uint64_t minimum_size);
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);

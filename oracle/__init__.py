@@ -66,6 +66,22 @@ def ref_lib():
         L.ref_iuwt_decompose.argtypes = [vp, u64, u64, C.c_int32, C.c_int32, vp]
         L.ref_iuwt_recompose.argtypes = [vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
         L.ref_iuwt_smooth.argtypes = [vp, u64, u64, C.c_int32]
+        i32, f32 = C.c_int32, C.c_float
+        for pre in ["ref_"]:
+            f = getattr(L, pre + "iuwt_select_structures")
+            f.restype = u64
+            f.argtypes = [vp, vp, u64, u64, i32, vp, i32, i32, f32, vp]
+            f = getattr(L, pre + "iuwt_floodfill")
+            f.restype = u64
+            f.argtypes = [vp, vp, u64, u64, i32, vp, i32, i32, u64, u64, i32, f32, vp]
+            f = getattr(L, pre + "iuwt_floodfill_2d")
+            f.restype = u64
+            f.argtypes = [vp, vp, u64, u64, f32, i32, u64, u64]
+            f = getattr(L, pre + "iuwt_max_abs")
+            f.restype = f32
+            f.argtypes = [vp, u64, u64, f32, i32, vp, C.POINTER(u64), C.POINTER(u64)]
+        L.ref_iuwt_mad.restype = f32
+        L.ref_iuwt_mad.argtypes = [vp, u64, u64]
         _ref = L
     return _ref
 
@@ -216,6 +232,22 @@ def lib():
                                          C.c_void_p]
         L.orc_iuwt_recompose.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32,
                                          C.c_void_p, C.c_void_p]
+        i32, f32 = C.c_int32, C.c_float
+        for pre in ["orc_"]:
+            f = getattr(L, pre + "iuwt_select_structures")
+            f.restype = C.c_uint64
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, i32, C.c_void_p, i32, i32, f32, C.c_void_p]
+            f = getattr(L, pre + "iuwt_floodfill")
+            f.restype = C.c_uint64
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, i32, C.c_void_p, i32, i32, C.c_uint64, C.c_uint64, i32, f32, C.c_void_p]
+            f = getattr(L, pre + "iuwt_floodfill_2d")
+            f.restype = C.c_uint64
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, f32, i32, C.c_uint64, C.c_uint64]
+            f = getattr(L, pre + "iuwt_max_abs")
+            f.restype = f32
+            f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, f32, i32, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.orc_iuwt_mad.restype = f32
+        L.orc_iuwt_mad.argtypes = [C.c_void_p, C.c_uint64]
         _lib = L
     return _lib
 
@@ -529,6 +561,72 @@ def ref_iuwt_smooth(image, to_scale):
     a = _f32(image).copy()
     ref_lib().ref_iuwt_smooth(_ptr(a), a.shape[1], a.shape[0], to_scale)
     return a
+
+
+def _iuwt_analysis(prefix):
+    """Structure selection / flood fills / plane measurements, from liboracle.so (prefix "orc_")
+    or from the reference's own sources in oracle/_ref (prefix "ref_"). Masks are uint8 arrays
+    [n_scales, H, W] (2-D for the 2-D fill); every call returns (new masks, area) or a scalar."""
+    L = lib() if prefix == "orc_" else ref_lib()
+
+    def select_structures(coefficients, masks, thresholds, min_scale, end_scale, clean_border=0.0,
+                          prior_mask=None):
+        c = _f32(coefficients)
+        m = np.ascontiguousarray(masks, np.uint8).copy()
+        t = _f32(thresholds)
+        p = None if prior_mask is None else np.ascontiguousarray(prior_mask, np.uint8)
+        area = getattr(L, prefix + "iuwt_select_structures")(
+            _ptr(c), _ptr(m), c.shape[2], c.shape[1], c.shape[0], _ptr(t), min_scale, end_scale,
+            clean_border, _ptr(p))
+        return m, area
+
+    def floodfill(coefficients, masks, thresholds, min_scale, end_scale, seed, clean_border=0.0,
+                  prior_mask=None):
+        c = _f32(coefficients)
+        m = np.ascontiguousarray(masks, np.uint8).copy()
+        t = _f32(thresholds)
+        p = None if prior_mask is None else np.ascontiguousarray(prior_mask, np.uint8)
+        x, y, scale = seed
+        area = getattr(L, prefix + "iuwt_floodfill")(
+            _ptr(c), _ptr(m), c.shape[2], c.shape[1], c.shape[0], _ptr(t), min_scale, end_scale,
+            x, y, scale, clean_border, _ptr(p))
+        return m, area
+
+    def floodfill_2d(image, mask, threshold, seed, use_abs=False):
+        a = _f32(image)
+        m = np.ascontiguousarray(mask, np.uint8).copy()
+        area = getattr(L, prefix + "iuwt_floodfill_2d")(_ptr(a), _ptr(m), a.shape[1], a.shape[0],
+                                                        threshold, int(use_abs), seed[0], seed[1])
+        return m, area
+
+    def mad(image):
+        a = _f32(image)
+        if prefix == "orc_":
+            return float(L.orc_iuwt_mad(_ptr(a), a.size))
+        return float(L.ref_iuwt_mad(_ptr(a), a.shape[1], a.shape[0]))
+
+    def max_abs(image, clean_border=0.0, allow_negative=True, mask=None):
+        a = _f32(image)
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        x, y = C.c_uint64(), C.c_uint64()
+        v = getattr(L, prefix + "iuwt_max_abs")(_ptr(a), a.shape[1], a.shape[0], clean_border,
+                                                int(allow_negative), _ptr(m), C.byref(x),
+                                                C.byref(y))
+        return float(v), x.value, y.value
+
+    return select_structures, floodfill, floodfill_2d, mad, max_abs
+
+
+def iuwt_analysis():
+    """(select_structures, floodfill, floodfill_2d, mad, max_abs) of the oracle restatement
+    (oracle/iuwt_analysis.cc)."""
+    return _iuwt_analysis("orc_")
+
+
+def ref_iuwt_analysis():
+    """The same five functions from the reference's own image_analysis.cc /
+    iuwt_deconvolution_algorithm.cc compiled in oracle/_ref."""
+    return _iuwt_analysis("ref_")
 
 
 def good_fft_size(n):

@@ -327,6 +327,33 @@ void orc_iuwt_recompose(const float* coefficients, uint64_t w, uint64_t h, int32
                         int32_t include_largest, const uint8_t* masks, float* out) {
   IuwtRecompose(coefficients, w, h, n_scales, include_largest != 0, masks, out);
 }
+uint64_t orc_iuwt_floodfill(const float* coefficients, uint8_t* masks, uint64_t w, uint64_t h,
+                            int32_t n_scales, const float* thresholds, int32_t min_scale,
+                            int32_t end_scale, uint64_t x, uint64_t y, int32_t scale,
+                            float clean_border, const uint8_t* prior_mask) {
+  return IuwtFloodfill(coefficients, masks, w, h, n_scales, thresholds, min_scale, end_scale, x, y,
+                       scale, clean_border, prior_mask);
+}
+uint64_t orc_iuwt_select_structures(const float* coefficients, uint8_t* masks, uint64_t w,
+                                    uint64_t h, int32_t n_scales, const float* thresholds,
+                                    int32_t min_scale, int32_t end_scale, float clean_border,
+                                    const uint8_t* prior_mask) {
+  return IuwtSelectStructures(coefficients, masks, w, h, n_scales, thresholds, min_scale,
+                              end_scale, clean_border, prior_mask);
+}
+uint64_t orc_iuwt_floodfill_2d(const float* image, uint8_t* mask, uint64_t w, uint64_t h,
+                               float threshold, int32_t use_abs, uint64_t x, uint64_t y) {
+  return IuwtFloodfill2D(image, mask, w, h, threshold, use_abs != 0, x, y);
+}
+float orc_iuwt_mad(const float* image, uint64_t n) { return IuwtMad(image, n); }
+float orc_iuwt_max_abs(const float* image, uint64_t w, uint64_t h, float clean_border,
+                       int32_t allow_negative, const uint8_t* mask, uint64_t* x, uint64_t* y) {
+  size_t px, py;
+  const float v = IuwtMaxAbs(image, w, h, clean_border, allow_negative != 0, mask, px, py);
+  *x = px;
+  *y = py;
+  return v;
+}
 uint64_t orc_good_fft_size(uint64_t n) { return CalculateGoodFFTSize(n); }
 uint64_t orc_convolution_size(double scale, uint64_t n, double padding) {
   return GetConvolutionSize(scale, n, padding);

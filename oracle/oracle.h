@@ -360,5 +360,21 @@ void IuwtDecompose(const float* input, size_t width, size_t height, int n_scales
 void IuwtRecompose(const float* coefficients, size_t width, size_t height, int n_scales,
                    bool include_largest, const uint8_t* masks, float* out);
 
+
+// ---- IUWT structure selection and plane measurements (iuwt_analysis.cc) ---------------------
+// masks: n_scales planes of width*height bytes (in/out); return value = voxels newly filled
+size_t IuwtFloodfill(const float* coefficients, uint8_t* masks, size_t width, size_t height,
+                     int n_scales, const float* thresholds, int min_scale, int end_scale,
+                     size_t seed_x, size_t seed_y, int seed_scale, float clean_border,
+                     const uint8_t* prior_mask);
+size_t IuwtSelectStructures(const float* coefficients, uint8_t* masks, size_t width, size_t height,
+                            int n_scales, const float* thresholds, int min_scale, int end_scale,
+                            float clean_border, const uint8_t* prior_mask);
+size_t IuwtFloodfill2D(const float* image, uint8_t* mask, size_t width, size_t height,
+                       float threshold, bool use_abs, size_t seed_x, size_t seed_y);
+float IuwtMad(const float* image, size_t n);
+float IuwtMaxAbs(const float* image, size_t width, size_t height, float clean_border,
+                 bool allow_negative, const uint8_t* mask, size_t& x, size_t& y);
+
 }  // namespace oracle
 #endif

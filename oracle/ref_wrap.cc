@@ -8,8 +8,13 @@
 #include <cstdint>
 #include <vector>
 
+#include "algorithms/iuwt/image_analysis.h"
 #include "algorithms/iuwt/iuwt_decomposition.h"
 #include "algorithms/iuwt/iuwt_mask.h"
+// Mad and GetMaxAbs are private members of the reference's class; the wrapper below needs them
+#define private public
+#include "algorithms/iuwt_deconvolution_algorithm.h"
+#undef private
 #include "algorithms/multiscale/multiscale_transforms.h"
 #include "algorithms/simple_clean.h"
 #include "math/dijkstra_splitter.h"
@@ -173,5 +178,87 @@ void ref_iuwt_smooth(float* image, uint64_t w, uint64_t h, int to_scale) {
   std::copy_n(image, w * h, img.Data());
   d.Convolve(img, to_scale);
   std::copy_n(img.Data(), w * h, image);
+}
+
+// ---- IUWT structure selection (iuwt/image_analysis.cc) and plane measurements
+// (iuwt_deconvolution_algorithm.cc:104-167) of the reference itself --------------------------
+namespace {
+struct IuwtFixture {
+  algorithms::iuwt::IuwtDecomposition d;
+  algorithms::iuwt::IuwtMask m;
+  aocommon::UVector<float> thresholds;
+  IuwtFixture(const float* coefficients, const uint8_t* masks, uint64_t w, uint64_t h,
+              int n_scales, const float* thr)
+      : d(n_scales, w, h), m(n_scales, w, h), thresholds(thr, thr + n_scales) {
+    for (int s = 0; s != n_scales; ++s) {
+      d[s].Coefficients() = aocommon::Image(w, h);
+      std::copy_n(coefficients + size_t(s) * w * h, w * h, d[s].Coefficients().Data());
+      for (size_t i = 0; i != w * h; ++i) m[s][i] = masks[size_t(s) * w * h + i] != 0;
+    }
+  }
+  void Store(uint8_t* masks, uint64_t w, uint64_t h, int n_scales) {
+    for (int s = 0; s != n_scales; ++s)
+      for (size_t i = 0; i != w * h; ++i) masks[size_t(s) * w * h + i] = m[s][i] ? 1 : 0;
+  }
+};
+}  // namespace
+
+uint64_t ref_iuwt_select_structures(const float* coefficients, uint8_t* masks, uint64_t w,
+                                    uint64_t h, int n_scales, const float* thresholds,
+                                    int min_scale, int end_scale, float clean_border,
+                                    const uint8_t* prior_mask) {
+  IuwtFixture f(coefficients, masks, w, h, n_scales, thresholds);
+  size_t area = 0;
+  algorithms::iuwt::image_analysis::SelectStructures(
+      f.d, f.m, f.thresholds, min_scale, end_scale, clean_border,
+      reinterpret_cast<const bool*>(prior_mask), area);
+  f.Store(masks, w, h, n_scales);
+  return area;
+}
+uint64_t ref_iuwt_floodfill(const float* coefficients, uint8_t* masks, uint64_t w, uint64_t h,
+                            int n_scales, const float* thresholds, int min_scale, int end_scale,
+                            uint64_t x, uint64_t y, int scale, float clean_border,
+                            const uint8_t* prior_mask) {
+  IuwtFixture f(coefficients, masks, w, h, n_scales, thresholds);
+  size_t area = 0;
+  const algorithms::iuwt::image_analysis::Component seed(x, y, scale);
+  if (prior_mask)
+    algorithms::iuwt::image_analysis::MaskedFloodfill(
+        f.d, f.m, f.thresholds, min_scale, end_scale, seed, clean_border,
+        reinterpret_cast<const bool*>(prior_mask), area);
+  else
+    algorithms::iuwt::image_analysis::Floodfill(f.d, f.m, f.thresholds, min_scale, end_scale, seed,
+                                                clean_border, area);
+  f.Store(masks, w, h, n_scales);
+  return area;
+}
+uint64_t ref_iuwt_floodfill_2d(const float* image, uint8_t* mask, uint64_t w, uint64_t h,
+                               float threshold, int use_abs, uint64_t x, uint64_t y) {
+  const algorithms::iuwt::image_analysis::Component2D seed(x, y);
+  bool* m = reinterpret_cast<bool*>(mask);
+  if (use_abs) {
+    std::vector<algorithms::iuwt::image_analysis::Component2D> area;
+    algorithms::iuwt::image_analysis::FloodFill2D(image, m, threshold, seed, w, h, area);
+    return area.size();
+  }
+  size_t area = 0;
+  algorithms::iuwt::image_analysis::FloodFill2D(image, m, threshold, seed, w, h, area);
+  return area;
+}
+float ref_iuwt_mad(const float* image, uint64_t w, uint64_t h) {
+  algorithms::IuwtDeconvolutionAlgorithm a(w, h, 0.1f, 0.8f, 0.0f, true, nullptr, 0.0f);
+  return a.Mad(image);
+}
+float ref_iuwt_max_abs(const float* image, uint64_t w, uint64_t h, float clean_border,
+                       int allow_negative, const uint8_t* mask, uint64_t* x, uint64_t* y) {
+  algorithms::IuwtDeconvolutionAlgorithm a(w, h, 0.1f, 0.8f, clean_border, allow_negative != 0,
+                                           reinterpret_cast<const bool*>(mask), 0.0f);
+  aocommon::Image img(w, h);
+  std::copy_n(image, w * h, img.Data());
+  size_t px = 0, py = 0;
+  const float v = a.GetMaxAbs(img, px, py, w);
+  *x = px;
+  *y = py;
+  return v;
 }
 }

@@ -93,6 +93,8 @@ EXPORTED_SYMBOLS = [
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
+    "rdl_iuwt_max_abs",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
     "rdl_facet_dividing_path", "rdl_facet_flood_area", "rdl_facet_bounding_mask", "rdl_facet_grid",
     "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
@@ -176,6 +178,14 @@ def lib():
     L.rdl_iuwt_smooth.argtypes = [vp, vp, vp, u64, u64, C.c_int32, C.c_int32, vp]
     L.rdl_iuwt_decompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
     L.rdl_iuwt_recompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp, vp]
+    i32, f32, pu64 = C.c_int32, C.c_float, C.POINTER(u64)
+    L.rdl_iuwt_select_structures.argtypes = [vp, vp, vp, u64, u64, i32, C.POINTER(f32), i32, i32,
+                                             f32, vp, pu64, vp]
+    L.rdl_iuwt_floodfill.argtypes = [vp, vp, vp, u64, u64, i32, C.POINTER(f32), i32, i32, u64, u64,
+                                     i32, f32, vp, pu64, vp]
+    L.rdl_iuwt_floodfill_2d.argtypes = [vp, vp, vp, u64, u64, f32, i32, u64, u64, pu64, vp]
+    L.rdl_iuwt_mad.argtypes = [vp, vp, u64, C.POINTER(f32), vp]
+    L.rdl_iuwt_max_abs.argtypes = [vp, vp, u64, u64, f32, i32, vp, C.POINTER(f32), pu64, pu64, vp]
     L.rdl_convolution_size.argtypes = [C.c_double, u64, C.c_double]
     L.rdl_convolution_size.restype = u64
     L.rdl_version.restype = C.c_char_p
@@ -510,6 +520,61 @@ class DeconvolutionAlgorithm:
                                              int(include_largest),
                                              None if masks is None else masks.data_ptr(),
                                              out.data_ptr(), stream))
+
+    # IUWT structure selection (cpp/algorithms/iuwt/image_analysis.cc) and plane measurements
+    # (iuwt_deconvolution_algorithm.cc:104-167). coefficients: float32 CUDA tensor [S, H, W];
+    # masks: uint8 CUDA tensor [S, H, W], updated in place; thresholds: S host floats.
+    def iuwt_select_structures(self, coefficients, masks, thresholds, min_scale, end_scale,
+                               clean_border=0.0, prior_mask=None, stream=None):
+        """image_analysis::SelectStructures (image_analysis.cc:208-239) -> voxels added."""
+        s, h, w = coefficients.shape
+        thr = (C.c_float * s)(*[float(t) for t in thresholds])
+        area = C.c_uint64()
+        self._check(lib().rdl_iuwt_select_structures(
+            self._h, coefficients.data_ptr(), masks.data_ptr(), w, h, s, thr, min_scale, end_scale,
+            clean_border, None if prior_mask is None else prior_mask.data_ptr(), C.byref(area),
+            stream))
+        return area.value
+
+    def iuwt_floodfill(self, coefficients, masks, thresholds, min_scale, end_scale, seed,
+                       clean_border=0.0, prior_mask=None, stream=None):
+        """image_analysis::Floodfill / MaskedFloodfill (image_analysis.cc:86-206); seed =
+        (x, y, scale) -> voxels filled."""
+        s, h, w = coefficients.shape
+        thr = (C.c_float * s)(*[float(t) for t in thresholds])
+        area = C.c_uint64()
+        self._check(lib().rdl_iuwt_floodfill(
+            self._h, coefficients.data_ptr(), masks.data_ptr(), w, h, s, thr, min_scale, end_scale,
+            seed[0], seed[1], seed[2], clean_border,
+            None if prior_mask is None else prior_mask.data_ptr(), C.byref(area), stream))
+        return area.value
+
+    def iuwt_floodfill_2d(self, image, mask, threshold, seed, use_abs=False, stream=None):
+        """image_analysis::FloodFill2D (image_analysis.cc:241-333) -> pixels filled."""
+        h, w = image.shape
+        area = C.c_uint64()
+        self._check(lib().rdl_iuwt_floodfill_2d(self._h, image.data_ptr(), mask.data_ptr(), w, h,
+                                                threshold, int(use_abs), seed[0], seed[1],
+                                                C.byref(area), stream))
+        return area.value
+
+    def iuwt_mad(self, image, stream=None):
+        """IuwtDeconvolutionAlgorithm::Mad (iuwt_deconvolution_algorithm.cc:104-110)."""
+        v = C.c_float()
+        self._check(lib().rdl_iuwt_mad(self._h, image.data_ptr(), image.numel(), C.byref(v),
+                                       stream))
+        return v.value
+
+    def iuwt_max_abs(self, image, clean_border=0.0, allow_negative=True, mask=None, stream=None):
+        """GetMaxAbsWithoutMask / WithMask (iuwt_deconvolution_algorithm.cc:112-167) ->
+        (value, x, y)."""
+        h, w = image.shape
+        v, x, y = C.c_float(), C.c_uint64(), C.c_uint64()
+        self._check(lib().rdl_iuwt_max_abs(self._h, image.data_ptr(), w, h, clean_border,
+                                           int(allow_negative),
+                                           None if mask is None else mask.data_ptr(), C.byref(v),
+                                           C.byref(x), C.byref(y), stream))
+        return v.value, x.value, y.value
 
 
 def GenericClean(use_sub_minor_optimization: bool = True, **kw) -> DeconvolutionAlgorithm:

@@ -688,6 +688,75 @@ rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, u
   });
 }
 
+rdl_status rdl_iuwt_select_structures(rdl_handle* h, const float* device_coefficients,
+                                      uint8_t* device_masks, uint64_t width, uint64_t height,
+                                      int32_t n_scales, const float* thresholds, int32_t min_scale,
+                                      int32_t end_scale, float clean_border,
+                                      const uint8_t* device_prior_mask, uint64_t* area_size,
+                                      void* stream_v) {
+  if (!h || !device_coefficients || !device_masks || !thresholds || !area_size)
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    *area_size = IuwtSelectStructures(*h, device_coefficients, device_masks, width, height,
+                                      n_scales, thresholds, min_scale, end_scale, clean_border,
+                                      device_prior_mask, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_floodfill(rdl_handle* h, const float* device_coefficients,
+                              uint8_t* device_masks, uint64_t width, uint64_t height,
+                              int32_t n_scales, const float* thresholds, int32_t min_scale,
+                              int32_t end_scale, uint64_t seed_x, uint64_t seed_y,
+                              int32_t seed_scale, float clean_border,
+                              const uint8_t* device_prior_mask, uint64_t* area_size,
+                              void* stream_v) {
+  if (!h || !device_coefficients || !device_masks || !thresholds || !area_size)
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    *area_size = IuwtFloodfill(*h, device_coefficients, device_masks, width, height, n_scales,
+                               thresholds, min_scale, end_scale, seed_x, seed_y, seed_scale,
+                               clean_border, device_prior_mask, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_floodfill_2d(rdl_handle* h, const float* device_image, uint8_t* device_mask,
+                                 uint64_t width, uint64_t height, float threshold, int32_t use_abs,
+                                 uint64_t seed_x, uint64_t seed_y, uint64_t* area_size,
+                                 void* stream_v) {
+  if (!h || !device_image || !device_mask || !area_size) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    *area_size = IuwtFloodfill2D(*h, device_image, device_mask, width, height, threshold,
+                                 use_abs != 0, seed_x, seed_y, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_mad(rdl_handle* h, const float* device_image, uint64_t n, float* mad,
+                        void* stream_v) {
+  if (!h || !device_image || !mad) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    *mad = IuwtMad(*h, device_image, n, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_iuwt_max_abs(rdl_handle* h, const float* device_image, uint64_t width,
+                            uint64_t height, float clean_border, int32_t allow_negative,
+                            const uint8_t* device_mask, float* value, uint64_t* x, uint64_t* y,
+                            void* stream_v) {
+  if (!h || !device_image || !value || !x || !y) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    size_t px = 0, py = 0;
+    *value = IuwtMaxAbs(*h, device_image, width, height, clean_border, allow_negative != 0,
+                        device_mask, px, py, StreamOf(h, stream_v));
+    *x = px;
+    *y = py;
+  });
+}
+
 uint64_t rdl_good_fft_size(uint64_t minimum_size) { return CalculateGoodFFTSize(minimum_size); }
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding) {
   return GetConvolutionSize(convolution_scale, original_size, padding);

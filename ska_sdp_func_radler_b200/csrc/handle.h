@@ -170,6 +170,8 @@ struct rdl_handle {
   rdl::DeviceBuffer<float> fft_scratch, small_kernel;
   rdl::DeviceBuffer<float2> fft_spectrum;
   rdl::DeviceBuffer<float> iuwt_a, iuwt_b;  // IUWT ping-pong planes
+  rdl::DeviceBuffer<uint8_t> iuwt_state;    // flood-fill state volume (iuwt_analysis.cu)
+  rdl::DeviceBuffer<unsigned long long> iuwt_scalars;  // counters, histogram, arg-max key
   // facet run state: per-facet clones and geometry (not cloned)
   std::unique_ptr<rdl::ParallelState, rdl::ParallelStateDeleter> parallel;
   // row-sharded multi-GPU loop (not cloned)
