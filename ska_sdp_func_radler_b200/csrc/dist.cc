@@ -18,6 +18,8 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
                             cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -42,6 +44,7 @@ const NcclApi& Api() {
     api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
     api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
   });
   if (!error.empty()) throw CudaError(error);
@@ -86,6 +89,13 @@ void NcclAllGatherBytes(DistContext& ctx, const void* send, void* recv, size_t b
   Check(Api().AllGather(send, recv, bytes_per_rank, ncclChar, static_cast<ncclComm_t>(ctx.comm),
                         stream),
         "ncclAllGather");
+}
+
+void NcclAllReduceSumFloat(DistContext& ctx, float* data, size_t count, cudaStream_t stream) {
+  if (!ctx.comm) throw std::invalid_argument("rdl_dist_init was not called on this handle");
+  Check(Api().AllReduce(data, data, count, ncclFloat, ncclSum, static_cast<ncclComm_t>(ctx.comm),
+                        stream),
+        "ncclAllReduce");
 }
 
 }  // namespace rdl

@@ -1,7 +1,10 @@
-// Multi-GPU plumbing of the row-sharded Hogbom loop: NCCL (over NVLink / NVSwitch) is loaded at
-// run time, so single-GPU users carry no NCCL dependency. One process per GPU; the only exchange
-// of the path is the joined arg-max: an all-gather of one DistCandidate (264 bytes) per rank per
-// minor iteration.
+// Multi-GPU plumbing: NCCL (over NVLink / NVSwitch) is loaded at run time, so single-GPU users
+// carry no NCCL dependency. One process per GPU.
+//   row-sharded Hogbom loop: the only exchange is the joined arg-max, an all-gather of one
+//     DistCandidate (264 bytes) per rank per minor iteration;
+//   facet-sharded ParallelDeconvolution: an all-gather of the facet results after each of the two
+//     passes (24 bytes per facet) and one in-place sum of the residual / model cubes at the end,
+//     in which every pixel has exactly one non-zero contributor.
 #ifndef RDL_DIST_H_
 #define RDL_DIST_H_
 
@@ -28,6 +31,9 @@ void NcclInit(DistContext& ctx, const uint8_t id[kUniqueIdBytes], int rank, int 
 void NcclDestroy(DistContext& ctx);
 void NcclAllGatherBytes(DistContext& ctx, const void* send, void* recv, size_t bytes_per_rank,
                         cudaStream_t stream);
+
+// In-place sum over the ranks.
+void NcclAllReduceSumFloat(DistContext& ctx, float* data, size_t count, cudaStream_t stream);
 
 }  // namespace rdl
 #endif

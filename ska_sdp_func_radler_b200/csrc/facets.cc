@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <limits>
 #include <queue>
 #include <stdexcept>
 #include <thread>
@@ -36,12 +37,101 @@ void FillStrip(float* output, const Axes& at, size_t lo, size_t hi, size_t n_pri
     for (size_t lat = lo; lat != hi; ++lat) output[at(lat, prim)] = v;
 }
 
+// The same path without a priority queue, when it is unique. The queue pops steps in order of
+// distance, so a cell is settled by its cheapest incoming step: dist(c) = |image(c)| + min over
+// the cells that can step to c (the three cells of the previous row and the two lateral
+// neighbours). Costs are non-negative and float addition is monotone, so the lateral part of a
+// path runs in one direction and the minimum over a row is two running sweeps whose sums are
+// accumulated in path order, i.e. to the very same floats the queue arrives at. The queue's
+// insertion history only matters where two incoming steps tie; the walk back from the exit
+// checks that at every cell and gives up (returns false) on the first tie or non-finite value,
+// and the caller then runs the queue.
+bool UniqueDividingPath(const float* image, float* output, const Axes& at, size_t lo, size_t hi,
+                        size_t n_prim) {
+  const size_t span = hi - lo;
+  const float inf = std::numeric_limits<float>::infinity();
+  std::vector<float> dist(span * n_prim), entry(span), cost(span), back(span);
+  for (size_t prim = 0; prim != n_prim; ++prim) {
+    float* d = &dist[prim * span];
+    const float* prev = d - span;
+    for (size_t i = 0; i != span; ++i) {
+      cost[i] = std::fabs(image[at(lo + i, prim)]);
+      if (!std::isfinite(cost[i])) return false;
+      if (prim == 0) {
+        entry[i] = 0.0f;
+      } else {
+        float e = prev[i];
+        if (i > 0) e = std::min(e, prev[i - 1]);
+        if (i + 1 < span) e = std::min(e, prev[i + 1]);
+        entry[i] = e;
+      }
+    }
+    d[0] = entry[0] + cost[0];
+    for (size_t i = 1; i != span; ++i) d[i] = std::min(entry[i], d[i - 1]) + cost[i];
+    back[span - 1] = entry[span - 1] + cost[span - 1];
+    for (size_t i = span - 1; i-- != 0;) back[i] = std::min(entry[i], back[i + 1]) + cost[i];
+    for (size_t i = 0; i != span; ++i) d[i] = std::min(d[i], back[i]);
+  }
+  // the exit: the cheapest cell of the last row
+  const float* last = &dist[(n_prim - 1) * span];
+  size_t lat = 0, ties = 0;
+  float best = inf;
+  for (size_t i = 0; i != span; ++i) {
+    if (last[i] < best) {
+      best = last[i];
+      lat = i;
+      ties = 1;
+    } else if (last[i] == best) {
+      ++ties;
+    }
+  }
+  if (ties != 1 || !std::isfinite(best)) return false;
+  std::vector<uint32_t> path_lat(n_prim + span * 2);
+  std::vector<uint32_t> path_prim(path_lat.size());
+  size_t n_path = 0, prim = n_prim - 1;
+  while (prim > 0) {
+    if (n_path == path_lat.size()) {
+      path_lat.resize(n_path * 2);
+      path_prim.resize(n_path * 2);
+    }
+    path_lat[n_path] = uint32_t(lat);
+    path_prim[n_path++] = uint32_t(prim);
+    const float* d = &dist[prim * span];
+    const float* prev = d - span;
+    // the five cells that can step here; the cheapest of them did, if it is alone
+    const size_t cand_lat[5] = {lat, lat - 1, lat + 1, lat - 1, lat + 1};
+    const bool cand_prev[5] = {true, true, true, false, false};
+    float low = inf;
+    size_t low_k = 0, low_n = 0;
+    for (size_t k = 0; k != 5; ++k) {
+      const size_t cl = cand_lat[k];
+      if (cl >= span) continue;  // also catches lat - 1 below zero
+      const float v = cand_prev[k] ? prev[cl] : d[cl];
+      if (v < low) {
+        low = v;
+        low_k = k;
+        low_n = 1;
+      } else if (v == low) {
+        ++low_n;
+      }
+    }
+    if (low_n != 1) return false;
+    lat = cand_lat[low_k];
+    if (cand_prev[low_k]) --prim;
+  }
+  FillStrip(output, at, lo, hi, n_prim, 0.0f);
+  for (size_t k = 0; k != n_path; ++k) output[at(lo + path_lat[k], path_prim[k])] = 1.0f;
+  output[at(lo + lat, 0)] = 1.0f;
+  return true;
+}
+
 }  // namespace
 
 void DividingPath(const float* image, float* output, size_t width, size_t height, size_t lo,
                   size_t hi, bool vertical) {
   if (hi <= lo) throw std::invalid_argument("empty divider strip");
   const Axes at{width, vertical};
+  if (UniqueDividingPath(image, output, at, lo, hi, vertical ? height : width)) return;
   const size_t n_prim = vertical ? height : width;
   const size_t span = hi - lo;
   std::priority_queue<Step> queue;
@@ -172,7 +262,10 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
   if (grid_width == 0 || grid_height == 0 || grid_width > width || grid_height > height)
     throw std::invalid_argument("bad facet grid");
   const size_t avg_w = width / grid_width, avg_h = height / grid_height;
-  std::vector<float> dividers(width * height, 0.0f);
+  // The reference computes the vertical dividers, floods the columns, zeroes the divider image
+  // and then computes the horizontal ones. The searches only read `image` and write disjoint
+  // strips, so all of them run at once here, into one image per orientation.
+  std::vector<float> dividers(width * height, 0.0f), dividers_h(width * height, 0.0f);
   std::vector<uint8_t> scratch_mask(width * height);
 
   struct Column {
@@ -180,11 +273,17 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
     size_t x = 0, width = 0;
   };
   std::vector<Column> columns(grid_width);
-  // vertical dividers: each searched inside the middle half of the strip between two facets;
-  // the strips are disjoint, so the dividers can be computed concurrently in one image
-  RunOnThreads(1, grid_width, [&](size_t d) {
-    const size_t mid = width * d / grid_width;
-    DividingPath(image, dividers.data(), width, height, mid - avg_w / 4, mid + avg_w / 4, true);
+  const size_t n_vertical = grid_width - 1, n_dividers = n_vertical + grid_height - 1;
+  RunOnThreads(0, n_dividers, [&](size_t k) {
+    if (k < n_vertical) {
+      // each divider is searched inside the middle half of the strip between two facets
+      const size_t mid = width * (k + 1) / grid_width;
+      DividingPath(image, dividers.data(), width, height, mid - avg_w / 4, mid + avg_w / 4, true);
+    } else {
+      const size_t mid = height * (k - n_vertical + 1) / grid_height;
+      DividingPath(image, dividers_h.data(), width, height, mid - avg_h / 4, mid + avg_h / 4,
+                   false);
+    }
   });
   for (size_t d = 0; d != grid_width; ++d) {
     Column& c = columns[d];
@@ -193,11 +292,8 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
     c.mask.resize(c.width * height);
     CropBox(c.mask.data(), c.x, 0, c.width, height, scratch_mask.data(), width);
   }
-  std::fill(dividers.begin(), dividers.end(), 0.0f);
-  RunOnThreads(1, grid_height, [&](size_t d) {
-    const size_t mid = height * d / grid_height;
-    DividingPath(image, dividers.data(), width, height, mid - avg_h / 4, mid + avg_h / 4, false);
-  });
+  dividers.swap(dividers_h);
+  std::vector<float>().swap(dividers_h);
 
   std::vector<uint8_t> bounding(width * height);
   std::vector<Facet> facets;

@@ -49,6 +49,24 @@ __global__ void PlaceKernel(float* frame, size_t frame_width, size_t x, size_t y
   }
 }
 
+// owned[box at (x, y)] = value where the facet's boundary mask is set
+__global__ void MarkOwnedKernel(uint8_t* owned, size_t frame_width, size_t x, size_t y, size_t w,
+                                size_t h, const uint8_t* mask, uint8_t value) {
+  const size_t n = w * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t row = i / w, col = i - row * w;
+    if (mask[i]) owned[(y + row) * frame_width + x + col] = value;
+  }
+}
+
+// zero what other ranks own, so that the sum over the ranks picks every pixel from its owner
+__global__ void KeepOwnedKernel(float* image, const uint8_t* owned, size_t n) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    if (!owned[i]) image[i] = 0.0f;
+}
+
 int GridFor(size_t n) { return int(std::min<size_t>((n + kThreads - 1) / kThreads, kSmCount * 8)); }
 
 }  // namespace
@@ -59,6 +77,9 @@ struct ParallelState {
   std::vector<Facet> facets;            // geometry + results of the last call
   DeviceBuffer<float> integrated, result_model, sub_residual, sub_model, sub_model_start, sub_psf;
   DeviceBuffer<uint8_t> boundary_mask;
+  // facet-sharded run over several GPUs (facet i belongs to rank i % world)
+  std::vector<uint64_t> iterations;  // IterationNumber() of every facet's algorithm, all ranks
+  DeviceBuffer<uint8_t> owned, wire_send, wire_recv;
   ~ParallelState() {
     for (rdl_handle* a : algorithms) rdl_destroy(a);
   }
@@ -174,6 +195,75 @@ void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
   RDL_CUDA(cudaGetLastError());
 }
 
+// What the ranks tell each other about a facet after a pass.
+struct FacetWire {
+  double peak;
+  uint64_t iteration;
+  int32_t reached_major_threshold;
+  int32_t pad;
+};
+
+// Every rank learns the results of the facets the other ranks ran (a no-op on one GPU apart from
+// recording the iteration numbers). Rank r sends its facets r, r + world, ... in that order.
+void ExchangeFacetResults(rdl_handle& h, ParallelState& st, cudaStream_t stream) {
+  const size_t n_facets = st.facets.size();
+  const size_t world = h.dist.comm ? size_t(h.dist.world) : 1, rank = h.dist.comm ? size_t(h.dist.rank) : 0;
+  for (const Facet& f : st.facets)
+    if (f.index % world == rank) st.iterations[f.index] = st.algorithms[f.index]->iteration_number;
+  if (world == 1) return;
+  const size_t per = (n_facets + world - 1) / world;
+  std::vector<FacetWire> send(per, FacetWire{}), recv(per * world);
+  for (const Facet& f : st.facets)
+    if (f.index % world == rank)
+      send[f.index / world] = FacetWire{f.peak, st.iterations[f.index], f.reached_major_threshold ? 1 : 0, 0};
+  st.wire_send.Reserve(per * sizeof(FacetWire));
+  st.wire_recv.Reserve(per * world * sizeof(FacetWire));
+  RDL_CUDA(cudaMemcpyAsync(st.wire_send.get(), send.data(), per * sizeof(FacetWire),
+                           cudaMemcpyHostToDevice, stream));
+  NcclAllGatherBytes(h.dist, st.wire_send.get(), st.wire_recv.get(), per * sizeof(FacetWire), stream);
+  RDL_CUDA(cudaMemcpyAsync(recv.data(), st.wire_recv.get(), per * world * sizeof(FacetWire),
+                           cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+  for (Facet& f : st.facets) {
+    const FacetWire& w = recv[(f.index % world) * per + f.index / world];
+    f.peak = w.peak;
+    f.reached_major_threshold = w.reached_major_threshold != 0;
+    st.iterations[f.index] = w.iteration;
+  }
+}
+
+// After pass 2 every rank holds the new residual in the pixels its facets own and the model of
+// its facets in result_model. Each rank zeroes the residual pixels that belong to facets of other
+// ranks (rank 0 keeps the pixels no facet owns), then both cubes are summed over the ranks: every
+// residual pixel has exactly one non-zero contributor, so the sum reproduces it exactly.
+void MergeOverRanks(rdl_handle& h, ParallelState& st, DeviceCube& cube, cudaStream_t stream) {
+  const size_t W = cube.width, A = cube.Pixels();
+  const size_t world = size_t(h.dist.world), rank = size_t(h.dist.rank);
+  st.owned.Reserve(A);
+  RDL_CUDA(cudaMemsetAsync(st.owned.get(), rank == 0 ? 1 : 0, A, stream));
+  for (const Facet& f : st.facets) {
+    const bool is_mine = f.index % world == rank;
+    if (is_mine == (rank == 0)) continue;  // rank 0 clears the others' pixels, the rest set their own
+    const size_t n = f.width * f.height;
+    st.boundary_mask.Reserve(n);
+    RDL_CUDA(cudaMemcpyAsync(st.boundary_mask.get(), f.boundary_mask.data(), n,
+                             cudaMemcpyHostToDevice, stream));
+    MarkOwnedKernel<<<GridFor(n), kThreads, 0, stream>>>(st.owned.get(), W, f.x, f.y, f.width,
+                                                         f.height, st.boundary_mask.get(),
+                                                         is_mine ? 1 : 0);
+    // the staging buffer is reused by the next facet
+    RDL_CUDA(cudaStreamSynchronize(stream));
+    ++h.launches;
+  }
+  for (size_t i = 0; i != cube.n_images; ++i) {
+    KeepOwnedKernel<<<GridFor(A), kThreads, 0, stream>>>(cube.residual.p[i], st.owned.get(), A);
+    ++h.launches;
+    NcclAllReduceSumFloat(h.dist, cube.residual.p[i], A, stream);
+  }
+  NcclAllReduceSumFloat(h.dist, st.result_model.get(), cube.n_images * A, stream);
+  RDL_CUDA(cudaGetLastError());
+}
+
 }  // namespace
 
 rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_t grid_height,
@@ -210,6 +300,7 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
     st.facets[0].width = cube.width;
     st.facets[0].height = cube.height;
     st.facets[0].peak = r.final_peak_value;
+    st.iterations.assign(1, a.iteration_number);
     return r;
   }
   if (h.track_per_scale_masks || h.use_per_scale_masks)
@@ -231,16 +322,26 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
                          grid_height);
   std::vector<float>().swap(integrated);
 
+  // several GPUs: facet i is run by rank i % world on that rank's copy of the cube
+  const int world = h.dist.comm ? h.dist.world : 1, rank = h.dist.comm ? h.dist.rank : 0;
+  auto mine = [&](const Facet& f) { return int(f.index % size_t(world)) == rank; };
+  st.iterations.assign(n_facets, 0);
+
   st.result_model.Reserve(cube.n_images * A);
   RDL_CUDA(cudaMemsetAsync(st.result_model.get(), 0, cube.n_images * A * sizeof(float), stream));
   // pass 1: every facet reports its peak (max_iterations = 0)
-  for (Facet& f : st.facets) RunFacet(h, st, f, cube, 0.0, true, stream);
+  for (Facet& f : st.facets)
+    if (mine(f)) RunFacet(h, st, f, cube, 0.0, true, stream);
+  ExchangeFacetResults(h, st, stream);
   double start_peak = 0.0;
   for (const Facet& f : st.facets)
     if (f.peak > start_peak) start_peak = f.peak;  // signed, like the reference (:592-599)
   const double threshold = start_peak * (1.0 - double(h.settings.major_loop_gain));
   // pass 2: deconvolve every facet down to the common major-iteration threshold
-  for (Facet& f : st.facets) RunFacet(h, st, f, cube, threshold, false, stream);
+  for (Facet& f : st.facets)
+    if (mine(f)) RunFacet(h, st, f, cube, threshold, false, stream);
+  ExchangeFacetResults(h, st, stream);
+  if (world > 1) MergeOverRanks(h, st, cube, stream);
   // model_image.SetImages(resultModel)
   for (size_t i = 0; i != cube.n_images; ++i)
     RDL_CUDA(cudaMemcpyAsync(cube.model.p[i], st.result_model.get() + i * A, A * sizeof(float),
@@ -252,8 +353,7 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
   double end_peak = 0.0;
   for (const Facet& f : st.facets) {
     if (!f.reached_major_threshold) ++finished;
-    const rdl_handle& a = *st.algorithms[f.index];
-    if (a.iteration_number >= a.settings.max_iterations) reached_max_iterations = true;
+    if (st.iterations[f.index] >= h.settings.max_iterations) reached_max_iterations = true;
     end_peak = std::max(end_peak, f.peak);
   }
   rdl_result r{};
@@ -262,7 +362,7 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
   r.final_peak_value = float(end_peak);
   r.another_iteration_required = (finished != st.facets.size()) && !reached_max_iterations;
   r.is_diverging = 0;
-  h.iteration_number = st.algorithms.front()->iteration_number;
+  h.iteration_number = st.iterations.front();
   r.iteration_number = h.iteration_number;
   return r;
 }
@@ -272,8 +372,7 @@ size_t ParallelFacetCount(const rdl_handle& h) { return h.parallel ? h.parallel-
 FacetInfo ParallelFacet(const rdl_handle& h, size_t i) {
   if (!h.parallel || i >= h.parallel->facets.size()) throw std::invalid_argument("no such facet");
   const Facet& f = h.parallel->facets[i];
-  const uint64_t it =
-      i < h.parallel->algorithms.size() ? h.parallel->algorithms[i]->iteration_number : 0;
+  const uint64_t it = i < h.parallel->iterations.size() ? h.parallel->iterations[i] : 0;
   return FacetInfo{f.x, f.y, f.width, f.height, f.peak, f.reached_major_threshold ? 1 : 0, it};
 }
 

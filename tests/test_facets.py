@@ -78,6 +78,32 @@ def test_dividing_paths_match_reference_source():
 
 
 @needs_ref
+def test_long_unique_paths_match_reference_source():
+    """Real-valued images have no exact ties, so the product takes its queue-free route
+    (facets.cc UniqueDividingPath); the path must still be the reference's, pixel for pixel."""
+    rng = np.random.default_rng(21)
+    noise = rng.standard_normal((700, 900)).astype(np.float32)
+    yy, xx = np.mgrid[0:512, 0:640]
+    smooth = (np.sin(xx / 37.0) * np.cos(yy / 53.0)
+              + 0.01 * rng.standard_normal((512, 640))).astype(np.float32)
+    for img in (noise, smooth):
+        h, w = img.shape
+        for (lo, hi, vertical) in [(w // 4, 3 * w // 4, True), (h // 4, 3 * h // 4, False),
+                                   (0, w, True), (10, 13, False)]:
+            got = rdl.facet_dividing_path(img, lo, hi, vertical)
+            assert np.array_equal(got, ref_divide(img, lo, hi, vertical)), (img.shape, lo, hi, vertical)
+    # a strip with a few exact ties inside an otherwise real-valued image: queue route
+    tied = noise.copy()
+    tied[100:140, 300:500] = 0.0
+    got = rdl.facet_dividing_path(tied, 250, 550, True)
+    assert np.array_equal(got, ref_divide(tied, 250, 550, True))
+    bad = noise.copy()
+    bad[50, 400] = np.inf
+    got = rdl.facet_dividing_path(bad, 250, 550, True)
+    assert np.array_equal(got, ref_divide(bad, 250, 550, True))
+
+
+@needs_ref
 def test_flood_and_bounding_mask_match_reference_source():
     L = oracle.ref_lib()
     u64 = C.c_uint64

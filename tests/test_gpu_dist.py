@@ -73,3 +73,21 @@ def test_two_ranks_nccl_joined_argmax(torch_cuda):
                           "29517", os.path.join(HERE, "dist_hogbom_check.py")],
                          capture_output=True, text=True, timeout=900)
     assert "DIST-OK 2" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_facets_single_rank_dist_context_is_identical(torch_cuda):
+    """world = 1: the facet-sharded code path (exchange + bookkeeping) must not change anything."""
+    out = subprocess.run([sys.executable, os.path.join(HERE, "dist_facets_check.py")],
+                         capture_output=True, text=True, timeout=600)
+    assert "FACETS-OK 1" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_two_ranks_facets_sharded(torch_cuda):
+    torch = torch_cuda
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run tests/dist_facets_check.py under torchrun with gpurun --gpus 2)")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                          "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",
+                          "29519", os.path.join(HERE, "dist_facets_check.py")],
+                         capture_output=True, text=True, timeout=900)
+    assert "FACETS-OK 2" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
