@@ -96,9 +96,11 @@ EXPORTED_SYMBOLS = [
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
+    "rdl_parallel_timing",
     "rdl_facet_dividing_path", "rdl_facet_flood_area", "rdl_facet_bounding_mask", "rdl_facet_grid",
     "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
     "rdl_dist_finalize",
+    "rdl_release_cached_memory",
     "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
     "rdl_device_count",
 ]
@@ -166,6 +168,7 @@ def lib():
     L.rdl_parallel_facet_count.argtypes = [vp]
     L.rdl_parallel_facet_count.restype = u64
     L.rdl_parallel_facet_get.argtypes = [vp, u64, C.POINTER(_FacetInfo), vp]
+    L.rdl_parallel_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.rdl_facet_dividing_path.argtypes = [vp, vp, u64, u64, u64, u64, i32]
     L.rdl_facet_flood_area.argtypes = [vp, u64, u64, u64, i32, vp, C.POINTER(u64), C.POINTER(u64)]
     L.rdl_facet_bounding_mask.argtypes = [vp, u64, u64, vp, vp, u64, u64, vp]
@@ -423,6 +426,12 @@ class DeconvolutionAlgorithm:
         return Result(out.starting_peak_value if out.has_starting_peak else None,
                       out.final_peak_value, bool(out.another_iteration_required),
                       bool(out.is_diverging), out.iteration_number)
+
+    def parallel_timing(self):
+        """(host divider search ms, whole call ms) of the last facet run."""
+        g, t = C.c_double(), C.c_double()
+        self._check(lib().rdl_parallel_timing(self._h, C.byref(g), C.byref(t)))
+        return g.value, t.value
 
     def facets(self, with_masks: bool = False):
         """SubImage records of the last facet run."""

@@ -1,6 +1,7 @@
 // extern "C" boundary (include/radler_b200.h). Exceptions never cross it: they are
 // turned into status codes + rdl_last_error().
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -17,6 +18,7 @@ using namespace rdl;
 namespace {
 
 thread_local std::string g_create_error;
+std::atomic<long> g_live_handles{0};
 
 template <typename F>
 rdl_status Guard(rdl_handle* h, F&& f) {
@@ -157,6 +159,7 @@ rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out) {
     delete h;
     return st;
   }
+  g_live_handles.fetch_add(1);
   *out = h;
   return RDL_OK;
 }
@@ -209,7 +212,11 @@ void rdl_destroy(rdl_handle* h) {
   }
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
+  // the last handle takes the cached device memory with it
+  if (g_live_handles.fetch_sub(1) == 1) DeviceTrim();
 }
+
+void rdl_release_cached_memory(void) { DeviceTrim(); }
 
 const char* rdl_last_error(const rdl_handle* h) {
   return h ? h->error.c_str() : g_create_error.c_str();
@@ -476,6 +483,12 @@ rdl_status rdl_facet_grid(const float* image, uint64_t width, uint64_t height,
 }
 
 uint64_t rdl_parallel_facet_count(const rdl_handle* h) { return h ? ParallelFacetCount(*h) : 0; }
+
+rdl_status rdl_parallel_timing(const rdl_handle* h, double* host_geometry_ms, double* total_ms) {
+  if (!h || !host_geometry_ms || !total_ms) return RDL_ERR_INVALID_ARGUMENT;
+  ParallelTiming(*h, *host_geometry_ms, *total_ms);
+  return RDL_OK;
+}
 
 rdl_status rdl_parallel_facet_get(const rdl_handle* h, uint64_t i, rdl_facet_info* out,
                                   uint8_t* boundary_mask) {

@@ -16,6 +16,12 @@
 
 namespace rdl {
 
+// Device memory comes from a size-keyed cache (device_pool.cc): blocks of 1 MB and more are kept
+// when a buffer is released and handed out again, smaller ones go to cudaMalloc / cudaFree.
+void* DeviceAlloc(size_t bytes);  // throws CudaError("cudaMalloc(...)") when HBM is exhausted
+void DeviceFree(void* p, size_t bytes);
+void DeviceTrim();  // gives every cached block back to the driver
+
 // RAII device allocation.
 template <typename T>
 class DeviceBuffer {
@@ -39,14 +45,7 @@ class DeviceBuffer {
   void Resize(size_t n) {
     if (n == n_) return;
     Free();
-    if (n) {
-      cudaError_t e = cudaMalloc(&ptr_, n * sizeof(T));
-      if (e != cudaSuccess) {
-        ptr_ = nullptr;
-        throw CudaError(std::string("cudaMalloc(") + std::to_string(n * sizeof(T)) +
-                        " bytes): " + cudaGetErrorString(e));
-      }
-    }
+    if (n) ptr_ = static_cast<T*>(DeviceAlloc(n * sizeof(T)));
     n_ = n;
   }
   // Grow-only variant for scratch space.
@@ -54,7 +53,7 @@ class DeviceBuffer {
     if (n > n_) Resize(n);
   }
   void Free() {
-    if (ptr_) cudaFree(ptr_);
+    if (ptr_) DeviceFree(ptr_, n_ * sizeof(T));
     ptr_ = nullptr;
     n_ = 0;
   }

@@ -240,6 +240,7 @@ class MultiScaleRun {
   }
   const std::vector<rdl_scale_info>& Scales2() const { return st_.scales; }
   const float2* PsfSpectrum(size_t p, size_t si, FftConvolver& padded);
+  const float* TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum);
   void Sync() { RDL_CUDA(cudaStreamSynchronize(stream_)); }
 
   rdl_handle& h_;
@@ -254,6 +255,7 @@ class MultiScaleRun {
   std::vector<DeviceBuffer<float>> twice_convolved_, individual_convolved_;
   std::vector<DeviceBuffer<float2>> scale_spectra_;
   std::map<std::pair<size_t, size_t>, DeviceBuffer<float2>> psf_spectra_;
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float>> twice_cache_;  // [psf, scale]
   DeviceBuffer<float2> psf_spectrum_tmp_;
   DeviceBuffer<double> sumsq_;
 };
@@ -420,6 +422,29 @@ void MultiScaleRun::ActivateScales(size_t last) {  // multiscale_algorithm.cc:63
 // Spectrum of PrepareConvolutionKernel(Untrim(convolved PSF)) for CorrectResidualDirty. The
 // reference recomputes it per image and per minor iteration (subminor_loop.cc:199-202); it only
 // depends on (psf, scale), so it is cached for the duration of the call when memory allows.
+// The PSF of slot p convolved twice with the kernel of scale si (multiscale_algorithm.cc:331-343).
+// The reference recomputes it in every minor iteration that selects the scale; the PSFs do not
+// change during a call, so it is kept while HBM allows (K4: 16 PSFs x 4 scales x 268 MB).
+const float* MultiScaleRun::TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum) {
+  const auto key = std::make_pair(p, si);
+  auto it = twice_cache_.find(key);
+  if (it != twice_cache_.end()) return it->second.get();
+  size_t free_bytes = 0, total_bytes = 0;
+  RDL_CUDA(cudaMemGetInfo(&free_bytes, &total_bytes));
+  float* out = nullptr;
+  if (free_bytes > n_ * sizeof(float) * 4 + (size_t(16) << 30)) {
+    DeviceBuffer<float> buf(n_);
+    out = buf.get();
+    twice_cache_.emplace(key, std::move(buf));
+  } else {
+    twice_convolved_[p].Reserve(n_);
+    out = twice_convolved_[p].get();
+  }
+  conv_.ConvolveWith(ConvolvedPsf(p, si), width_, height_, scale_spectrum, out, width_, height_, 0,
+                     stream_);
+  return out;
+}
+
 const float2* MultiScaleRun::PsfSpectrum(size_t p, size_t si, FftConvolver& padded) {
   const auto key = std::make_pair(p, si);
   auto it = psf_spectra_.find(key);
@@ -521,17 +546,14 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     ConstPtrTable psf_per_image{}, conv_residual{};
     if (S[swp].scale != 0.0f) {
       const float2* spectrum = ScaleSpectrum(swp);
-      for (size_t p = 0; p != n_psfs; ++p) {
-        twice_convolved_[p].Reserve(n_);
-        conv_.ConvolveWith(ConvolvedPsf(p, swp), width_, height_, spectrum, twice_convolved_[p].get(),
-                           width_, height_, 0, stream_);
-      }
+      std::vector<const float*> twice(n_psfs);
+      for (size_t p = 0; p != n_psfs; ++p) twice[p] = TwiceConvolvedPsf(p, swp, spectrum);
       for (size_t i = 0; i != cube_.n_images; ++i) {
         individual_convolved_[i].Reserve(n_);
         conv_.ConvolveWith(cube_.residual.p[i], width_, height_, spectrum, individual_convolved_[i].get(),
                            width_, height_, 0, stream_);
         conv_residual.p[i] = individual_convolved_[i].get();
-        psf_per_image.p[i] = twice_convolved_[cube_.PsfIndex(i)].get();
+        psf_per_image.p[i] = twice[cube_.PsfIndex(i)];
       }
       h.launches += conv_.TakeLaunchCount();
     } else {

@@ -11,6 +11,7 @@
 #include "parallel.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <stdexcept>
 
@@ -67,6 +68,10 @@ __global__ void KeepOwnedKernel(float* image, const uint8_t* owned, size_t n) {
     if (!owned[i]) image[i] = 0.0f;
 }
 
+double MsSince(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
 int GridFor(size_t n) { return int(std::min<size_t>((n + kThreads - 1) / kThreads, kSmCount * 8)); }
 
 }  // namespace
@@ -79,6 +84,7 @@ struct ParallelState {
   DeviceBuffer<uint8_t> boundary_mask;
   // facet-sharded run over several GPUs (facet i belongs to rank i % world)
   std::vector<uint64_t> iterations;  // IterationNumber() of every facet's algorithm, all ranks
+  double geometry_ms = 0.0, total_ms = 0.0;  // host divider search / whole last call
   DeviceBuffer<uint8_t> owned, wire_send, wire_recv;
   ~ParallelState() {
     for (rdl_handle* a : algorithms) rdl_destroy(a);
@@ -269,6 +275,7 @@ void MergeOverRanks(rdl_handle& h, ParallelState& st, DeviceCube& cube, cudaStre
 rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_t grid_height,
                        cudaStream_t stream) {
   if (grid_width == 0 || grid_height == 0) throw std::invalid_argument("empty facet grid");
+  const auto call_start = std::chrono::steady_clock::now();
   if (h.dist.band_set) throw std::domain_error("facets of a row-sharded cube are not supported");
   if (!h.parallel) h.parallel.reset(new ParallelState);
   ParallelState& st = *h.parallel;
@@ -317,9 +324,11 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
   RDL_CUDA(cudaMemcpyAsync(integrated.data(), st.integrated.get(), A * sizeof(float),
                            cudaMemcpyDeviceToHost, stream));
   RDL_CUDA(cudaStreamSynchronize(stream));
+  const auto geometry_start = std::chrono::steady_clock::now();
   st.facets = MakeFacets(integrated.data(), W, H,
                          h.mask_host.empty() ? nullptr : h.mask_host.data(), grid_width,
                          grid_height);
+  st.geometry_ms = MsSince(geometry_start);
   std::vector<float>().swap(integrated);
 
   // several GPUs: facet i is run by rank i % world on that rank's copy of the cube
@@ -364,7 +373,13 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
   r.is_diverging = 0;
   h.iteration_number = st.iterations.front();
   r.iteration_number = h.iteration_number;
+  st.total_ms = MsSince(call_start);
   return r;
+}
+
+void ParallelTiming(const rdl_handle& h, double& geometry_ms, double& total_ms) {
+  geometry_ms = h.parallel ? h.parallel->geometry_ms : 0.0;
+  total_ms = h.parallel ? h.parallel->total_ms : 0.0;
 }
 
 size_t ParallelFacetCount(const rdl_handle& h) { return h.parallel ? h.parallel->facets.size() : 0; }

@@ -21,6 +21,8 @@ size_t ParallelFacetCount(const rdl_handle& h);
 FacetInfo ParallelFacet(const rdl_handle& h, size_t i);
 // host copy of a facet's boundary mask (width * height bytes)
 const std::vector<uint8_t>& ParallelFacetBoundaryMask(const rdl_handle& h, size_t i);
+// wall-clock split of the last facet run: host divider search, whole call (milliseconds)
+void ParallelTiming(const rdl_handle& h, double& geometry_ms, double& total_ms);
 
 }  // namespace rdl
 #endif

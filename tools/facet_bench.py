@@ -54,10 +54,7 @@ for rep in range(2):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         wall = float(t)
     facets = alg.facets()
-    host = res0[0].cpu().numpy()
-    t1 = time.perf_counter()
-    rdl.facet_grid(host, g, g)
-    geom = time.perf_counter() - t1
+    geom = alg.parallel_timing()[0] * 1e-3  # this rank's divider search inside the call
     if rank == 0:
       print(json.dumps({"n": n, "grid": g, "n_gpus": world, "rep": rep, "wall_ms": wall * 1e3,
                       "residual_checksum": float(res.double().abs().sum()),
