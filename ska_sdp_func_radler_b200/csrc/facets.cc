@@ -10,19 +10,11 @@
 #include <cfloat>
 #include <cmath>
 #include <limits>
-#include <queue>
 #include <stdexcept>
 #include <thread>
 
 namespace rdl {
 namespace {
-
-struct Step {
-  float distance;
-  uint32_t lat, prim;            // cell to visit
-  uint32_t from_lat, from_prim;  // cell we came from
-  bool operator<(const Step& rhs) const { return distance > rhs.distance; }  // min-heap
-};
 
 struct Axes {
   size_t width;
@@ -127,55 +119,104 @@ bool UniqueDividingPath(const float* image, float* output, const Axes& at, size_
 
 }  // namespace
 
-void DividingPath(const float* image, float* output, size_t width, size_t height, size_t lo,
-                  size_t hi, bool vertical) {
-  if (hi <= lo) throw std::invalid_argument("empty divider strip");
-  const Axes at{width, vertical};
-  if (UniqueDividingPath(image, output, at, lo, hi, vertical ? height : width)) return;
-  const size_t n_prim = vertical ? height : width;
+namespace {
+
+// The reference's walk (dijkstra_splitter.cc:34-121 / 123-205) with the same queue discipline:
+// std::priority_queue is push_heap / pop_heap on a vector, and the comparator only looks at the
+// distance, so a heap of compact steps goes through exactly the same sequence of moves and
+// breaks equal-distance ties exactly like the reference's queue of (distance, x, y, prev_x,
+// prev_y) records. A step is 8 bytes here: the distance, and the target cell of the strip
+// (prim * span + lat) with the direction it was entered from in the low 3 bits. Costs and
+// distances live in dense strip-local arrays, so the horizontal search does not stride through
+// the frame.
+struct CompactStep {
+  float distance;
+  uint32_t code;
+  bool operator<(const CompactStep& rhs) const { return distance > rhs.distance; }  // min-heap
+};
+
+// where a step came from, relative to its target (lat, prim)
+enum From : uint32_t {
+  kFromHigherLatPrevPrim = 0,  // pushed as (s.lat - 1, s.prim + 1)
+  kFromHigherLatSamePrim = 1,  // pushed as (s.lat - 1, s.prim)
+  kFromSameLatPrevPrim = 2,    // pushed as (s.lat, s.prim + 1)
+  kFromLowerLatPrevPrim = 3,   // pushed as (s.lat + 1, s.prim + 1)
+  kFromLowerLatSamePrim = 4,   // pushed as (s.lat + 1, s.prim)
+  kFromItself = 5              // the seeds of the first row
+};
+
+void StepBack(uint32_t from, size_t& lat, size_t& prim) {
+  switch (from) {
+    case kFromHigherLatPrevPrim: ++lat; --prim; break;
+    case kFromHigherLatSamePrim: ++lat; break;
+    case kFromSameLatPrevPrim: --prim; break;
+    case kFromLowerLatPrevPrim: --lat; --prim; break;
+    case kFromLowerLatSamePrim: --lat; break;
+    default: break;
+  }
+}
+
+void QueueDividingPath(const float* image, float* output, const Axes& at, size_t lo, size_t hi,
+                       size_t n_prim) {
   const size_t span = hi - lo;
-  std::priority_queue<Step> queue;
-  for (size_t lat = lo; lat != hi; ++lat)
-    queue.push(Step{0.0f, uint32_t(lat), 0u, uint32_t(lat), 0u});
-  std::vector<uint32_t> back_lat(span * n_prim), back_prim(span * n_prim);
-  FillStrip(output, at, lo, hi, n_prim, FLT_MAX);
-  Step s{};
-  while (!queue.empty()) {
-    s = queue.top();
-    queue.pop();
-    if (s.prim == n_prim) break;  // first path to leave the far edge is the cheapest
-    const size_t cell = at(s.lat, s.prim);
-    const float reached = s.distance + std::fabs(image[cell]);
-    if (reached < output[cell]) {
-      output[cell] = reached;
-      back_lat[(s.lat - lo) + s.prim * span] = s.from_lat;
-      back_prim[(s.lat - lo) + s.prim * span] = s.from_prim;
-      Step next{reached, 0u, 0u, s.lat, s.prim};
-      auto push = [&](uint32_t lat, uint32_t prim) {
-        next.lat = lat;
-        next.prim = prim;
-        queue.push(next);
-      };
-      if (s.lat > lo) {
-        push(s.lat - 1, s.prim + 1);
-        push(s.lat - 1, s.prim);
+  if (span * (n_prim + 1) >= (size_t(1) << 29))
+    throw std::invalid_argument("divider strip too large");
+  std::vector<float> cost(span * n_prim), dist(span * n_prim, FLT_MAX);
+  std::vector<uint8_t> back(span * n_prim, uint8_t(kFromItself));
+  for (size_t prim = 0; prim != n_prim; ++prim)
+    for (size_t i = 0; i != span; ++i) cost[prim * span + i] = std::fabs(image[at(lo + i, prim)]);
+  std::vector<CompactStep> heap;
+  heap.reserve(span * 64);
+  auto push = [&heap](float distance, size_t cell, uint32_t from) {
+    heap.push_back(CompactStep{distance, uint32_t(cell << 3) | from});
+    std::push_heap(heap.begin(), heap.end());
+  };
+  for (size_t i = 0; i != span; ++i) push(0.0f, i, kFromItself);
+  size_t end_lat = 0, end_prim = 0;
+  while (!heap.empty()) {
+    const CompactStep s = heap.front();
+    std::pop_heap(heap.begin(), heap.end());
+    heap.pop_back();
+    const size_t cell = s.code >> 3, prim = cell / span, lat = cell - prim * span;
+    if (prim == n_prim) {  // first path to leave the far edge is the cheapest
+      end_lat = lat;
+      end_prim = prim;
+      StepBack(s.code & 7u, end_lat, end_prim);
+      break;
+    }
+    const float reached = s.distance + cost[cell];
+    if (reached < dist[cell]) {
+      dist[cell] = reached;
+      back[cell] = uint8_t(s.code & 7u);
+      if (lat > 0) {
+        push(reached, cell + span - 1, kFromHigherLatPrevPrim);
+        push(reached, cell - 1, kFromHigherLatSamePrim);
       }
-      push(s.lat, s.prim + 1);
-      if (s.lat + 1 < hi) {
-        push(s.lat + 1, s.prim + 1);
-        push(s.lat + 1, s.prim);
+      push(reached, cell + span, kFromSameLatPrevPrim);
+      if (lat + 1 < span) {
+        push(reached, cell + span + 1, kFromLowerLatPrevPrim);
+        push(reached, cell + 1, kFromLowerLatSamePrim);
       }
     }
   }
   FillStrip(output, at, lo, hi, n_prim, 0.0f);
-  uint32_t lat = s.from_lat, prim = s.from_prim;
+  size_t lat = end_lat, prim = end_prim;
   while (prim > 0) {
-    output[at(lat, prim)] = 1.0f;
-    const size_t k = (lat - lo) + size_t(prim) * span;
-    lat = back_lat[k];
-    prim = back_prim[k];
+    output[at(lo + lat, prim)] = 1.0f;
+    StepBack(back[prim * span + lat], lat, prim);
   }
-  output[at(lat, 0)] = 1.0f;
+  output[at(lo + lat, 0)] = 1.0f;
+}
+
+}  // namespace
+
+void DividingPath(const float* image, float* output, size_t width, size_t height, size_t lo,
+                  size_t hi, bool vertical) {
+  if (hi <= lo) throw std::invalid_argument("empty divider strip");
+  const Axes at{width, vertical};
+  const size_t n_prim = vertical ? height : width;
+  if (UniqueDividingPath(image, output, at, lo, hi, n_prim)) return;
+  QueueDividingPath(image, output, at, lo, hi, n_prim);
 }
 
 void FloodArea(const float* dividers, size_t width, size_t height, size_t inside, bool vertical,
