@@ -50,6 +50,20 @@ void DeviceTrim() {
   pool.cached_bytes = 0;
 }
 
+size_t DeviceAvailableBytes() {
+  size_t free_bytes = 0, total_bytes = 0;
+  if (cudaMemGetInfo(&free_bytes, &total_bytes) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  Pool& pool = ThePool();
+  std::lock_guard<std::mutex> guard(pool.lock);
+  const int device = CurrentDevice();
+  for (const auto& entry : pool.blocks)
+    if (entry.first.first == device) free_bytes += entry.first.second * entry.second.size();
+  return free_bytes;
+}
+
 void* DeviceAlloc(size_t bytes) {
   Pool& pool = ThePool();
   if (bytes >= kPooledFrom) {

@@ -21,6 +21,7 @@ namespace rdl {
 void* DeviceAlloc(size_t bytes);  // throws CudaError("cudaMalloc(...)") when HBM is exhausted
 void DeviceFree(void* p, size_t bytes);
 void DeviceTrim();  // gives every cached block back to the driver
+size_t DeviceAvailableBytes();  // free HBM of the current device, cached blocks included
 
 // RAII device allocation.
 template <typename T>
@@ -170,6 +171,7 @@ struct rdl_handle {
   rdl::DeviceBuffer<float2> fft_spectrum;
   rdl::DeviceBuffer<float> iuwt_a, iuwt_b;  // IUWT ping-pong planes
   rdl::DeviceBuffer<uint8_t> iuwt_state;    // flood-fill state volume (iuwt_analysis.cu)
+  rdl::DeviceBuffer<int> iuwt_due;          // flood fill: round in which a tile has to run
   rdl::DeviceBuffer<unsigned long long> iuwt_scalars;  // counters, histogram, arg-max key
   // facet run state: per-facet clones and geometry (not cloned)
   std::unique_ptr<rdl::ParallelState, rdl::ParallelStateDeleter> parallel;

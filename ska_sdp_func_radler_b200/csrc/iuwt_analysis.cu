@@ -143,10 +143,15 @@ __global__ void SeedKernel(uint8_t* state, size_t voxel) { state[voxel] = kMayFi
 // the tile plus a one-pixel halo, spreads the filled bit until the tile is stable and writes the
 // new voxels back. The moves are the reference's (image_analysis.cc:105-146): they are bounded
 // by the position of the voxel that is LEFT, which is why the tests below look at the neighbour.
+// A tile only has work in round r if it, or one of its four neighbours, filled a voxel in round
+// r - 1 (or holds the seed): due[tile] is the latest round the tile was asked to run in.
 __global__ void __launch_bounds__(kFillThreads)
-FillPropagateKernel(FillGeometry g, uint8_t* state, int s_lo, int s_hi, unsigned* changed) {
+FillPropagateKernel(FillGeometry g, uint8_t* state, int s_lo, int s_hi, unsigned* changed,
+                    int* due, int round) {
   extern __shared__ uint8_t tile[];
   constexpr int PW = kFillTX + 2, PH = kFillTY + 2;
+  const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+  if (due[tile_id] < round) return;
   const int n_s = s_hi - s_lo + 1;
   const size_t area = g.width * g.height;
   const long x0 = long(blockIdx.x) * kFillTX - 1, y0 = long(blockIdx.y) * kFillTY - 1;
@@ -192,7 +197,21 @@ FillPropagateKernel(FillGeometry g, uint8_t* state, int s_lo, int s_hi, unsigned
     if (!__syncthreads_or(grew)) break;
     wrote = true;
   }
-  if (wrote && threadIdx.x == 0) atomicAdd(changed, 1u);
+  if (wrote && threadIdx.x == 0) {
+    atomicAdd(changed, 1u);
+    atomicMax(&due[tile_id], round + 1);
+    if (blockIdx.x > 0) atomicMax(&due[tile_id - 1], round + 1);
+    if (blockIdx.x + 1 < gridDim.x) atomicMax(&due[tile_id + 1], round + 1);
+    if (blockIdx.y > 0) atomicMax(&due[tile_id - int(gridDim.x)], round + 1);
+    if (blockIdx.y + 1 < gridDim.y) atomicMax(&due[tile_id + int(gridDim.x)], round + 1);
+  }
+}
+
+// the seed's tile and its neighbours run in round 0
+__global__ void SeedTilesKernel(int* due, int tiles_x, int tiles_y, int tx, int ty) {
+  const int dx = int(threadIdx.x) - 1, dy = int(threadIdx.y) - 1;
+  const int x = tx + dx, y = ty + dy;
+  if (x >= 0 && y >= 0 && x < tiles_x && y < tiles_y) due[y * tiles_x + x] = 0;
 }
 
 // masks |= filled; count the filled voxels (the seed included, image_analysis.cc:101-104)
@@ -301,11 +320,17 @@ uint64_t RunFill(rdl_handle& h, const FillGeometry& g, const float* coefficients
   // rounds are launched in batches; each round has its own change counter, and the first
   // round that changed nothing ends the fill
   unsigned* changed = reinterpret_cast<unsigned*>(h.iuwt_scalars.get() + kIuwtChangedWord);
-  for (;;) {
+  h.iuwt_due.Reserve(size_t(tiles.x) * tiles.y);
+  int* due = h.iuwt_due.get();
+  RDL_CUDA(cudaMemsetAsync(due, 0xff, size_t(tiles.x) * tiles.y * sizeof(int), stream));  // -1
+  SeedTilesKernel<<<1, dim3(3, 3), 0, stream>>>(due, int(tiles.x), int(tiles.y),
+                                                 int(seed_x / kFillTX), int(seed_y / kFillTY));
+  for (int round = 0;;) {
     unsigned flags[kIuwtFillBatch];
     RDL_CUDA(cudaMemsetAsync(changed, 0, sizeof(flags), stream));
-    for (int r = 0; r != kIuwtFillBatch; ++r)
-      FillPropagateKernel<<<tiles, kFillThreads, smem, stream>>>(g, state, s_lo, s_hi, changed + r);
+    for (int r = 0; r != kIuwtFillBatch; ++r, ++round)
+      FillPropagateKernel<<<tiles, kFillThreads, smem, stream>>>(g, state, s_lo, s_hi, changed + r,
+                                                                 due, round);
     RDL_CUDA(cudaGetLastError());
     RDL_CUDA(cudaMemcpyAsync(flags, changed, sizeof(flags), cudaMemcpyDeviceToHost, stream));
     RDL_CUDA(cudaStreamSynchronize(stream));

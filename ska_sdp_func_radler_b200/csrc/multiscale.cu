@@ -429,8 +429,7 @@ const float* MultiScaleRun::TwiceConvolvedPsf(size_t p, size_t si, const float2*
   const auto key = std::make_pair(p, si);
   auto it = twice_cache_.find(key);
   if (it != twice_cache_.end()) return it->second.get();
-  size_t free_bytes = 0, total_bytes = 0;
-  RDL_CUDA(cudaMemGetInfo(&free_bytes, &total_bytes));
+  const size_t free_bytes = DeviceAvailableBytes();
   float* out = nullptr;
   if (free_bytes > n_ * sizeof(float) * 4 + (size_t(16) << 30)) {
     DeviceBuffer<float> buf(n_);
@@ -449,8 +448,7 @@ const float2* MultiScaleRun::PsfSpectrum(size_t p, size_t si, FftConvolver& padd
   const auto key = std::make_pair(p, si);
   auto it = psf_spectra_.find(key);
   if (it != psf_spectra_.end()) return it->second.get();
-  size_t free_bytes = 0, total_bytes = 0;
-  RDL_CUDA(cudaMemGetInfo(&free_bytes, &total_bytes));
+  const size_t free_bytes = DeviceAvailableBytes();
   const size_t need = padded.SpectrumSize() * sizeof(float2);
   float2* out = nullptr;
   if (free_bytes > need * 4 + (size_t(8) << 30)) {
