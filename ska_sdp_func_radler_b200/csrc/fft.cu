@@ -883,10 +883,11 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
     const size_t row_bytes = size_t(d.row_stride) * sizeof(float2);
     if (row_bytes > kMaxSmemBytes) throw std::domain_error("image row does not fit in shared memory");
     size_t row_budget_kb = 75;
-    if (const char* e = std::getenv("RDL_FFT_ROW_SMEM_KB")) row_budget_kb = size_t(std::atoi(e));
+    const char* budget_override = std::getenv("RDL_FFT_ROW_SMEM_KB");
+    if (budget_override) row_budget_kb = size_t(std::atoi(budget_override));
     d.rows_per_cta = int(std::clamp<size_t>(row_budget_kb * 1024 / row_bytes, 1, 8));
     // long rows: two per CTA (and two CTAs per SM) still beat one (9408: 2.23 -> 2.08 ms)
-    if (d.rows_per_cta == 1 && 2 * row_bytes <= 113 * 1024) d.rows_per_cta = 2;
+    if (!budget_override && d.rows_per_cta == 1 && 2 * row_bytes <= 113 * 1024) d.rows_per_cta = 2;
     d.row_smem = row_bytes * d.rows_per_cta;
     d.row_threads = d.n * d.rows_per_cta >= 4096 ? 256 : 128;
 
