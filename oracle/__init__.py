@@ -714,6 +714,9 @@ def _refa():
         L.refa_scale_mask_count.restype = u64
         L.refa_scale_mask_count.argtypes = [vp]
         L.refa_scale_mask.argtypes = [vp, u64, vp]
+        L.refa_parallel_scale_mask_count.restype = u64
+        L.refa_parallel_scale_mask_count.argtypes = [vp]
+        L.refa_parallel_scale_mask.argtypes = [vp, u64, u64, u64, vp]
         _refa_ready = True
     return L
 
@@ -823,3 +826,12 @@ class Reference:
         m = np.zeros((self.height, self.width), np.uint8)
         self._check(_ref.refa_scale_mask(self._h, i, _ptr(m)))
         return m
+
+    def parallel_scale_masks(self):
+        """ParallelDeconvolution's frame-sized per-scale masks (facet runs)."""
+        out = []
+        for i in range(_ref.refa_parallel_scale_mask_count(self._h)):
+            m = np.zeros((self.height, self.width), np.uint8)
+            self._check(_ref.refa_parallel_scale_mask(self._h, i, self.width, self.height, _ptr(m)))
+            out.append(m)
+        return out

@@ -19,7 +19,10 @@
 #include "algorithms/generic_clean.h"
 #include "algorithms/iuwt_deconvolution.h"
 #include "algorithms/multiscale_algorithm.h"
+// the frame-sized per-scale masks of ParallelDeconvolution are private; a test reads them
+#define private public
 #include "algorithms/parallel_deconvolution.h"
+#undef private
 #include "image_set.h"
 #include "settings.h"
 #include "work_table.h"
@@ -317,6 +320,18 @@ int refa_scale_mask(void* handle, uint64_t i, uint8_t* out) {
     auto& m = static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
                   .GetScaleMask(i);
     for (size_t k = 0; k != m.size(); ++k) out[k] = m[k] ? 1 : 0;
+  });
+}
+
+// ParallelDeconvolution::scale_masks_ (frame-sized, kept between major iterations of a facet run)
+uint64_t refa_parallel_scale_mask_count(void* handle) {
+  return static_cast<Handle*>(handle)->parallel->scale_masks_.size();
+}
+int refa_parallel_scale_mask(void* handle, uint64_t i, uint64_t width, uint64_t height,
+                             uint8_t* out) {
+  Handle* h = static_cast<Handle*>(handle);
+  return Guard(h, [&] {
+    h->parallel->scale_masks_.at(i).GetBox(reinterpret_cast<bool*>(out), 0, 0, width, height);
   });
 }
 

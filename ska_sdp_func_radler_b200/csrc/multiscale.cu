@@ -172,6 +172,12 @@ std::shared_ptr<MultiScaleState> CloneMultiScaleState(const MultiScaleState& src
 uint64_t MultiScaleScaleCount(const MultiScaleState& s) { return s.scales.size(); }
 rdl_scale_info MultiScaleScaleInfo(const MultiScaleState& s, uint64_t i) { return s.scales[i]; }
 
+std::vector<DeviceBuffer<uint8_t>>& MultiScaleMasks(rdl_handle& h, size_t mask_pixels) {
+  if (!h.ms) h.ms = std::make_shared<MultiScaleState>();
+  h.ms->mask_pixels = mask_pixels;
+  return h.ms->scale_masks;
+}
+
 void MultiScaleCopyScaleMask(const MultiScaleState& s, uint64_t i, uint8_t* out_host) {
   if (i >= s.scale_masks.size()) throw std::invalid_argument("scale mask index out of range");
   RDL_CUDA(cudaMemcpy(out_host, s.scale_masks[i].get(), s.scale_masks[i].size(), cudaMemcpyDeviceToHost));

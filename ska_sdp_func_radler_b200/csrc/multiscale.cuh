@@ -12,6 +12,9 @@ std::shared_ptr<MultiScaleState> CloneMultiScaleState(const MultiScaleState& src
 uint64_t MultiScaleScaleCount(const MultiScaleState& s);
 rdl_scale_info MultiScaleScaleInfo(const MultiScaleState& s, uint64_t i);
 void MultiScaleCopyScaleMask(const MultiScaleState& s, uint64_t i, uint8_t* out_host);
+// The per-scale masks of an algorithm (MultiScaleAlgorithm::GetScaleMask / SetScaleMaskCount,
+// multiscale_algorithm.h:41-56), created on first use; mask_pixels = pixels of one mask.
+std::vector<DeviceBuffer<uint8_t>>& MultiScaleMasks(rdl_handle& h, size_t mask_pixels);
 void MultiScaleTransform(rdl_handle& h, float* const* images, uint64_t n_images, uint64_t width,
                          uint64_t height, float scale, int32_t shape, cudaStream_t stream);
 }  // namespace rdl

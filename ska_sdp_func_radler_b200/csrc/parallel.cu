@@ -17,6 +17,7 @@
 
 #include "clean_kernels.cuh"
 #include "facets.h"
+#include "multiscale.cuh"
 
 namespace rdl {
 namespace {
@@ -68,6 +69,29 @@ __global__ void KeepOwnedKernel(float* image, const uint8_t* owned, size_t n) {
     if (!owned[i]) image[i] = 0.0f;
 }
 
+// facet scale mask = frame scale mask box AND the facet's clean mask (:376-389)
+__global__ void ScaleMaskInKernel(uint8_t* dst, const uint8_t* frame, size_t frame_width, size_t x,
+                                  size_t y, size_t w, size_t h, const uint8_t* facet_mask) {
+  const size_t n = w * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t row = i / w, col = i - row * w;
+    dst[i] = (frame[(y + row) * frame_width + x + col] && facet_mask[i]) ? 1 : 0;
+  }
+}
+
+// frame scale mask box = facet scale mask where the facet owns the pixel (:438-452)
+__global__ void ScaleMaskOutKernel(uint8_t* frame, size_t frame_width, size_t x, size_t y, size_t w,
+                                   size_t h, const uint8_t* facet_scale_mask,
+                                   const uint8_t* boundary_mask) {
+  const size_t n = w * h;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t row = i / w, col = i - row * w;
+    if (boundary_mask[i]) frame[(y + row) * frame_width + x + col] = facet_scale_mask[i] ? 1 : 0;
+  }
+}
+
 double MsSince(std::chrono::steady_clock::time_point t0) {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -86,6 +110,7 @@ struct ParallelState {
   std::vector<uint64_t> iterations;  // IterationNumber() of every facet's algorithm, all ranks
   double geometry_ms = 0.0, total_ms = 0.0;  // host divider search / whole last call
   DeviceBuffer<uint8_t> owned, wire_send, wire_recv;
+  DeviceBuffer<uint8_t> facet_mask;  // a facet's clean mask on the device (scale-mask trims)
   ~ParallelState() {
     for (rdl_handle* a : algorithms) rdl_destroy(a);
   }
@@ -169,6 +194,33 @@ void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
   else
     a.settings.major_iteration_threshold = float(major_iteration_threshold);
 
+  const bool scale_masks_on = (h.use_per_scale_masks || h.track_per_scale_masks) &&
+                              a.config.algorithm == RDL_MULTISCALE;
+  if (scale_masks_on) {
+    // the frame's masks of the previous major iteration, trimmed to this facet (:359-391);
+    // they live in the parent handle, where rdl_scale_mask_get finds them
+    std::vector<DeviceBuffer<uint8_t>>& frame_masks = MultiScaleMasks(h, cube.Pixels());
+    if (!frame_masks.empty()) {
+      std::vector<DeviceBuffer<uint8_t>>& masks = MultiScaleMasks(a, n);
+      const size_t count = std::max(masks.size(), frame_masks.size());
+      while (masks.size() < count) masks.emplace_back();
+      st.facet_mask.Reserve(n);
+      RDL_CUDA(cudaMemcpyAsync(st.facet_mask.get(), f.mask.data(), n, cudaMemcpyHostToDevice,
+                               stream));
+      for (size_t i = 0; i != count; ++i) {
+        masks[i].Resize(n);
+        if (i < frame_masks.size()) {
+          ScaleMaskInKernel<<<GridFor(n), kThreads, 0, stream>>>(
+              masks[i].get(), frame_masks[i].get(), W, f.x, f.y, w, fh, st.facet_mask.get());
+          ++h.launches;
+        } else {
+          RDL_CUDA(cudaMemsetAsync(masks[i].get(), 0, n, stream));
+        }
+      }
+      RDL_CUDA(cudaStreamSynchronize(stream));  // f.mask is pageable host memory
+    }
+  }
+
   const double peak_at_start = std::fabs(f.peak);
   const rdl_result r = RunAlgorithm(a, sub, stream);
   h.launches += a.launches;
@@ -184,6 +236,23 @@ void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
   if (find_peak_only) {
     a.settings.max_iterations = max_iterations;
     return;
+  }
+  if (scale_masks_on && h.track_per_scale_masks && converging) {
+    // the facet's new masks go back into the frame's, inside the pixels it owns (:421-463)
+    std::vector<DeviceBuffer<uint8_t>>& frame_masks = MultiScaleMasks(h, cube.Pixels());
+    std::vector<DeviceBuffer<uint8_t>>& masks = MultiScaleMasks(a, n);
+    const size_t scale_count = rdl_scale_count(&a);
+    if (frame_masks.empty()) {
+      for (size_t i = 0; i != scale_count; ++i) {
+        frame_masks.emplace_back(cube.Pixels());
+        RDL_CUDA(cudaMemsetAsync(frame_masks.back().get(), 0, cube.Pixels(), stream));
+      }
+    }
+    for (size_t i = 0; i != scale_count && i < frame_masks.size() && i < masks.size(); ++i) {
+      ScaleMaskOutKernel<<<GridFor(n), kThreads, 0, stream>>>(
+          frame_masks[i].get(), W, f.x, f.y, w, fh, masks[i].get(), st.boundary_mask.get());
+      ++h.launches;
+    }
   }
   for (size_t i = 0; i != cube.n_images; ++i) {
     if (converging) {
@@ -310,8 +379,8 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
     st.iterations.assign(1, a.iteration_number);
     return r;
   }
-  if (h.track_per_scale_masks || h.use_per_scale_masks)
-    throw std::domain_error("per-scale masks under facets are not supported yet");
+  if ((h.track_per_scale_masks || h.use_per_scale_masks) && h.dist.comm && h.dist.world > 1)
+    throw std::domain_error("per-scale masks under facets sharded over several GPUs are not built");
 
   const size_t W = cube.width, H = cube.height, A = cube.Pixels();
   // image = data_image.GetLinearIntegrated(); the dividers follow its minimum-power paths

@@ -71,3 +71,46 @@ def test_facet_run_with_host_buffers_and_mask(rdl, oracle, torch_cuda):
     g = alg.parallel_execute_major_iteration(2, 2, rdl.Cube(n, n, c, 1, weights), g_res, g_model, psfs)
     assert g.another_iteration_required == w.another_iteration_required
     assert np.array_equal(g_res, r_res) and np.array_equal(g_model, r_model)
+
+
+def test_multiscale_facets_two_phase_automask(rdl, oracle, torch_cuda):
+    """MultiScaleAlgorithm under a 2 x 2 facet grid with auto-masking (radler.cc:254-266 over
+    parallel_deconvolution.cc:359-463): phase 1 tracks the per-scale masks, which are merged into
+    frame-sized masks facet by facet; phase 2 cleans deeper inside them. Against the reference's
+    own ParallelDeconvolution + MultiScaleAlgorithm sources (one thread = facets in index order):
+    same per-call results, identical frame-sized masks, images within the FFT tolerance."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    from helpers import multiscale_case
+    n, grid = 256, (2, 2)
+    res, psfs, weights, freqs = multiscale_case(n, 1, seed=7)
+    ref = oracle.Reference("multiscale", n, n, 1, weights=weights, frequencies=freqs, beam_size=6.0,
+                           max_scales=4, grid=grid, threads=1, max_iterations=20000,
+                           major_loop_gain=0.8, clean_border_ratio=0.0)
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4)
+    alg.apply(max_iterations=20000, major_loop_gain=0.8, clean_border_ratio=0.0)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((1, n, n), device="cuda")
+    d_psf = torch.from_numpy(psfs).cuda()
+    cube = rdl.Cube(n, n, 1, 1, weights)
+    peak = np.abs(res).max()
+    calls = [((True, False), 0.5)] * 3 + [((False, True), 0.25)] * 2  # call 3 has a diverging facet
+    for phase, (automask, threshold) in enumerate(calls):
+        ref.set_auto_mask_mode(*automask)
+        ref.set_threshold(float(threshold))
+        alg.set_auto_mask_mode(*automask)
+        alg.set_threshold(float(threshold))
+        w = ref.execute(r_res, r_model, psfs)
+        g = alg.parallel_execute_major_iteration(grid[0], grid[1], cube, d_res, d_model, d_psf)
+        assert g.another_iteration_required == w.another_iteration_required, phase
+        assert abs(g.final_peak_value - w.final_peak_value) <= 1e-4 * peak, phase
+        want_masks = ref.parallel_scale_masks()
+        assert len(want_masks) >= 3 and sum(int(m.sum()) for m in want_masks) > 0
+        for i, m in enumerate(want_masks):
+            assert np.array_equal(alg.scale_mask(i, n, n), m), (phase, i)
+        with pytest.raises(rdl.RadlerError):
+            alg.scale_mask(len(want_masks), n, n)
+        assert np.abs(d_res.cpu().numpy() - r_res).max() <= 1e-5 * peak, phase
+        assert np.abs(d_model.cpu().numpy() - r_model).max() <= 1e-5 * max(np.abs(r_model).max(), 1e-30), phase
+    assert sum(f["iteration_number"] for f in alg.facets()) > 50
