@@ -198,6 +198,42 @@ void MakeScaleSpectrum(rdl_handle& h, FftConvolver& conv, float scale, int shape
   conv.MakeSmallKernelSpectrum(h.small_kernel.get(), n, spectrum, stream);
 }
 
+// values[i] = images[i][index]  (MeasureComponentValues, multiscale_algorithm.cc:658-674)
+__global__ void GatherPixelKernel(ConstPtrTable images, int n_images, size_t index, float* values) {
+  const int i = threadIdx.x;
+  if (i < n_images) values[i] = images.p[i][index];
+}
+
+struct ComponentValues {
+  float v[kMaxImages];
+};
+
+// AddComponentToModel for a non-zero scale (multiscale_transforms.h:62-89): the n x n shape
+// function centred on (x, y), clipped at the frame, row = fma(kernel, gain, row).
+__global__ void AddShapeKernel(PtrTable model, int n_images, size_t width, size_t height,
+                               const float* __restrict__ shape, size_t n, size_t x, size_t y,
+                               ComponentValues gains) {
+  const size_t left = x > n / 2 ? x - n / 2 : 0, top = y > n / 2 ? y - n / 2 : 0;
+  const size_t right = min(x + (n + 1) / 2, width), bottom = min(y + (n + 1) / 2, height);
+  const size_t bw = right - left, bh = bottom - top;
+  const int image = blockIdx.y;
+  float* data = model.p[image];
+  const float gain = gains.v[image];
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < bw * bh;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t yi = top + i / bw, xi = left + i % bw;
+    const float k = shape[(yi + n / 2 - y) * n + xi + n / 2 - x];
+    float* d = data + yi * width + xi;
+    *d = __fmaf_rn(k, gain, *d);
+  }
+}
+
+// model[i][index] += values[i]  (scale 0)
+__global__ void AddPointKernel(PtrTable model, int n_images, size_t index, ComponentValues gains) {
+  const int i = threadIdx.x;
+  if (i < n_images) model.p[i][index] = __fadd_rn(model.p[i][index], gains.v[i]);
+}
+
 struct Peak {
   bool has = false;
   float value = 0.0f;
@@ -241,6 +277,9 @@ class MultiScaleRun {
   void FindActiveScaleConvolvedMaxima(bool report_rms);
   bool SelectMaximumScale(size_t& scale);
   void ActivateScales(size_t last);
+  bool RunWithoutSubMinorLoop(size_t swp, float first_sub_iteration_threshold,
+                              float initial_peak_value, PtrTable& conv_residual,
+                              const ConstPtrTable& psf_per_image);
   const float* ConvolvedPsf(size_t p, size_t si) const {
     return Scales2()[si].scale == 0.0f ? base_psf_[p] : convolved_psfs_[p * st_.scales.size() + si].get();
   }
@@ -263,6 +302,7 @@ class MultiScaleRun {
   std::map<std::pair<size_t, size_t>, DeviceBuffer<float2>> psf_spectra_;
   std::map<std::pair<size_t, size_t>, DeviceBuffer<float>> twice_cache_;  // [psf, scale]
   DeviceBuffer<float2> psf_spectrum_tmp_;
+  DeviceBuffer<float> shape_dev_, values_dev_;  // loop without the sub-minor optimisation
   DeviceBuffer<double> sumsq_;
 };
 
@@ -428,6 +468,104 @@ void MultiScaleRun::ActivateScales(size_t last) {  // multiscale_algorithm.cc:63
 // Spectrum of PrepareConvolutionKernel(Untrim(convolved PSF)) for CorrectResidualDirty. The
 // reference recomputes it per image and per minor iteration (subminor_loop.cc:199-202); it only
 // depends on (psf, scale), so it is cached for the duration of the call when memory allows.
+// The minor loop without the sub-minor optimisation (multiscale_algorithm.cc:462-520): one
+// component per iteration at the peak of the selected scale; it is subtracted from the data
+// images with the scale-convolved PSF and from the scale-convolved images with the twice-convolved
+// PSF, added to the model as a scaled shape function, and the peak of that scale is searched
+// again. The host reads one peak per iteration, like the reference.
+bool MultiScaleRun::RunWithoutSubMinorLoop(size_t swp, float first_sub_iteration_threshold,
+                                           float initial_peak_value, PtrTable& convolved,
+                                           const ConstPtrTable& twice_convolved) {
+  rdl_handle& h = h_;
+  const Settings& set = h.settings;
+  rdl_scale_info& info = Scales()[swp];
+  const int n_images = int(cube_.n_images);
+  size_t shape_n = 0;
+  if (info.scale != 0.0f) {
+    const std::vector<float> shape =
+        MakeShapeFunction(info.scale, shape_n, std::min(width_, height_), h.config.ms_shape);
+    shape_dev_.Reserve(shape.size());
+    RDL_CUDA(cudaMemcpyAsync(shape_dev_.get(), shape.data(), shape.size() * sizeof(float),
+                             cudaMemcpyHostToDevice, stream_));
+    Sync();  // `shape` is pageable host memory
+  }
+  ConstPtrTable convolved_const{}, psf_at_scale{};
+  PtrTable residual{}, model{};
+  for (int i = 0; i != n_images; ++i) {
+    convolved_const.p[i] = convolved.p[i];
+    psf_at_scale.p[i] = ConvolvedPsf(cube_.PsfIndex(i), swp);
+    residual.p[i] = cube_.residual.p[i];
+    model.p[i] = cube_.model.p[i];
+  }
+  values_dev_.Reserve(kMaxImages);
+  const IntegSpec linear = MakeLinearSpec(cube_);
+  const int n_fit = int(h.fit_freqs.size()), n_pol = int(cube_.n_pol);
+  bool diverging = false;
+  while (h.iteration_number < set.max_iterations &&
+         std::fabs(info.max_unnormalized_image_value * info.bias_factor) >
+             first_sub_iteration_threshold &&
+         (!set.stop_on_negative_component || info.max_unnormalized_image_value >= 0.0f) &&
+         !diverging) {
+    const size_t x = info.max_x, y = info.max_y, index = x + y * width_;
+    // MeasureComponentValues + PerformSpectralFit (deconvolution_algorithm.cc:29-46)
+    float values[kMaxImages];
+    GatherPixelKernel<<<1, kMaxImages, 0, stream_>>>(convolved_const, n_images, index,
+                                                     values_dev_.get());
+    RDL_CUDA(cudaMemcpyAsync(values, values_dev_.get(), n_images * sizeof(float),
+                             cudaMemcpyDeviceToHost, stream_));
+    Sync();
+    if (h.fit_mode == RDL_FIT_POLYNOMIAL) {
+      float fitted[kMaxImages];
+      for (int i = 0; i != n_images; ++i) {
+        const int ch = i / n_pol, pol = i - ch * n_pol;
+        double sum = 0.0;
+        for (int j = 0; j != n_fit; ++j)
+          sum = std::fma(h.projection_host[ch * n_fit + j], double(values[j * n_pol + pol]), sum);
+        fitted[i] = float(sum);
+      }
+      std::copy_n(fitted, n_images, values);
+    }
+    ComponentValues gains{};
+    for (int i = 0; i != n_images; ++i) {
+      values[i] = values[i] * info.gain;
+      gains.v[i] = values[i];
+    }
+    LaunchSubtract(residual, psf_at_scale, n_images, int(width_), int(height_), int(x), int(y),
+                   values, stream_);
+    LaunchSubtract(convolved, twice_convolved, n_images, int(width_), int(height_), int(x), int(y),
+                   values, stream_);
+    // AddComponentToModel (:676-698), once per image
+    if (info.scale == 0.0f) {
+      AddPointKernel<<<1, kMaxImages, 0, stream_>>>(model, n_images, index, gains);
+    } else {
+      const dim3 grid(unsigned((shape_n * shape_n + 255) / 256), unsigned(n_images));
+      AddShapeKernel<<<grid, 256, 0, stream_>>>(model, n_images, width_, height_, shape_dev_.get(),
+                                                shape_n, x, y, gains);
+    }
+    for (int i = 0; i != n_images; ++i) {
+      info.n_components_cleaned++;
+      info.total_flux_cleaned += values[i];
+    }
+    if (h.track_per_scale_masks)
+      RDL_CUDA(cudaMemsetAsync(st_.scale_masks[swp].get() + index, 1, 1, stream_));
+    // the peak of this scale again
+    LaunchIntegrate(linear, convolved_const, n_, integrated_.get(), cube_.vec, stream_);
+    h.launches += 5;
+    FindPeakDirect(integrated_.get(), swp);
+    const float abs_peak_value =
+        std::fabs(info.max_unnormalized_image_value * info.bias_factor);
+    if (set.divergence_limit != 0.0f)
+      diverging = abs_peak_value > initial_peak_value * set.divergence_limit;
+    ++h.iteration_number;
+    if (h.trace_host.size() < h.trace_capacity)
+      h.trace_host.push_back(TraceEntry{uint32_t(h.iteration_number), uint32_t(swp),
+                                        uint32_t(info.max_x), uint32_t(info.max_y),
+                                        info.max_unnormalized_image_value});
+  }
+  RDL_CUDA(cudaGetLastError());
+  return diverging;
+}
+
 // The PSF of slot p convolved twice with the kernel of scale si (multiscale_algorithm.cc:331-343).
 // The reference recomputes it in every minor iteration that selects the scale; the PSFs do not
 // change during a call, so it is kept while HBM allows (K4: 16 PSFs x 4 scales x 268 MB).
@@ -474,8 +612,8 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
   rdl_handle& h = h_;
   Settings& set = h.settings;
   if (set.stop_on_negative_component) set.allow_negative_components = true;
-  if (!h.config.ms_fast_sub_minor_loop)
-    throw std::domain_error("multiscale with fast_sub_minor_loop = false is not built yet");
+  if (!h.config.ms_fast_sub_minor_loop && h.fit_mode != RDL_FIT_NONE && h.fit_mode != RDL_FIT_POLYNOMIAL)
+    throw std::domain_error("multiscale without the sub-minor loop supports the polynomial fit only");
   if (h.config.track_components)
     throw std::domain_error("multiscale component tracking (save_source_list) is not built yet");
   InitializeScales(Scales(), h.beam_size_in_pixels, std::min(width_, height_), h.config.ms_shape,
@@ -566,6 +704,14 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       for (size_t i = 0; i != cube_.n_images; ++i) {
         conv_residual.p[i] = cube_.residual.p[i];
         psf_per_image.p[i] = ConvolvedPsf(cube_.PsfIndex(i), swp);
+        if (!h.config.ms_fast_sub_minor_loop) {
+          // without the sub-minor loop the convolved images are subtracted from as well (:489):
+          // they have to be the copies the reference makes (:346-349)
+          individual_convolved_[i].Reserve(n_);
+          RDL_CUDA(cudaMemcpyAsync(individual_convolved_[i].get(), cube_.residual.p[i],
+                                   n_ * sizeof(float), cudaMemcpyDeviceToDevice, stream_));
+          conv_residual.p[i] = individual_convolved_[i].get();
+        }
       }
     }
 
@@ -576,6 +722,21 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     if (first_threshold > first_sub_iteration_threshold) {
       first_sub_iteration_threshold = first_threshold;
       threshold_countdown--;
+    }
+
+    if (!h.config.ms_fast_sub_minor_loop) {
+      PtrTable convolved{};
+      for (size_t i = 0; i != cube_.n_images; ++i) convolved.p[i] = individual_convolved_[i].get();
+      diverging = RunWithoutSubMinorLoop(swp, first_sub_iteration_threshold, initial_peak_value,
+                                         convolved, psf_per_image);
+      ActivateScales(swp);
+      FindActiveScaleConvolvedMaxima(false);
+      if (!SelectMaximumScale(swp)) {
+        result.iteration_number = h.iteration_number;
+        result.another_iteration_required = 0;
+        return result;
+      }
+      continue;
     }
 
     const uint64_t sub_minor_start_iteration = h.iteration_number;

@@ -60,7 +60,7 @@ def run_both(rdl, oracle, res, psfs, weights, settings, beam=6.0, ms_kwargs=None
     return o, (o_res, o_model), g, (g_res, g_model), (oalg, galg)
 
 
-def check(o, oi, g, gi, algs, value_rtol=2e-4, minor_before=0):
+def check(o, oi, g, gi, algs, value_rtol=2e-4, minor_before=0, image_scale=None):
     oalg, galg = algs
     assert g.iteration_number == o.iteration_number
     # the oracle's counter runs over the object's lifetime, the C ABI's getter per call
@@ -87,7 +87,7 @@ def check(o, oi, g, gi, algs, value_rtol=2e-4, minor_before=0):
     assert g.another_iteration_required == o.another_iteration_required
     assert g.is_diverging == o.is_diverging
     assert g.final_peak_value == pytest.approx(o.final_peak_value, rel=value_rtol, abs=1e-7)
-    scale = max(np.abs(oi[0]).max(), np.abs(oi[1]).max(), 1e-30)
+    scale = image_scale or max(np.abs(oi[0]).max(), np.abs(oi[1]).max(), 1e-30)
     # a near-tie moves one component by one pixel: the images then differ by that
     # component's (scale-kernel shaped) footprint, not by round-off
     tol = REL_TOL if near_ties == 0 else NEAR_TIE_IMAGE_TOL
@@ -189,3 +189,19 @@ def test_multiscale_clone_keeps_state(rdl, oracle, torch_cuda):
     assert clone.scale_infos() == galg.scale_infos()
     for i in range(clone.scale_count):
         assert np.array_equal(clone.scale_mask(i, 128, 128), galg.scale_mask(i, 128, 128))
+
+
+@pytest.mark.parametrize("n,c,iters,fit", [(192, 1, 600, False), (160, 3, 400, True)])
+def test_multiscale_without_sub_minor_loop(rdl, oracle, torch_cuda, n, c, iters, fit):
+    """settings.fast_sub_minor_loop = false (multiscale_algorithm.cc:462-520): one component per
+    iteration, subtracted from the data and from the scale-convolved images, model built from
+    shape functions; joined channels with the polynomial fit in the second case."""
+    res, psfs, weights, freqs = multiscale_case(n, c, seed=3)
+    st = dict(threshold=0.0, max_iterations=iters, clean_border_ratio=0.0, major_loop_gain=0.98)
+    o, oi, g, gi, algs = run_both(rdl, oracle, res, psfs, weights, st,
+                                  fit=(2, freqs, weights) if fit else None,
+                                  ms_kwargs=dict(max_scales=4, fast_sub_minor_loop=False))
+    assert o.iteration_number > 20
+    assert len({int(s) for s in o.trace["scale"]}) > 1
+    # cleaned to 2 % of the peak: the 1e-5 image tolerance refers to the image that went in
+    check(o, oi, g, gi, algs, image_scale=float(np.abs(res).max()))
