@@ -205,3 +205,27 @@ def test_multiscale_without_sub_minor_loop(rdl, oracle, torch_cuda, n, c, iters,
     assert len({int(s) for s in o.trace["scale"]}) > 1
     # cleaned to 2 % of the peak: the 1e-5 image tolerance refers to the image that went in
     check(o, oi, g, gi, algs, image_scale=float(np.abs(res).max()))
+
+
+def test_multiscale_without_sub_minor_loop_automask(rdl, oracle, torch_cuda):
+    """The per-iteration loop marks the per-scale mask at every component (:692-697) and phase 2
+    searches inside the masks."""
+    res, psfs, weights, freqs = multiscale_case(160, 1, seed=1)
+    slow = dict(max_scales=4, fast_sub_minor_loop=False)
+    st1 = dict(threshold=0.0, max_iterations=250, clean_border_ratio=0.0, major_loop_gain=0.98)
+    o, oi, g, gi, algs = run_both(rdl, oracle, res, psfs, weights, st1, automask=(True, False),
+                                  ms_kwargs=slow)
+    scale = float(np.abs(res).max())
+    check(o, oi, g, gi, algs, image_scale=scale)
+    oalg, galg = algs
+    masks = [oalg.scale_mask(i, 160, 160) for i in range(len(oalg.scale_infos()))]
+    assert sum(int(m.sum()) for m in masks) > 20
+    for i, m in enumerate(masks):
+        assert np.array_equal(galg.scale_mask(i, 160, 160), m), i
+    minor_before = oalg.minor_iterations()
+    st2 = dict(threshold=0.0, max_iterations=400, clean_border_ratio=0.0, major_loop_gain=0.9,
+               iteration_number=o.iteration_number)
+    o2, oi2, g2, gi2, _ = run_both(rdl, oracle, oi[0], psfs, weights, st2, automask=(False, True),
+                                   algs=algs)
+    assert o2.iteration_number > o.iteration_number
+    check(o2, oi2, g2, gi2, algs, minor_before=minor_before, image_scale=scale)

@@ -130,6 +130,20 @@ def test_multiscale_restatement_is_bit_exact(ref):
                    max_iterations=1500, major_loop_gain=0.85)
 
 
+def test_multiscale_without_sub_minor_loop_bit_exact(ref):
+    # settings.fast_sub_minor_loop = false: multiscale_algorithm.cc:462-520
+    res, psfs, weights, freqs = multiscale_case(128, 3, seed=3)
+    kw = dict(max_iterations=300, major_loop_gain=0.97)
+    slow = dict(max_scales=4, fast_sub_minor_loop=False)
+    _, _, outs = run_multiscale(ref, res, psfs, weights, freqs, ms=slow, **kw)
+    assert outs[0].iteration_number > 30
+    run_multiscale(ref, res, psfs, weights, freqs, fit=2, ms=slow, **kw)
+    single = multiscale_case(160, 1, seed=1)
+    run_multiscale(ref, single[0], single[1], None, single[3], ms=slow, max_iterations=400,
+                   major_loop_gain=0.98,
+                   phases=[dict(automask=(True, False)), dict(automask=(False, True))])
+
+
 def test_multiscale_automask_phases_bit_exact(ref):
     # radler.cc:244-268: phase 1 tracks per-scale masks, phase 2 cleans inside them
     res, psfs, weights, freqs = multiscale_case(128, 1, seed=7)
