@@ -153,6 +153,19 @@ rdl_status rdl_set_trace_capacity(rdl_handle* h, uint64_t capacity);
 uint64_t rdl_iteration_number(const rdl_handle* h);             /* IterationNumber */
 uint64_t rdl_scale_count(const rdl_handle* h);                  /* ScaleCount */
 rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* out); /* ScaleSize & co */
+/* ---- component list (cpp/component_list.h; rdl_config.track_components = settings.save_source_list)
+ * MultiScaleAlgorithm::GetComponentList() (multiscale_algorithm.h:46-48): the components of every
+ * major iteration since creation / the last clear, per scale, after ComponentList::MergeDuplicates
+ * (component_list.h:113-131): one record per position, values summed in the order the components
+ * were found, one value per image of the cube. rdl_component_get copies `count` records starting
+ * at `first`: x[count], y[count], values[count * n_images]. */
+uint64_t rdl_component_scale_count(const rdl_handle* h);
+rdl_status rdl_component_count(rdl_handle* h, uint64_t scale_index, uint64_t* count);
+rdl_status rdl_component_get(rdl_handle* h, uint64_t scale_index, uint64_t first, uint64_t count,
+                             uint64_t* x, uint64_t* y, float* values);
+/* MultiScaleAlgorithm::ClearComponentList() */
+void rdl_component_list_clear(rdl_handle* h);
+
 /* GetScaleMask(i): copies width*height bytes to host memory */
 rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out);
 uint64_t rdl_trace_size(const rdl_handle* h);

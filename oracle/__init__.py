@@ -714,6 +714,11 @@ def _refa():
         L.refa_scale_mask_count.restype = u64
         L.refa_scale_mask_count.argtypes = [vp]
         L.refa_scale_mask.argtypes = [vp, u64, vp]
+        L.refa_component_count.restype = u64
+        L.refa_component_count.argtypes = [vp, u64]
+        L.refa_component_scales.restype = u64
+        L.refa_component_scales.argtypes = [vp]
+        L.refa_component_get.argtypes = [vp, u64, u64, C.POINTER(u64), C.POINTER(u64), vp]
         L.refa_parallel_scale_mask_count.restype = u64
         L.refa_parallel_scale_mask_count.argtypes = [vp]
         L.refa_parallel_scale_mask.argtypes = [vp, u64, u64, u64, vp]
@@ -826,6 +831,22 @@ class Reference:
         m = np.zeros((self.height, self.width), np.uint8)
         self._check(_ref.refa_scale_mask(self._h, i, _ptr(m)))
         return m
+
+    def component_list(self, n_images):
+        """MultiScaleAlgorithm::GetComponentList() after MergeDuplicates: per scale
+        (x[n], y[n], values[n, n_images])."""
+        out = []
+        for scale in range(_ref.refa_component_scales(self._h)):
+            n = _ref.refa_component_count(self._h, scale)
+            x, y = np.zeros(n, np.uint64), np.zeros(n, np.uint64)
+            v = np.zeros((n, n_images), np.float32)
+            cx, cy = C.c_uint64(), C.c_uint64()
+            for i in range(n):
+                self._check(_ref.refa_component_get(self._h, scale, i, C.byref(cx), C.byref(cy),
+                                                    _ptr(v[i])))
+                x[i], y[i] = cx.value, cy.value
+            out.append((x, y, v))
+        return out
 
     def parallel_scale_masks(self):
         """ParallelDeconvolution's frame-sized per-scale masks (facet runs)."""

@@ -100,7 +100,8 @@ EXPORTED_SYMBOLS = [
     "rdl_facet_dividing_path", "rdl_facet_flood_area", "rdl_facet_bounding_mask", "rdl_facet_grid",
     "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
     "rdl_dist_finalize",
-    "rdl_release_cached_memory",
+    "rdl_release_cached_memory", "rdl_component_scale_count", "rdl_component_count",
+    "rdl_component_get", "rdl_component_list_clear",
     "rdl_good_fft_size", "rdl_convolution_size", "rdl_version",
     "rdl_device_count",
 ]
@@ -168,6 +169,12 @@ def lib():
     L.rdl_parallel_facet_count.argtypes = [vp]
     L.rdl_parallel_facet_count.restype = u64
     L.rdl_parallel_facet_get.argtypes = [vp, u64, C.POINTER(_FacetInfo), vp]
+    L.rdl_component_scale_count.argtypes = [vp]
+    L.rdl_component_scale_count.restype = u64
+    L.rdl_component_count.argtypes = [vp, u64, C.POINTER(u64)]
+    L.rdl_component_get.argtypes = [vp, u64, u64, u64, vp, vp, vp]
+    L.rdl_component_list_clear.argtypes = [vp]
+    L.rdl_component_list_clear.restype = None
     L.rdl_parallel_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.rdl_facet_dividing_path.argtypes = [vp, vp, u64, u64, u64, u64, i32]
     L.rdl_facet_flood_area.argtypes = [vp, u64, u64, u64, i32, vp, C.POINTER(u64), C.POINTER(u64)]
@@ -376,6 +383,25 @@ class DeconvolutionAlgorithm:
             self._check(lib().rdl_scale_info_get(self._h, i, C.byref(s)))
             out.append({k: getattr(s, k) for k, _ in _ScaleInfo._fields_})
         return out
+
+    def component_list(self, n_images):
+        """MultiScaleAlgorithm::GetComponentList() after MergeDuplicates: per scale a tuple
+        (x[n], y[n], values[n, n_images])."""
+        out = []
+        for scale in range(lib().rdl_component_scale_count(self._h)):
+            n = C.c_uint64()
+            self._check(lib().rdl_component_count(self._h, scale, C.byref(n)))
+            x = np.zeros(n.value, np.uint64)
+            y = np.zeros(n.value, np.uint64)
+            v = np.zeros((n.value, n_images), np.float32)
+            if n.value:
+                self._check(lib().rdl_component_get(self._h, scale, 0, n.value, x.ctypes.data,
+                                                    y.ctypes.data, v.ctypes.data))
+            out.append((x, y, v))
+        return out
+
+    def clear_component_list(self):
+        lib().rdl_component_list_clear(self._h)
 
     def scale_mask(self, i, width, height):
         m = np.zeros((height, width), np.uint8)

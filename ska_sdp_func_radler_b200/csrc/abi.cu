@@ -194,6 +194,7 @@ rdl_status rdl_clone(const rdl_handle* src, rdl_handle** out) {
       h->fit_n_pol = src->fit_n_pol;
     }
     if (src->ms) h->ms = CloneMultiScaleState(*src->ms, h->own_stream);
+    h->components = src->components;  // cloned_ptr<ComponentList>
   });
   if (st != RDL_OK) {
     rdl_destroy(h);
@@ -331,6 +332,37 @@ rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* o
   *out = MultiScaleScaleInfo(*h->ms, i);
   return RDL_OK;
 }
+uint64_t rdl_component_scale_count(const rdl_handle* h) { return h ? h->components.scales.size() : 0; }
+
+rdl_status rdl_component_count(rdl_handle* h, uint64_t scale_index, uint64_t* count) {
+  if (!h || !count || scale_index >= h->components.scales.size()) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    h->components.MergeDuplicates();
+    *count = h->components.scales[scale_index].x.size();
+  });
+}
+
+rdl_status rdl_component_get(rdl_handle* h, uint64_t scale_index, uint64_t first, uint64_t count,
+                             uint64_t* x, uint64_t* y, float* values) {
+  if (!h || !x || !y || !values || scale_index >= h->components.scales.size())
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    h->components.MergeDuplicates();
+    const rdl::ComponentScaleList& list = h->components.scales[scale_index];
+    if (first + count > list.x.size()) throw std::invalid_argument("component range out of bounds");
+    const size_t n_values = h->components.n_values;
+    for (uint64_t k = 0; k != count; ++k) {
+      x[k] = list.x[first + k];
+      y[k] = list.y[first + k];
+    }
+    std::copy_n(list.values.begin() + first * n_values, count * n_values, values);
+  });
+}
+
+void rdl_component_list_clear(rdl_handle* h) {
+  if (h) h->components = rdl::ComponentList{};
+}
+
 rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out) {
   if (!h || !out || !h->ms) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(const_cast<rdl_handle*>(h), [&] {

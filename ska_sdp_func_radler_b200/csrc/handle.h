@@ -12,6 +12,7 @@
 #include "../../include/radler_b200.h"
 #include "clean_kernels.cuh"
 #include "common.cuh"
+#include "components.h"
 #include "dist.h"
 
 namespace rdl {
@@ -178,6 +179,7 @@ struct rdl_handle {
   // row-sharded multi-GPU loop (not cloned)
   rdl::DistContext dist;
   rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;
+  rdl::ComponentList components;     // MultiScaleAlgorithm::component_list_ (track_components)
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
   // FFT engines by frame size (plans, twiddle tables, work spectrum); not cloned

@@ -548,6 +548,7 @@ bool MultiScaleRun::RunWithoutSubMinorLoop(size_t swp, float first_sub_iteration
     }
     if (h.track_per_scale_masks)
       RDL_CUDA(cudaMemsetAsync(st_.scale_masks[swp].get() + index, 1, 1, stream_));
+    if (h.config.track_components) h.components.Add(x, y, swp, values);  // :502-504
     // the peak of this scale again
     LaunchIntegrate(linear, convolved_const, n_, integrated_.get(), cube_.vec, stream_);
     h.launches += 5;
@@ -614,11 +615,19 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
   if (set.stop_on_negative_component) set.allow_negative_components = true;
   if (!h.config.ms_fast_sub_minor_loop && h.fit_mode != RDL_FIT_NONE && h.fit_mode != RDL_FIT_POLYNOMIAL)
     throw std::domain_error("multiscale without the sub-minor loop supports the polynomial fit only");
-  if (h.config.track_components)
-    throw std::domain_error("multiscale component tracking (save_source_list) is not built yet");
   InitializeScales(Scales(), h.beam_size_in_pixels, std::min(width_, height_), h.config.ms_shape,
                    h.config.ms_max_scales, h.ms_scale_list);
   const size_t n_scales = Scales().size();
+  if (h.config.track_components) {  // multiscale_algorithm.cc:228-240
+    if (h.components.Empty()) {
+      h.components.width = width_;
+      h.components.height = height_;
+      h.components.n_values = cube_.n_images;
+      h.components.scales.resize(n_scales);
+    } else if (h.components.width != width_ || h.components.height != height_) {
+      throw std::invalid_argument("Error in component list dimensions!");
+    }
+  }
   if (h.track_per_scale_masks) {
     // multiscale_algorithm.cc:214-229
     for (const auto& m : st_.scale_masks)
@@ -780,6 +789,8 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
                           height_, 1, stream_);
       if (i == 0 && h.track_per_scale_masks)
         SubMinorUpdateAutoMask(h, int(cube_.n_images), st_.scale_masks[swp].get(), stream_);
+      if (i == 0 && h.config.track_components)
+        SubMinorUpdateComponentList(h, int(cube_.n_images), swp, stream_);
       // model += Transform(full model, scale)  (multiscale_algorithm.cc:442-460)
       if (S[swp].scale != 0.0f)
         conv_.ConvolveWith(scratch_.get(), width_, height_, ScaleSpectrum(swp), cube_.model.p[i], width_,

@@ -19,6 +19,8 @@
 #include "fft.cuh"
 #include "subminor.cuh"
 
+#include <vector>
+
 namespace rdl {
 
 namespace {
@@ -526,6 +528,31 @@ void SubMinorUpdateAutoMask(rdl_handle& h, int n_images, uint8_t* mask, cudaStre
   AutoMaskKernel<<<ScatterGrid(b.n_selected), 256, 0, stream>>>(
       b.positions.get(), model, n_images, int(b.n_selected), int(b.width), mask);
   ++h.launches;
+}
+
+// SubMinorLoop::UpdateComponentList (subminor_loop.cc:230-246): one component per selected pixel
+// whose model is non-zero in any image, in the order of the selection (row-major).
+void SubMinorUpdateComponentList(rdl_handle& h, int n_images, size_t scale_index,
+                                 cudaStream_t stream) {
+  SubMinorBuffers& b = h.sub;
+  if (b.n_selected == 0) return;
+  std::vector<float> model(size_t(n_images) * b.n_selected);
+  std::vector<uint32_t> positions(b.n_selected);
+  RDL_CUDA(cudaMemcpyAsync(model.data(), b.model.get(), model.size() * sizeof(float),
+                           cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaMemcpyAsync(positions.data(), b.positions.get(),
+                           positions.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+  float values[kMaxImages];
+  for (size_t px = 0; px != b.n_selected; ++px) {
+    bool non_zero = false;
+    for (int i = 0; i != n_images; ++i) {
+      values[i] = model[size_t(i) * b.n_selected + px];
+      non_zero = non_zero || values[i] != 0.0f;
+    }
+    if (non_zero)
+      h.components.Add(positions[px] & 0xffffu, positions[px] >> 16, scale_index, values);
+  }
 }
 
 void SubMinorCollectTrace(rdl_handle& h, cudaStream_t stream) {

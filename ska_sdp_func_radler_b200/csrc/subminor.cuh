@@ -43,6 +43,9 @@ void SubMinorScatterModel(rdl_handle& h, int image_index, float* full, size_t n_
 void SubMinorAddModelTo(rdl_handle& h, int image_index, float* model_full, cudaStream_t stream);
 // UpdateAutoMask (subminor_loop.cc:220-228)
 void SubMinorUpdateAutoMask(rdl_handle& h, int n_images, uint8_t* mask, cudaStream_t stream);
+// UpdateComponentList (subminor_loop.cc:230-246): appends to h.components
+void SubMinorUpdateComponentList(rdl_handle& h, int n_images, size_t scale_index,
+                                 cudaStream_t stream);
 // appends the device trace of the last run to h.trace_host
 void SubMinorCollectTrace(rdl_handle& h, cudaStream_t stream);
 

@@ -229,3 +229,40 @@ def test_multiscale_without_sub_minor_loop_automask(rdl, oracle, torch_cuda):
                                    algs=algs)
     assert o2.iteration_number > o.iteration_number
     check(o2, oi2, g2, gi2, algs, minor_before=minor_before, image_scale=scale)
+
+
+@pytest.mark.parametrize("fast", [True, False])
+def test_multiscale_component_list(rdl, oracle, torch_cuda, fast):
+    """settings.save_source_list: MultiScaleAlgorithm keeps every component (position, scale,
+    one value per image) over the major iterations; after ComponentList::MergeDuplicates the
+    list must equal the reference's own (oracle/_ref): same positions in the same order, values
+    within the FFT tolerance. Joined channels with the polynomial fit, two major iterations."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, c = 128, 3
+    res, psfs, weights, freqs = multiscale_case(n, c, seed=3)
+    kw = dict(max_iterations=400 if fast else 150, major_loop_gain=0.9, clean_border_ratio=0.0)
+    ref = oracle.Reference("multiscale", n, n, c, weights=weights, frequencies=freqs, beam_size=6.0,
+                           max_scales=4, track_components=True, fast_sub_minor_loop=fast,
+                           fit_terms=2, **kw)
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4, track_components=True,
+                                  fast_sub_minor_loop=fast)
+    alg.apply(**kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, freqs, weights, 1)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, n, n), device="cuda")
+    d_psf = torch.from_numpy(psfs).cuda()
+    for call in range(2):
+        w = ref.execute(r_res, r_model, psfs)
+        g = alg.execute_major_iteration(rdl.Cube(n, n, c, 1, weights), d_res, d_model, d_psf)
+        assert g.iteration_number == w.iteration_number, call
+    want, got = ref.component_list(c), alg.component_list(c)
+    assert len(got) == len(want) and sum(len(x) for x, _, _ in want) > 20
+    peak = float(np.abs(res).max())
+    for scale, ((wx, wy, wv), (gx, gy, gv)) in enumerate(zip(want, got)):
+        assert np.array_equal(gx, wx) and np.array_equal(gy, wy), scale
+        assert np.abs(gv - wv).max(initial=0.0) <= 1e-5 * peak, scale
+    # the model is what the components add up to (scale 0 components are single pixels)
+    alg.clear_component_list()
+    assert alg.component_list(c) == []
