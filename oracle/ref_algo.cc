@@ -335,28 +335,32 @@ int refa_parallel_scale_mask(void* handle, uint64_t i, uint64_t width, uint64_t 
   });
 }
 
-// MultiScaleAlgorithm::GetComponentList() of the first algorithm, after MergeDuplicates
+// The component list Radler would hand out (ParallelDeconvolution::GetComponentList, :184-207):
+// the single algorithm's own list, or the list merged over the facets; after MergeDuplicates.
+}  // extern "C"
+namespace {
+ComponentList& ComponentsOf(Handle* h) {
+  if (h->parallel->algorithms_.size() == 1)
+    return static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
+        .GetComponentList();
+  return *h->parallel->component_list_;
+}
+}  // namespace
+extern "C" {
 uint64_t refa_component_count(void* handle, uint64_t scale) {
-  Handle* h = static_cast<Handle*>(handle);
-  auto& list = static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
-                   .GetComponentList();
+  ComponentList& list = ComponentsOf(static_cast<Handle*>(handle));
   list.MergeDuplicates();
   return scale < list.NScales() ? list.ComponentCount(scale) : 0;
 }
 uint64_t refa_component_scales(void* handle) {
-  Handle* h = static_cast<Handle*>(handle);
-  return static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
-      .GetComponentList()
-      .NScales();
+  return ComponentsOf(static_cast<Handle*>(handle)).NScales();
 }
 int refa_component_get(void* handle, uint64_t scale, uint64_t i, uint64_t* x, uint64_t* y,
                        float* values) {
   Handle* h = static_cast<Handle*>(handle);
   return Guard(h, [&] {
-    auto& list = static_cast<algorithms::MultiScaleAlgorithm&>(h->parallel->FirstAlgorithm())
-                     .GetComponentList();
     size_t px = 0, py = 0;
-    list.GetComponent(scale, i, px, py, values);
+    ComponentsOf(h).GetComponent(scale, i, px, py, values);
     *x = px;
     *y = py;
   });

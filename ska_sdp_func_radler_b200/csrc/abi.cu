@@ -332,25 +332,39 @@ rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* o
   *out = MultiScaleScaleInfo(*h->ms, i);
   return RDL_OK;
 }
-uint64_t rdl_component_scale_count(const rdl_handle* h) { return h ? h->components.scales.size() : 0; }
+}  // extern "C"
+namespace {
+// the handle's own list, or the list of the single algorithm behind a 1 x 1 facet run
+rdl::ComponentList& ComponentsOf(rdl_handle* h) {
+  if (h->components.Empty())
+    if (rdl_handle* single = ParallelSingleAlgorithm(*h)) return single->components;
+  return h->components;
+}
+}  // namespace
+extern "C" {
+
+uint64_t rdl_component_scale_count(const rdl_handle* h) {
+  return h ? ComponentsOf(const_cast<rdl_handle*>(h)).scales.size() : 0;
+}
 
 rdl_status rdl_component_count(rdl_handle* h, uint64_t scale_index, uint64_t* count) {
-  if (!h || !count || scale_index >= h->components.scales.size()) return RDL_ERR_INVALID_ARGUMENT;
+  if (!h || !count || scale_index >= ComponentsOf(h).scales.size()) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
-    h->components.MergeDuplicates();
-    *count = h->components.scales[scale_index].x.size();
+    ComponentsOf(h).MergeDuplicates();
+    *count = ComponentsOf(h).scales[scale_index].x.size();
   });
 }
 
 rdl_status rdl_component_get(rdl_handle* h, uint64_t scale_index, uint64_t first, uint64_t count,
                              uint64_t* x, uint64_t* y, float* values) {
-  if (!h || !x || !y || !values || scale_index >= h->components.scales.size())
+  if (!h || !x || !y || !values || scale_index >= ComponentsOf(h).scales.size())
     return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
-    h->components.MergeDuplicates();
-    const rdl::ComponentScaleList& list = h->components.scales[scale_index];
+    rdl::ComponentList& components = ComponentsOf(h);
+    components.MergeDuplicates();
+    const rdl::ComponentScaleList& list = components.scales[scale_index];
     if (first + count > list.x.size()) throw std::invalid_argument("component range out of bounds");
-    const size_t n_values = h->components.n_values;
+    const size_t n_values = components.n_values;
     for (uint64_t k = 0; k != count; ++k) {
       x[k] = list.x[first + k];
       y[k] = list.y[first + k];
@@ -360,7 +374,9 @@ rdl_status rdl_component_get(rdl_handle* h, uint64_t scale_index, uint64_t first
 }
 
 void rdl_component_list_clear(rdl_handle* h) {
-  if (h) h->components = rdl::ComponentList{};
+  if (!h) return;
+  if (rdl_handle* single = ParallelSingleAlgorithm(*h)) single->components = rdl::ComponentList{};
+  h->components = rdl::ComponentList{};
 }
 
 rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out) {

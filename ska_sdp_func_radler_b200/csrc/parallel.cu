@@ -233,6 +233,25 @@ void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
   if (!converging && !find_peak_only) f.reached_major_threshold = false;
   if (!h.rms_host.empty()) rdl_set_rms_factor_image(&a, nullptr, 0, 0);
 
+  if (h.config.track_components && a.config.algorithm == RDL_MULTISCALE) {
+    // the facet's components join the frame's list at the facet's offset (:465-479)
+    if (converging && !a.components.Empty()) {
+      ComponentList& frame = h.components;
+      if (frame.Empty()) {
+        frame.width = W;
+        frame.height = cube.height;
+        frame.n_values = cube.n_images;
+      }
+      if (a.components.scales.size() > frame.scales.size())
+        frame.scales.resize(a.components.scales.size());
+      for (size_t s = 0; s != a.components.scales.size(); ++s) {
+        const ComponentScaleList& list = a.components.scales[s];
+        for (size_t k = 0; k != list.x.size(); ++k)
+          frame.Add(list.x[k] + f.x, list.y[k] + f.y, s, &list.values[k * frame.n_values]);
+      }
+    }
+    a.components = ComponentList{};
+  }
   if (find_peak_only) {
     a.settings.max_iterations = max_iterations;
     return;
@@ -379,8 +398,10 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
     st.iterations.assign(1, a.iteration_number);
     return r;
   }
-  if ((h.track_per_scale_masks || h.use_per_scale_masks) && h.dist.comm && h.dist.world > 1)
-    throw std::domain_error("per-scale masks under facets sharded over several GPUs are not built");
+  if ((h.track_per_scale_masks || h.use_per_scale_masks || h.config.track_components) &&
+      h.dist.comm && h.dist.world > 1)
+    throw std::domain_error(
+        "per-scale masks / component lists under facets sharded over several GPUs are not built");
 
   const size_t W = cube.width, H = cube.height, A = cube.Pixels();
   // image = data_image.GetLinearIntegrated(); the dividers follow its minimum-power paths
@@ -449,6 +470,13 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
 void ParallelTiming(const rdl_handle& h, double& geometry_ms, double& total_ms) {
   geometry_ms = h.parallel ? h.parallel->geometry_ms : 0.0;
   total_ms = h.parallel ? h.parallel->total_ms : 0.0;
+}
+
+// ParallelDeconvolution::GetComponentList (:184-207): without facets the list is the single
+// algorithm's own.
+rdl_handle* ParallelSingleAlgorithm(const rdl_handle& h) {
+  if (!h.parallel || h.parallel->algorithms.size() != 1) return nullptr;
+  return h.parallel->algorithms.front();
 }
 
 size_t ParallelFacetCount(const rdl_handle& h) { return h.parallel ? h.parallel->facets.size() : 0; }

@@ -17,6 +17,8 @@ struct FacetInfo {
   int reached_major_threshold;
   uint64_t iteration_number;
 };
+// the one algorithm of a 1 x 1 grid run (nullptr otherwise)
+rdl_handle* ParallelSingleAlgorithm(const rdl_handle& h);
 size_t ParallelFacetCount(const rdl_handle& h);
 FacetInfo ParallelFacet(const rdl_handle& h, size_t i);
 // host copy of a facet's boundary mask (width * height bytes)

@@ -87,8 +87,9 @@ def test_multiscale_facets_two_phase_automask(rdl, oracle, torch_cuda):
     res, psfs, weights, freqs = multiscale_case(n, 1, seed=7)
     ref = oracle.Reference("multiscale", n, n, 1, weights=weights, frequencies=freqs, beam_size=6.0,
                            max_scales=4, grid=grid, threads=1, max_iterations=20000,
+                           track_components=True,
                            major_loop_gain=0.8, clean_border_ratio=0.0)
-    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4)
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4, track_components=True)
     alg.apply(max_iterations=20000, major_loop_gain=0.8, clean_border_ratio=0.0)
     r_res, r_model = res.copy(), np.zeros_like(res)
     d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((1, n, n), device="cuda")
@@ -114,3 +115,9 @@ def test_multiscale_facets_two_phase_automask(rdl, oracle, torch_cuda):
         assert np.abs(d_res.cpu().numpy() - r_res).max() <= 1e-5 * peak, phase
         assert np.abs(d_model.cpu().numpy() - r_model).max() <= 1e-5 * max(np.abs(r_model).max(), 1e-30), phase
     assert sum(f["iteration_number"] for f in alg.facets()) > 50
+    # save_source_list: the facets' component lists merged at their offsets (:465-479)
+    want_list, got_list = ref.component_list(1), alg.component_list(1)
+    assert len(got_list) == len(want_list) and sum(len(x) for x, _, _ in want_list) > 50
+    for scale, ((wx, wy, wv), (gx, gy, gv)) in enumerate(zip(want_list, got_list)):
+        assert np.array_equal(gx, wx) and np.array_equal(gy, wy), scale
+        assert np.abs(gv - wv).max(initial=0.0) <= 1e-5 * peak, scale
