@@ -60,7 +60,9 @@ struct Plan {
 };
 
 // One padding slot per 32 complex values keeps the strided late stages off the same banks.
-__host__ __device__ __forceinline__ int Pad(int i) { return i + (i >> 5); }
+// one pad slot per 32 elements (unit-stride butterflies) and one more per 512: the digit-reversed
+// gathers of the split phase walk with stride n/8, which the first term alone maps to one bank
+__host__ __device__ __forceinline__ int Pad(int i) { return i + (i >> 5) + (i >> 9); }
 inline int PaddedLength(int n) { return (Pad(n - 1) + 1) | 1; }
 
 __device__ __forceinline__ float2 operator+(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
