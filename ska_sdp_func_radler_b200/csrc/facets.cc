@@ -7,9 +7,12 @@
 #include "facets.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <exception>
 #include <limits>
+#include <mutex>
 #include <stdexcept>
 #include <thread>
 
@@ -290,12 +293,123 @@ void CropBox(uint8_t* dst, size_t x, size_t y, size_t w, size_t h, const uint8_t
     std::copy_n(src + (y + row) * src_width + x, w, dst + row * w);
 }
 
+// f(i) for i in [begin, end) on up to hardware_concurrency threads
 template <typename F>
 void RunOnThreads(size_t begin, size_t end, F&& f) {
+  if (end <= begin) return;
+  const size_t n_workers =
+      std::min<size_t>(end - begin, std::max(1u, std::thread::hardware_concurrency()));
+  std::atomic<size_t> next{begin};
+  std::exception_ptr failure;
+  std::mutex failure_lock;
   std::vector<std::thread> pool;
-  for (size_t i = begin; i < end; ++i) pool.emplace_back([&f, i] { f(i); });
+  for (size_t w = 0; w != n_workers; ++w)
+    pool.emplace_back([&] {
+      try {
+        for (size_t i = next.fetch_add(1); i < end; i = next.fetch_add(1)) f(i);
+      } catch (...) {
+        std::lock_guard<std::mutex> guard(failure_lock);
+        if (!failure) failure = std::current_exception();
+        next.store(end);
+      }
+    });
   for (std::thread& t : pool) t.join();
+  if (failure) std::rethrow_exception(failure);
 }
+}  // namespace
+
+namespace {
+
+// FloodArea without the frame-sized mask: along every line of the primary axis the area between
+// two dividers is one run of pixels [lo, hi), so two numbers per line describe it.
+struct AreaRuns {
+  std::vector<uint32_t> lo, hi;  // per primary coordinate
+  size_t start = 0, extent = 0;  // lateral range covered by any run
+};
+
+AreaRuns FloodRuns(const float* dividers, size_t width, size_t height, size_t inside,
+                   bool vertical) {
+  const Axes at{width, vertical};
+  const long n_lat = long(vertical ? width : height);
+  const size_t n_prim = vertical ? height : width;
+  AreaRuns runs;
+  runs.lo.resize(n_prim);
+  runs.hi.resize(n_prim);
+  size_t start = size_t(n_lat), end = 0;
+  for (size_t prim = 0; prim != n_prim; ++prim) {
+    long lat = long(inside);
+    while (lat >= 0 && dividers[at(size_t(lat), prim)] == 0.0f) --lat;
+    while (lat >= 0 && dividers[at(size_t(lat), prim)] != 0.0f) --lat;
+    runs.lo[prim] = uint32_t(lat + 1);
+    lat = long(inside) + 1;
+    while (lat < n_lat && dividers[at(size_t(lat), prim)] == 0.0f) ++lat;
+    runs.hi[prim] = uint32_t(lat);
+    start = std::min(start, size_t(runs.lo[prim]));
+    end = std::max(end, size_t(runs.hi[prim]));
+  }
+  runs.start = start;
+  runs.extent = end < start ? 0 : end - start;
+  return runs;
+}
+
+// GetBoundingMask for the facet where a column area and a row area cross, straight into the
+// facet's own mask: the same box (grown to even sizes by one cleared column / row) and the same
+// pixels as BoundingMask + TrimBox on frame-sized masks.
+void FacetFromRuns(const AreaRuns& column, const AreaRuns& row, size_t width, size_t height,
+                   Facet& f) {
+  auto in = [&](size_t x, size_t y) {
+    return x >= column.lo[y] && x < column.hi[y] && y >= row.lo[x] && y < row.hi[x];
+  };
+  const size_t cx0 = column.start, cx1 = column.start + column.extent;
+  const size_t ry0 = row.start, ry1 = std::min(height, row.start + row.extent);
+  size_t x_lo = cx1, y_lo = height, x_hi = 0, y_hi = 0;
+  for (size_t y = ry0; y < ry1; ++y) {
+    const size_t xa = std::max<size_t>(cx0, column.lo[y]), xb = std::min<size_t>(cx1, column.hi[y]);
+    for (size_t x = xa; x < xb; ++x)
+      if (y >= row.lo[x] && y < row.hi[x]) {
+        x_lo = std::min(x_lo, x);
+        x_hi = std::max(x_hi, x);
+        y_lo = std::min(y_lo, y);
+        y_hi = y;
+      }
+  }
+  size_t sub_x = x_lo, sub_y = y_lo, sub_w = 0, sub_h = 0;
+  if (x_hi >= x_lo) {
+    sub_w = x_hi + 1 - x_lo;
+    sub_h = y_hi + 1 - y_lo;
+  }
+  // even frames keep even facets: one more column / row, cleared (see BoundingMask)
+  long clear_x = -1, clear_y = -1;
+  size_t clear_x_rows_y = 0, clear_x_rows_h = 0;
+  if (width % 2 == 0 && sub_w % 2 != 0) {
+    ++sub_w;
+    clear_x = long(sub_x + sub_w - 1);
+    if (sub_w + sub_x >= width) clear_x = long(--sub_x);
+    clear_x_rows_y = sub_y;
+    clear_x_rows_h = sub_h;
+  }
+  if (height % 2 == 0 && sub_h % 2 != 0) {
+    ++sub_h;
+    clear_y = long(sub_y + sub_h - 1);
+    if (sub_h + sub_y >= height) clear_y = long(--sub_y);
+  }
+  f.x = sub_x;
+  f.y = sub_y;
+  f.width = sub_w;
+  f.height = sub_h;
+  f.mask.assign(sub_w * sub_h, 0);
+  for (size_t y = sub_y; y != sub_y + sub_h; ++y) {
+    if (long(y) == clear_y) continue;
+    uint8_t* out = &f.mask[(y - sub_y) * sub_w];
+    for (size_t x = sub_x; x != sub_x + sub_w; ++x) {
+      if (long(x) == clear_x && y >= clear_x_rows_y && y < clear_x_rows_y + clear_x_rows_h) continue;
+      // BoundingMask only writes the columns of the column area; the rest of the box is one of
+      // the cleared lines above
+      if (x >= cx0 && x < cx1) out[x - sub_x] = in(x, y) ? 1 : 0;
+    }
+  }
+}
+
 }  // namespace
 
 std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
@@ -307,13 +421,6 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
   // and then computes the horizontal ones. The searches only read `image` and write disjoint
   // strips, so all of them run at once here, into one image per orientation.
   std::vector<float> dividers(width * height, 0.0f), dividers_h(width * height, 0.0f);
-  std::vector<uint8_t> scratch_mask(width * height);
-
-  struct Column {
-    std::vector<uint8_t> mask;
-    size_t x = 0, width = 0;
-  };
-  std::vector<Column> columns(grid_width);
   const size_t n_vertical = grid_width - 1, n_dividers = n_vertical + grid_height - 1;
   RunOnThreads(0, n_dividers, [&](size_t k) {
     if (k < n_vertical) {
@@ -326,40 +433,31 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
                    false);
     }
   });
-  for (size_t d = 0; d != grid_width; ++d) {
-    Column& c = columns[d];
-    FloodArea(dividers.data(), width, height, d * width / grid_width + avg_w / 2, true,
-              scratch_mask.data(), c.x, c.width);
-    c.mask.resize(c.width * height);
-    CropBox(c.mask.data(), c.x, 0, c.width, height, scratch_mask.data(), width);
-  }
-  dividers.swap(dividers_h);
+  // FloodVerticalArea / FloodHorizontalArea for every column / row of facets, as runs per line
+  std::vector<AreaRuns> columns(grid_width), rows(grid_height);
+  RunOnThreads(0, grid_width + grid_height, [&](size_t k) {
+    if (k < grid_width)
+      columns[k] = FloodRuns(dividers.data(), width, height, k * width / grid_width + avg_w / 2,
+                             true);
+    else
+      rows[k - grid_width] = FloodRuns(dividers_h.data(), width, height,
+                                       (k - grid_width) * height / grid_height + avg_h / 2, false);
+  });
+  std::vector<float>().swap(dividers);
   std::vector<float>().swap(dividers_h);
 
-  std::vector<uint8_t> bounding(width * height);
-  std::vector<Facet> facets;
-  facets.reserve(grid_width * grid_height);
-  for (size_t gy = 0; gy != grid_height; ++gy) {
-    size_t row_y, row_h;
-    FloodArea(dividers.data(), width, height, gy * height / grid_height + avg_h / 2, false,
-              scratch_mask.data(), row_y, row_h);
-    for (size_t gx = 0; gx != grid_width; ++gx) {
-      Facet f;
-      f.index = facets.size();
-      const Column& c = columns[gx];
-      BoundingMask(c.mask.data(), c.x, c.width, scratch_mask.data(), bounding.data(), width,
-                   height, f.x, f.y, f.width, f.height);
-      f.mask.resize(f.width * f.height);
-      CropBox(f.mask.data(), f.x, f.y, f.width, f.height, bounding.data(), width);
-      f.boundary_mask = f.mask;
-      if (user_mask) {
-        for (size_t row = 0; row != f.height; ++row)
-          for (size_t col = 0; col != f.width; ++col)
-            f.mask[row * f.width + col] &= user_mask[(f.y + row) * width + f.x + col] ? 1 : 0;
-      }
-      facets.push_back(std::move(f));
+  std::vector<Facet> facets(grid_width * grid_height);
+  RunOnThreads(0, facets.size(), [&](size_t index) {
+    Facet& f = facets[index];
+    f.index = index;
+    FacetFromRuns(columns[index % grid_width], rows[index / grid_width], width, height, f);
+    f.boundary_mask = f.mask;
+    if (user_mask) {
+      for (size_t row = 0; row != f.height; ++row)
+        for (size_t col = 0; col != f.width; ++col)
+          f.mask[row * f.width + col] &= user_mask[(f.y + row) * width + f.x + col] ? 1 : 0;
     }
-  }
+  });
   return facets;
 }
 

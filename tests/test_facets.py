@@ -153,3 +153,34 @@ def test_facet_grid_tiles_the_frame():
         assert w % 2 == 0 and h % 2 == 0 and x + w <= 160 and y + h <= 128
         cover[y:y + h, x:x + w] += 1
     assert cover.min() >= 1  # bounding boxes overlap, together they cover the frame
+
+
+@pytest.mark.parametrize("shape,grid", [((128, 160), (4, 2)), ((96, 96), (3, 3)), ((131, 97), (2, 3)),
+                                        ((200, 256), (5, 4))])
+def test_facet_grid_equals_the_reference_steps(shape, grid):
+    """MakeSubImages (parallel_deconvolution.cc:69-168) builds the facets from the splitter's
+    steps; the product computes them from per-line runs instead of frame-sized masks. Boxes must
+    equal the composition of the individual steps, each of which is pinned to the reference's
+    source above (even / odd frame sizes: the even-size padding of the boxes)."""
+    rng = np.random.default_rng(shape[0] + grid[0])
+    img = rng.standard_normal(shape).astype(np.float32)
+    h, w = shape
+    gw, gh = grid
+    avg_w, avg_h = w // gw, h // gh
+    div_v = np.zeros_like(img)
+    for d in range(1, gw):
+        mid = w * d // gw
+        div_v += rdl.facet_dividing_path(img, mid - avg_w // 4, mid + avg_w // 4, True)
+    div_h = np.zeros_like(img)
+    for d in range(1, gh):
+        mid = h * d // gh
+        div_h += rdl.facet_dividing_path(img, mid - avg_h // 4, mid + avg_h // 4, False)
+    want = []
+    for gy in range(gh):
+        hm, _, _ = rdl.facet_flood_area(div_h, gy * h // gh + avg_h // 2, False)
+        for gx in range(gw):
+            vm, vx, vw = rdl.facet_flood_area(div_v, gx * w // gw + avg_w // 2, True)
+            _, box = rdl.facet_bounding_mask(np.ascontiguousarray(vm[:, vx:vx + vw]), vx, hm)
+            want.append(tuple(int(v) for v in box))
+    got = [tuple(int(v) for v in b) for b in rdl.facet_grid(img, gw, gh)]
+    assert got == want
