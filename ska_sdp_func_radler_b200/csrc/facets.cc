@@ -413,7 +413,8 @@ void FacetFromRuns(const AreaRuns& column, const AreaRuns& row, size_t width, si
 }  // namespace
 
 std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
-                              const uint8_t* user_mask, size_t grid_width, size_t grid_height) {
+                              const uint8_t* user_mask, size_t grid_width, size_t grid_height,
+                              const DividerSharing* sharing) {
   if (grid_width == 0 || grid_height == 0 || grid_width > width || grid_height > height)
     throw std::invalid_argument("bad facet grid");
   const size_t avg_w = width / grid_width, avg_h = height / grid_height;
@@ -422,7 +423,9 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
   // strips, so all of them run at once here, into one image per orientation.
   std::vector<float> dividers(width * height, 0.0f), dividers_h(width * height, 0.0f);
   const size_t n_vertical = grid_width - 1, n_dividers = n_vertical + grid_height - 1;
+  const bool shared = sharing && sharing->world > 1;
   RunOnThreads(0, n_dividers, [&](size_t k) {
+    if (shared && int(k % size_t(sharing->world)) != sharing->rank) return;
     if (k < n_vertical) {
       // each divider is searched inside the middle half of the strip between two facets
       const size_t mid = width * (k + 1) / grid_width;
@@ -433,6 +436,7 @@ std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
                    false);
     }
   });
+  if (shared) sharing->merge(dividers.data(), dividers_h.data(), width * height);
   // FloodVerticalArea / FloodHorizontalArea for every column / row of facets, as runs per line
   std::vector<AreaRuns> columns(grid_width), rows(grid_height);
   RunOnThreads(0, grid_width + grid_height, [&](size_t k) {

@@ -9,6 +9,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <functional>
 #include <vector>
 
 namespace rdl {
@@ -38,10 +39,20 @@ void BoundingMask(const uint8_t* vertical_mask, size_t vertical_mask_x, size_t v
                   const uint8_t* horizontal_mask, uint8_t* mask, size_t width, size_t height,
                   size_t& sub_x, size_t& sub_y, size_t& sub_width, size_t& sub_height);
 
+// Several processes that hold the same frame can split the divider searches (the expensive part
+// of the geometry): rank r searches dividers k with k % world == r into otherwise zero divider
+// images, and `merge` sums the two images over the ranks in place (every pixel belongs to at
+// most one divider, so the sum is exact).
+struct DividerSharing {
+  int rank = 0, world = 1;
+  std::function<void(float* vertical, float* horizontal, size_t n_pixels)> merge;
+};
+
 // MakeSubImages (parallel_deconvolution.cc:69-168). `image` = the integrated residual on the
 // host; user_mask may be null. Facets are ordered row-major over the grid.
 std::vector<Facet> MakeFacets(const float* image, size_t width, size_t height,
-                              const uint8_t* user_mask, size_t grid_width, size_t grid_height);
+                              const uint8_t* user_mask, size_t grid_width, size_t grid_height,
+                              const DividerSharing* sharing = nullptr);
 
 }  // namespace rdl
 #endif

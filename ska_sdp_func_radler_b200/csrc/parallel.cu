@@ -415,9 +415,26 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
                            cudaMemcpyDeviceToHost, stream));
   RDL_CUDA(cudaStreamSynchronize(stream));
   const auto geometry_start = std::chrono::steady_clock::now();
+  // several GPUs: every rank searches its share of the dividers, the divider images are summed
+  // over the ranks (the integrated image on the device is free to serve as the buffer)
+  DividerSharing sharing;
+  if (h.dist.comm && h.dist.world > 1) {
+    sharing.rank = h.dist.rank;
+    sharing.world = h.dist.world;
+    sharing.merge = [&](float* vertical, float* horizontal, size_t n_pixels) {
+      for (float* image : {vertical, horizontal}) {
+        RDL_CUDA(cudaMemcpyAsync(st.integrated.get(), image, n_pixels * sizeof(float),
+                                 cudaMemcpyHostToDevice, stream));
+        NcclAllReduceSumFloat(h.dist, st.integrated.get(), n_pixels, stream);
+        RDL_CUDA(cudaMemcpyAsync(image, st.integrated.get(), n_pixels * sizeof(float),
+                                 cudaMemcpyDeviceToHost, stream));
+        RDL_CUDA(cudaStreamSynchronize(stream));
+      }
+    };
+  }
   st.facets = MakeFacets(integrated.data(), W, H,
                          h.mask_host.empty() ? nullptr : h.mask_host.data(), grid_width,
-                         grid_height);
+                         grid_height, &sharing);
   st.geometry_ms = MsSince(geometry_start);
   std::vector<float>().swap(integrated);
 
