@@ -634,6 +634,8 @@ def run_reference_multiscale(args):
 
 
 def main():
+    # stdout carries the one JSON line: NCCL's version banner / debug output goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
