@@ -267,6 +267,15 @@ rdl_status rdl_integrate(rdl_handle* h, const rdl_cube_desc* cube, const float* 
 rdl_status rdl_convolve(rdl_handle* h, float* const* images, uint64_t n_images,
                         const float* device_kernel, uint64_t width, uint64_t height, void* stream);
 
+/* schaapcommon::math::PaddedConvolution as used by CorrectResidualDirty
+ * (subminor_loop.cc:195-218): out = Trim(Convolve(Untrim(image, padded), PrepareConvolutionKernel(
+ * Untrim(psf, padded)))). image / psf / out are width x height device images; out may alias
+ * image. The padded size is free (GenericClean: even(ceil(1.1f * N)), generic_clean.cc:63-66);
+ * sizes with large prime factors are evaluated through a larger smooth frame (same result). */
+rdl_status rdl_padded_convolution(rdl_handle* h, const float* device_image, const float* device_psf,
+                                  float* device_out, uint64_t width, uint64_t height,
+                                  uint64_t padded_width, uint64_t padded_height, void* stream);
+
 /* MultiScaleTransforms::Transform (multiscale_transforms.cc:11-23). */
 rdl_status rdl_multiscale_transform(rdl_handle* h, float* const* images, uint64_t n_images,
                                     uint64_t width, uint64_t height, float scale, int32_t shape,

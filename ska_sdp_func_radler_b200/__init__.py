@@ -92,7 +92,7 @@ EXPORTED_SYMBOLS = [
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
-    "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
@@ -162,6 +162,7 @@ def lib():
     L.rdl_integrate.argtypes = [vp, C.POINTER(_CubeDesc), vp, i32, vp, vp]
     L.rdl_convolve.argtypes = [vp, vp, u64, vp, u64, u64, vp]
     L.rdl_multiscale_transform.argtypes = [vp, vp, u64, u64, u64, f32, i32, vp]
+    L.rdl_padded_convolution.argtypes = [vp, vp, vp, vp, u64, u64, u64, u64, vp]
     L.rdl_good_fft_size.argtypes = [u64]
     L.rdl_good_fft_size.restype = u64
     L.rdl_parallel_execute_major_iteration.argtypes = [vp, u64, u64, C.POINTER(_CubeDesc), vp, vp,
@@ -511,6 +512,16 @@ class DeconvolutionAlgorithm:
         t, space = _plane_pointers(images, n, h * w)
         assert space == MEM_DEVICE
         self._check(lib().rdl_convolve(self._h, t, n, kernel.data_ptr(), w, h, stream))
+
+    def padded_psf_convolve(self, image, psf, padded_width, padded_height, stream=None):
+        """Trim(Convolve(Untrim(image), PrepareConvolutionKernel(Untrim(psf)))) on [H,W] device
+        images (subminor_loop.cc:195-218); returns a new device image."""
+        h, w = image.shape
+        out = image.clone()
+        self._check(lib().rdl_padded_convolution(self._h, image.data_ptr(), psf.data_ptr(),
+                                                 out.data_ptr(), w, h, padded_width, padded_height,
+                                                 stream))
+        return out
 
     def multiscale_transform(self, images, scale, shape=0, stream=None):
         n, h, w = images.shape

@@ -152,7 +152,10 @@ rdl_status rdl_create(const rdl_config* cfg, rdl_handle** out) {
   if (!(h->beam_size_in_pixels > 0.0)) h->beam_size_in_pixels = 1.0;
   const rdl_status st = Guard(h, [&] {
     RDL_CUDA(cudaSetDevice(h->device));
-    RDL_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    // a BLOCKING stream: with stream == NULL the calls are ordered after the caller's
+    // legacy-default-stream work that produced RDL_MEM_DEVICE planes (torch's default stream)
+    // and after the synchronous cudaMemcpy uploads of mask / RMS image / projection
+    RDL_CUDA(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamDefault));
   });
   if (st != RDL_OK) {
     g_create_error = h->error;
@@ -251,6 +254,7 @@ rdl_status rdl_set_clean_mask(rdl_handle* h, const uint8_t* mask, uint64_t width
   if (!h) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
     RDL_CUDA(cudaSetDevice(h->device));
+    ++h->mask_generation;
     if (!mask) {
       h->mask.Free();
       h->mask_host.clear();
@@ -270,6 +274,7 @@ rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t 
   if (!h) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
     RDL_CUDA(cudaSetDevice(h->device));
+    ++h->rms_generation;
     if (!image) {
       h->rms.Free();
       h->rms_host.clear();
@@ -293,6 +298,7 @@ rdl_status rdl_set_spectral_fitter(rdl_handle* h, int32_t mode, uint64_t n_terms
     if (mode != RDL_FIT_NONE && mode != RDL_FIT_POLYNOMIAL)
       throw std::domain_error("only kNoFitting and kPolynomial spectral fitting are supported");
     if (n_polarizations == 0) throw std::invalid_argument("n_polarizations must be >= 1");
+    ++h->fit_generation;
     h->fit_mode = mode;
     h->fit_terms = n_terms;
     h->fit_n_pol = n_polarizations;
@@ -398,6 +404,8 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
     if (!residual || !model || !psfs) throw std::invalid_argument("null image table");
     const bool sharded = h->dist.band_set;
     const uint64_t frame_height = sharded ? h->dist.global_height : c->height;
+    if (c->width * frame_height >= (1ull << 32))  // peak keys carry a 32-bit frame index
+      throw std::domain_error("frames of 2^32 pixels or more are not supported");
     if (sharded && (h->config.algorithm != RDL_GENERIC_CLEAN ||
                     (h->dist.block_rows
                          ? c->height * uint64_t(h->dist.world) != h->dist.global_height
@@ -575,6 +583,10 @@ rdl_status rdl_find_peak(rdl_handle* h, const rdl_cube_desc* c, const float* con
       cube.residual.p[i] = const_cast<float*>(images[i]);
     }
     SetVec(cube);
+    // the 128-bit path also reads the mask (uchar4) and the RMS image (float4)
+    if ((device_mask && (reinterpret_cast<uintptr_t>(device_mask) & 3u)) ||
+        (device_rms_factor && !Aligned16(device_rms_factor)))
+      cube.vec = 1;
     const IntegSpec spec = integration_mode == 0 ? MakeLinearSpec(cube) : MakeSquareSpec(cube);
     const PeakWindow w = MakePeakWindow(cube.width, cube.height, start_y, end_y, horizontal_border,
                                         vertical_border, device_mask, device_rms_factor,
@@ -650,6 +662,25 @@ rdl_status rdl_convolve(rdl_handle* h, float* const* images, uint64_t n_images,
     FftConvolver& conv = GetConvolver(*h, width, height);
     conv.SetKernel(device_kernel, stream);
     for (uint64_t i = 0; i != n_images; ++i) conv.Convolve(images[i], images[i], stream);
+    h->launches += conv.TakeLaunchCount();
+    RDL_CUDA(cudaGetLastError());
+  });
+}
+
+rdl_status rdl_padded_convolution(rdl_handle* h, const float* device_image, const float* device_psf,
+                                  float* device_out, uint64_t width, uint64_t height,
+                                  uint64_t padded_width, uint64_t padded_height, void* stream_v) {
+  if (!h || !device_image || !device_psf || !device_out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    if (padded_width < width || padded_height < height)
+      throw std::invalid_argument("the padded size is smaller than the image");
+    RDL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = StreamOf(h, stream_v);
+    FftConvolver& conv = GetConvolver(*h, padded_width, padded_height, width, height);
+    h->fft_spectrum.Reserve(conv.SpectrumSize());
+    conv.MakePsfKernelSpectrum(device_psf, width, height, h->fft_spectrum.get(), stream);
+    conv.ConvolveWith(device_image, width, height, h->fft_spectrum.get(), device_out, width, height,
+                      0, stream);
     h->launches += conv.TakeLaunchCount();
     RDL_CUDA(cudaGetLastError());
   });

@@ -21,6 +21,17 @@
 // small permutation table. Algorithmic HBM traffic: 28 bytes per padded pixel;
 // the four-step column transform moves 44.
 // Results are not bit-comparable with FFTW or the CPU checker; parity is by tolerance.
+//
+// Embedded frames. GenericClean pads to even(ceil(1.1f * N)) (generic_clean.cc:63-66) and facets
+// have data-dependent sizes, so a frame length can contain a large prime (8192 -> 9012 = 4 * 3 *
+// 751) for which FFTW falls back to Rader/Bluestein. Here such a frame is NOT transformed
+// directly: the circular convolution at P is, term for term, the sum
+//   out[x] = sum_x' src[x'] * k[(x - x') mod P],
+// and with sources and destinations confined to `content` pixels only displacements |d| < content
+// occur. Writing the kernel out over those displacements, K[d mod Q] = k[d mod P], gives the
+// identical sum as a circular convolution at any Q >= 2 * content - 1, so Q is chosen 2-3-5-7
+// smooth and the native engine is used. The result is the reference's circular convolution at P
+// (including its wrap-around), evaluated at FFT round-off like every other convolution here.
 #include "fft.cuh"
 
 #include <algorithm>
@@ -856,14 +867,66 @@ int TileThreads(int len) {
 }
 }  // namespace
 
-FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width_(width), height_(height) {
+// Embedded frames: K[d mod Q] = k[d mod P] for the displacements |dx| < cw, |dy| < ch, else 0.
+__global__ void ExpandKernelKernel(float* dst, int qw, int qh, const float* k, int w, int h, int cw,
+                                   int ch) {
+  const size_t total = size_t(qw) * qh;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const int jy = int(i / qw), jx = int(i - size_t(jy) * qw);
+    const int dy = jy < ch ? jy : jy - qh, dx = jx < cw ? jx : jx - qw;
+    float v = 0.0f;
+    if (dy > -ch && dx > -cw) v = __ldg(k + size_t(dy < 0 ? dy + h : dy) * w + (dx < 0 ? dx + w : dx));
+    dst[i] = v;
+  }
+}
+
+namespace {
+bool PlanSupported(size_t n) {
+  for (size_t p : {2, 3, 5, 7})
+    while (n % p == 0) n /= p;
+  for (size_t p = 11; n > 1; p += 2) {
+    if (p * p > n) p = n;
+    while (n % p == 0) {
+      if (p > size_t(kMaxGenericRadix)) return false;
+      n /= p;
+    }
+  }
+  return true;
+}
+}  // namespace
+
+bool FftConvolver::HasNativePlan(size_t width, size_t height) {
+  if (width < 2 || height < 1 || width % 2 != 0) return false;
+  if (!PlanSupported(width / 2) || !PlanSupported(height)) return false;
+  if (size_t(PaddedLength(int(width / 2))) * sizeof(float2) > kMaxSmemBytes) return false;
+  if (height > 512) {  // four-step columns: the contiguous factor has to fit in shared memory
+    size_t best = 1;
+    for (size_t f = 1; f * f <= height; ++f)
+      if (height % f == 0) best = f;
+    if ((height / best) * (kTileCols * sizeof(float2) + sizeof(float2)) > kMaxSmemBytes) return false;
+  }
+  return true;
+}
+
+FftConvolver::FftConvolver(size_t width, size_t height, size_t content_width, size_t content_height)
+    : impl_(new Impl), width_(width), height_(height),
+      content_w_(content_width ? std::min(content_width, width) : width),
+      content_h_(content_height ? std::min(content_height, height) : height) {
   Impl& d = *impl_;
   try {
-    if (width < 2 || height < 1 || width % 2 != 0)
-      throw std::domain_error("FFT convolution needs an even image width (got " +
-                              std::to_string(width) + " x " + std::to_string(height) + ")");
+    if (width < 1 || height < 1) throw std::invalid_argument("empty FFT frame");
     d.W = int(width);
     d.H = int(height);
+    if (!HasNativePlan(width, height)) {
+      const size_t qw = CalculateGoodFFTSize(std::max<size_t>(2 * content_w_ - 1, 2));
+      const size_t qh = CalculateGoodFFTSize(std::max<size_t>(2 * content_h_ - 1, 2));
+      if (!HasNativePlan(qw, qh))
+        throw std::domain_error("no FFT plan for a " + std::to_string(width) + " x " +
+                                std::to_string(height) + " frame");
+      inner_ = new FftConvolver(qw, qh);
+      return;
+    }
     d.n = d.W / 2;
     // whole 128-byte lines per spectrum row: the column passes work on 16-column tiles
     d.pitch = (d.n + 1 + kTileCols - 1) / kTileCols * kTileCols;
@@ -946,23 +1009,43 @@ FftConvolver::FftConvolver(size_t width, size_t height) : impl_(new Impl), width
   } catch (...) {
     delete impl_;
     impl_ = nullptr;
+    delete inner_;
+    inner_ = nullptr;
     throw;
   }
 }
 
-FftConvolver::~FftConvolver() { delete impl_; }
+FftConvolver::~FftConvolver() {
+  delete impl_;
+  delete inner_;
+}
 
-size_t FftConvolver::SpectrumSize() const { return size_t(impl_->H) * impl_->pitch; }
+size_t FftConvolver::SpectrumSize() const {
+  return inner_ ? inner_->SpectrumSize() : size_t(impl_->H) * impl_->pitch;
+}
 
-void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, cudaStream_t stream) {
+// embedded frames: impl_->kernel_image (W x H, origin at 0,0) -> spectrum of the inner frame
+void FftConvolver::ExpandKernel(float2* spectrum_out, cudaStream_t stream) {
   Impl& d = *impl_;
-  if (sw > size_t(d.W) || sh > size_t(d.H)) throw std::invalid_argument("source larger than the FFT frame");
+  Impl& q = *inner_->impl_;
+  q.kernel_image.Reserve(size_t(q.W) * q.H);
+  ExpandKernelKernel<<<1184, 256, 0, stream>>>(q.kernel_image.get(), q.W, q.H, d.kernel_image.get(),
+                                               d.W, d.H, int(content_w_), int(content_h_));
+  ++launches_;
+  inner_->MakeKernelSpectrum(q.kernel_image.get(), spectrum_out, stream);
+}
+
+void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, size_t ox, size_t oy,
+                               cudaStream_t stream) {
+  Impl& d = *impl_;
+  if (ox + sw > size_t(d.W) || oy + sh > size_t(d.H))
+    throw std::invalid_argument("source larger than the FFT frame");
   RowParams p{};
   p.src = src;
   p.sw = int(sw);
   p.sh = int(sh);
-  p.ox = (d.W - int(sw)) / 2;
-  p.oy = (d.H - int(sh)) / 2;
+  p.ox = int(ox);
+  p.oy = int(oy);
   p.W = d.W;
   p.H = d.H;
   p.spec = d.work.get();
@@ -982,7 +1065,17 @@ void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, cudaStrea
 
 void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectrum_out, cudaStream_t stream) {
   Impl& d = *impl_;
-  ForwardRows(kernel_image, d.W, d.H, stream);
+  if (inner_) {
+    // the caller's W x H kernel image (origin at 0,0) written out over the displacements
+    if (kernel_image != d.kernel_image.get()) {
+      d.kernel_image.Reserve(size_t(d.W) * d.H);
+      RDL_CUDA(cudaMemcpyAsync(d.kernel_image.get(), kernel_image, size_t(d.W) * d.H * sizeof(float),
+                               cudaMemcpyDeviceToDevice, stream));
+    }
+    ExpandKernel(spectrum_out, stream);
+    return;
+  }
+  ForwardRows(kernel_image, d.W, d.H, 0, 0, stream);
   ColParams c = d.MakeColParams();
   c.kspec_out = spectrum_out;
   c.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
@@ -1011,6 +1104,7 @@ void FftConvolver::MakeSmallKernelSpectrum(const float* small_kernel, size_t n, 
   WrapSmallKernelKernel<<<std::min((total + 255) / 256, 1184), 256, 0, stream>>>(
       d.kernel_image.get(), d.W, d.H, small_kernel, int(n));
   ++launches_;
+  if (inner_) return ExpandKernel(spectrum_out, stream);
   MakeKernelSpectrum(d.kernel_image.get(), spectrum_out, stream);
 }
 
@@ -1021,19 +1115,43 @@ void FftConvolver::MakePsfKernelSpectrum(const float* psf, size_t pw, size_t ph,
   d.kernel_image.Reserve(size_t(d.W) * d.H);
   PreparePsfKernelKernel<<<1184, 256, 0, stream>>>(d.kernel_image.get(), d.W, d.H, psf, int(pw), int(ph));
   ++launches_;
+  if (inner_) return ExpandKernel(spectrum_out, stream);
   MakeKernelSpectrum(d.kernel_image.get(), spectrum_out, stream);
 }
 
 void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const float2* kernel_spectrum,
                                 float* dst, size_t dw, size_t dh, int mode, cudaStream_t stream) {
+  if (sw > width_ || sh > height_) throw std::invalid_argument("source larger than the FFT frame");
+  if (dw > width_ || dh > height_) throw std::invalid_argument("destination larger than the FFT frame");
+  // Image::Untrim / Trim: centred, start = (outer - inner) / 2
+  ConvolveAt(src, sw, sh, (width_ - sw) / 2, (height_ - sh) / 2, kernel_spectrum, dst, dw, dh,
+             (width_ - dw) / 2, (height_ - dh) / 2, mode, stream);
+}
+
+void FftConvolver::ConvolveAt(const float* src, size_t sw, size_t sh, size_t sox, size_t soy,
+                              const float2* kernel_spectrum, float* dst, size_t dw, size_t dh,
+                              size_t dox, size_t doy, int mode, cudaStream_t stream) {
+  if (inner_) {
+    // only the relative position matters for a circular convolution: shift both to the corner
+    if (sw > content_w_ || dw > content_w_ || sh > content_h_ || dh > content_h_)
+      throw std::invalid_argument("image larger than the content size of an embedded FFT frame");
+    const size_t bx = std::min(sox, dox), by = std::min(soy, doy);
+    if (sox - bx + sw > content_w_ || dox - bx + dw > content_w_ || soy - by + sh > content_h_ ||
+        doy - by + dh > content_h_)
+      throw std::invalid_argument("source and destination are further apart than the content size");
+    inner_->ConvolveAt(src, sw, sh, sox - bx, soy - by, kernel_spectrum, dst, dw, dh, dox - bx,
+                       doy - by, mode, stream);
+    return;
+  }
   Impl& d = *impl_;
-  if (dw > size_t(d.W) || dh > size_t(d.H)) throw std::invalid_argument("destination larger than the FFT frame");
-  ForwardRows(src, sw, sh, stream);
+  if (dox + dw > size_t(d.W) || doy + dh > size_t(d.H))
+    throw std::invalid_argument("destination larger than the FFT frame");
+  ForwardRows(src, sw, sh, sox, soy, stream);
   ColParams c = d.MakeColParams();
   c.kspec = kernel_spectrum;
-  c.y0 = (d.H - int(sh)) / 2;
+  c.y0 = int(soy);
   c.y1 = c.y0 + int(sh);
-  c.out_y0 = (d.H - int(dh)) / 2;
+  c.out_y0 = int(doy);
   c.out_y1 = c.out_y0 + int(dh);
   const int tiles = d.pitch / kTileCols;
   if (d.H2 > 1) {
@@ -1059,7 +1177,7 @@ void FftConvolver::ConvolveWith(const float* src, size_t sw, size_t sh, const fl
   p.dst = dst;
   p.sw = int(dw);
   p.sh = int(dh);
-  p.ox = (d.W - int(dw)) / 2;
+  p.ox = int(dox);
   p.oy = c.out_y0;
   p.W = d.W;
   p.H = d.H;
@@ -1088,14 +1206,18 @@ void FftConvolver::SetKernel(const float* kernel, cudaStream_t stream) {
 void FftConvolver::Convolve(const float* in, float* out, cudaStream_t stream) {
   Impl& d = *impl_;
   if (d.kernel_spectrum.empty()) throw std::invalid_argument("FftConvolver::Convolve without a kernel");
-  ConvolveWith(in, d.W, d.H, d.kernel_spectrum.get(), out, d.W, d.H, 0, stream);
+  ConvolveWith(in, width_, height_, d.kernel_spectrum.get(), out, width_, height_, 0, stream);
 }
 
-FftConvolver& GetConvolver(rdl_handle& h, size_t width, size_t height) {
-  auto key = std::make_pair(width, height);
+FftConvolver& GetConvolver(rdl_handle& h, size_t width, size_t height, size_t content_width,
+                           size_t content_height) {
+  const std::array<size_t, 4> key{width, height, content_width ? content_width : width,
+                                  content_height ? content_height : height};
   auto it = h.convolvers.find(key);
   if (it == h.convolvers.end())
-    it = h.convolvers.emplace(key, std::make_shared<FftConvolver>(width, height)).first;
+    it = h.convolvers
+             .emplace(key, std::make_shared<FftConvolver>(width, height, key[2], key[3]))
+             .first;
   return *it->second;
 }
 

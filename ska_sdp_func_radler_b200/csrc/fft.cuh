@@ -17,8 +17,14 @@ size_t GetConvolutionSize(double convolution_scale, size_t original_size, double
 // In-place circular convolution engine for one (width, height).
 class FftConvolver {
  public:
-  FftConvolver(size_t width, size_t height);
+  // content_width x content_height: the largest source / destination ever passed to
+  // ConvolveWith (0 = the whole frame). Only used when the frame has no native plan.
+  FftConvolver(size_t width, size_t height, size_t content_width = 0, size_t content_height = 0);
   ~FftConvolver();
+  // true when width x height is transformed directly; false when the circular convolution is
+  // evaluated through a larger smooth frame (see fft.cu, "embedded frames")
+  bool Native() const { return inner_ == nullptr; }
+  static bool HasNativePlan(size_t width, size_t height);
   size_t Width() const { return width_; }
   size_t Height() const { return height_; }
   // Transforms `kernel` (already wrapped around the origin) and keeps its spectrum.
@@ -41,21 +47,29 @@ class FftConvolver {
   // mode 0: dst = result, 1: dst -= result, 2: dst += result. src may equal dst.
   void ConvolveWith(const float* src, size_t sw, size_t sh, const float2* kernel_spectrum,
                     float* dst, size_t dw, size_t dh, int mode, cudaStream_t stream);
+  // The same with explicit positions of the source and the destination inside the frame.
+  void ConvolveAt(const float* src, size_t sw, size_t sh, size_t sox, size_t soy,
+                  const float2* kernel_spectrum, float* dst, size_t dw, size_t dh, size_t dox,
+                  size_t doy, int mode, cudaStream_t stream);
   uint64_t TakeLaunchCount() {
-    const uint64_t n = launches_;
+    const uint64_t n = launches_ + (inner_ ? inner_->TakeLaunchCount() : 0);
     launches_ = 0;
     return n;
   }
 
  private:
-  void ForwardRows(const float* src, size_t sw, size_t sh, cudaStream_t stream);
+  void ForwardRows(const float* src, size_t sw, size_t sh, size_t ox, size_t oy, cudaStream_t stream);
+  void ExpandKernel(float2* spectrum_out, cudaStream_t stream);
   struct Impl;
-  Impl* impl_;
-  size_t width_, height_;
+  Impl* impl_ = nullptr;
+  FftConvolver* inner_ = nullptr;  // embedded frames: the engine of the larger smooth frame
+  size_t width_, height_, content_w_, content_h_;
   uint64_t launches_ = 0;
 };
 
-FftConvolver& GetConvolver(rdl_handle& h, size_t width, size_t height);
+// content_*: see FftConvolver's constructor
+FftConvolver& GetConvolver(rdl_handle& h, size_t width, size_t height, size_t content_width = 0,
+                           size_t content_height = 0);
 
 }  // namespace rdl
 #endif

@@ -3,6 +3,7 @@
 #ifndef RDL_HANDLE_H_
 #define RDL_HANDLE_H_
 
+#include <array>
 #include <map>
 #include <memory>
 #include <string>
@@ -140,6 +141,9 @@ struct rdl_handle {
   rdl::DeviceBuffer<float> rms;
   std::vector<float> rms_host;
   size_t rms_w = 0, rms_h = 0;
+  // bumped by the setters; facet clones remember the parent's value they were last synced to
+  uint64_t mask_generation = 0, rms_generation = 0, fit_generation = 0;
+  uint64_t synced_mask = 0, synced_rms = 0, synced_fit = 0;
 
   // spectral fitter
   int32_t fit_mode = RDL_FIT_NONE;
@@ -183,7 +187,7 @@ struct rdl_handle {
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone
   // FFT engines by frame size (plans, twiddle tables, work spectrum); not cloned
-  std::map<std::pair<size_t, size_t>, std::shared_ptr<rdl::FftConvolver>> convolvers;
+  std::map<std::array<size_t, 4>, std::shared_ptr<rdl::FftConvolver>> convolvers;
 };
 
 namespace rdl {

@@ -127,6 +127,9 @@ void EnsureAlgorithms(rdl_handle& h, ParallelState& st, size_t n) {
   for (size_t i = 0; i != n; ++i) {  // SetAlgorithm: algorithms_[i] = front()->Clone()
     rdl_handle* c = nullptr;
     if (rdl_clone(&h, &c) != RDL_OK) throw std::runtime_error("cloning the facet algorithm failed");
+    c->synced_mask = h.mask_generation;  // rdl_clone copied mask, RMS image and fitter
+    c->synced_rms = h.rms_generation;
+    c->synced_fit = h.fit_generation;
     st.algorithms.push_back(c);
   }
 }
@@ -382,11 +385,31 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
     a->track_per_scale_masks = h.track_per_scale_masks;
     a->use_per_scale_masks = h.use_per_scale_masks;
     a->trace_capacity = 0;
+    // SetSpectralFitter set or changed on the parent after the clones were made
+    if (a->synced_fit != h.fit_generation) {
+      if (rdl_set_spectral_fitter(a, h.fit_mode, h.fit_terms, h.fit_freqs.data(),
+                                  h.fit_weights.data(), h.fit_freqs.size(), h.fit_n_pol) != RDL_OK)
+        throw std::runtime_error(a->error);
+      a->synced_fit = h.fit_generation;
+    }
   }
   if (n_facets == 1) {
-    // ExecuteSingleThreadedRun (:505-546): the algorithm on the whole frame, user mask and all
+    // ExecuteSingleThreadedRun (:505-546): the algorithm on the whole frame, user mask and all.
+    // SetCleanMask / SetRmsFactorImage are forwarded on every call (:244-292): a mask or RMS
+    // image set, replaced or CLEARED on the parent since the last call reaches the algorithm.
     rdl_handle& a = *st.algorithms.front();
-    if (!h.mask_host.empty()) rdl_set_clean_mask(&a, h.mask_host.data(), h.mask_w, h.mask_h);
+    if (a.synced_mask != h.mask_generation) {
+      if (rdl_set_clean_mask(&a, h.mask_host.empty() ? nullptr : h.mask_host.data(), h.mask_w,
+                             h.mask_h) != RDL_OK)
+        throw std::runtime_error(a.error);
+      a.synced_mask = h.mask_generation;
+    }
+    if (a.synced_rms != h.rms_generation) {
+      if (rdl_set_rms_factor_image(&a, h.rms_host.empty() ? nullptr : h.rms_host.data(), h.rms_w,
+                                   h.rms_h) != RDL_OK)
+        throw std::runtime_error(a.error);
+      a.synced_rms = h.rms_generation;
+    }
     const rdl_result r = RunAlgorithm(a, cube, stream);
     h.launches += a.launches;
     a.launches = 0;

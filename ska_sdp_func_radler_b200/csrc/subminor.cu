@@ -577,6 +577,9 @@ rdl_result RunGenericCleanSubMinor(rdl_handle& h, DeviceCube& cube, cudaStream_t
   size_t conv_h = size_t(std::ceil(padding * float(height)));
   if (conv_w % 2 != 0) ++conv_w;
   if (conv_h % 2 != 0) ++conv_h;
+  // the FFT plan is made (or refused) before anything is changed: a failing call leaves the
+  // handle and the images untouched
+  FftConvolver& conv = GetConvolver(h, conv_w, conv_h, width, height);
 
   const IntegSpec linear = MakeLinearSpec(cube);
   ConstPtrTable resid{};
@@ -642,7 +645,6 @@ rdl_result RunGenericCleanSubMinor(rdl_handle& h, DeviceCube& cube, cudaStream_t
   max_value = o.max_value;
 
   // CorrectResidualDirty per image (subminor_loop.cc:195-218) + model += components
-  FftConvolver& conv = GetConvolver(h, conv_w, conv_h);
   h.fft_scratch.Reserve(n);
   h.fft_spectrum.Reserve(conv.SpectrumSize());
   size_t spectrum_of_psf = size_t(-1);

@@ -121,3 +121,42 @@ def test_multiscale_facets_two_phase_automask(rdl, oracle, torch_cuda):
     for scale, ((wx, wy, wv), (gx, gy, gv)) in enumerate(zip(want_list, got_list)):
         assert np.array_equal(gx, wx) and np.array_equal(gy, wy), scale
         assert np.abs(gv - wv).max(initial=0.0) <= 1e-5 * peak, scale
+
+
+@pytest.mark.parametrize("grid", [(1, 1), (2, 2)])
+def test_rms_image_and_mask_changed_between_parallel_calls(rdl, oracle, torch_cuda, grid):
+    """ParallelDeconvolution forwards SetRmsFactorImage / SetCleanMask to its algorithms on every
+    call (parallel_deconvolution.cc:244-292): an RMS image set after the first call, then a mask
+    set and later cleared again, must reach the facet algorithms (the clones used to
+    keep what they were cloned with)."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, c = 128, 1
+    res, psfs, weights, _ = hogbom_case(n, c)
+    rng = np.random.default_rng(12)
+    rms = rng.uniform(0.5, 1.5, (n, n)).astype(np.float32)
+    mask = np.zeros((n, n), np.uint8)
+    mask[20:110, 10:90] = 1
+    ref = oracle.Reference("generic", n, n, c, weights=weights, use_sub_minor_optimization=False,
+                           grid=grid, threads=1, max_iterations=10000, major_loop_gain=0.6)
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    alg.apply(max_iterations=10000, major_loop_gain=0.6, clean_border_ratio=0.0)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, n, n), device="cuda")
+    d_psf = torch.from_numpy(psfs).cuda()
+    cube = rdl.Cube(n, n, c, 1, weights)
+    steps = [dict(), dict(rms=rms), dict(mask=mask), dict(rms=None), dict(mask=None)]
+    for k, step in enumerate(steps):
+        if "rms" in step:
+            ref.set_rms_factor_image(step["rms"])
+            alg.set_rms_factor_image(step["rms"])
+        if "mask" in step:
+            ref.set_clean_mask(step["mask"])
+            alg.set_clean_mask(step["mask"])
+        w = ref.execute(r_res, r_model, psfs)
+        g = alg.parallel_execute_major_iteration(grid[0], grid[1], cube, d_res, d_model, d_psf)
+        assert g.another_iteration_required == w.another_iteration_required, k
+        assert np.float32(g.final_peak_value) == np.float32(w.final_peak_value), k
+        assert np.array_equal(d_res.cpu().numpy(), r_res), k
+        assert np.array_equal(d_model.cpu().numpy(), r_model), k

@@ -11,7 +11,10 @@ TOL = 1e-5
 SIZES = [(64, 64), (30, 42), (18, 128), (250, 256), (512, 384), (1176, 1134),
          (1128, 1128),   # GenericClean padding of 1024: 2^3 * 3 * 47 (generic prime radix)
          (2254, 282),    # 2 * 7^2 * 23
-         (4608, 4536)]   # multiscale padded sizes of 4096
+         (4608, 4536),   # multiscale padded sizes of 4096
+         # frames with a prime factor > 127 (or an odd width): evaluated through a larger smooth
+         # frame (fft.cu, "embedded frames"); 1502 = 2 * 751 is GenericClean's padding of 1364
+         (302, 254), (16, 15), (131, 151), (1502, 1502), (64, 4506)]
 
 
 def _f64_convolve(img, ker):
@@ -52,12 +55,25 @@ def test_convolve_matches_oracle(rdl, oracle, torch_cuda):
         assert np.abs(got - want).max() / np.abs(want).max() < TOL
 
 
-def test_odd_width_is_rejected_loudly(rdl, torch_cuda):
+def test_padded_convolution_large_prime_frame(rdl, oracle, torch_cuda):
+    """CorrectResidualDirty's convolution (subminor_loop.cc:195-218) at GenericClean's padded size
+    with a large prime factor: Untrim -> circular convolution at P -> Trim, wrap-around included
+    (the PSF is as large as the image, so the aliasing terms are not negligible)."""
     torch = torch_cuda
-    dev = torch.zeros((1, 16, 15), dtype=torch.float32, device="cuda")
-    with pytest.raises(rdl.RadlerError) as e:
-        rdl.GenericClean().convolve(dev, torch.zeros((16, 15), dtype=torch.float32, device="cuda"))
-    assert e.value.status == rdl.RDL_ERR_UNSUPPORTED
+    rng = np.random.default_rng(8)
+    for n, p in [(238, 262), (252, 278)]:
+        model = np.zeros((n, n), np.float32)
+        model[rng.integers(0, n, 40), rng.integers(0, n, 40)] = rng.uniform(0.1, 2.0, 40)
+        psf = rng.standard_normal((n, n)).astype(np.float32) * 0.05
+        psf[n // 2, n // 2] = 1.0
+        kernel = oracle.prepare_convolution_kernel(oracle.untrim(psf, p, p))
+        want = oracle.trim(_f64_convolve(oracle.untrim(model, p, p), kernel), n, n)
+        res = rng.standard_normal((1, n, n)).astype(np.float32)
+        alg = rdl.GenericClean()
+        got = alg.padded_psf_convolve(torch.from_numpy(model).cuda(), torch.from_numpy(psf).cuda(),
+                                      p, p)
+        err = np.abs(got.cpu().numpy() - want).max() / np.abs(want).max()
+        assert err < TOL, (n, p, err)
 
 
 @pytest.mark.parametrize("shape", [0, 1])

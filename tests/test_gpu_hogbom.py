@@ -97,14 +97,17 @@ def test_subtract_image_kernel_matches_oracle(rdl, oracle, torch_cuda):
 
 
 def _run_both(rdl, oracle, res, psfs, weights, settings, sub_minor=False, device_resident=False,
-              fit=None):
+              fit=None, n_pol=1, pol_norm=1.0, squared_joins=False, pol_linked=None):
+    """res: [n_channels * n_pol, H, W] ordered [channel][pol]; psfs: [n_channels, H, W]."""
     c, h, w = res.shape
+    c //= n_pol
+    cube_args = (w, h, c, n_pol, weights, pol_linked, pol_norm, squared_joins)
     o_res, o_model = res.copy(), np.zeros_like(res)
     oalg = oracle.GenericClean(use_sub_minor_optimization=sub_minor)
     os_ = oracle.Settings(record_trace=True, **settings)
     if fit:
         os_.spectral_mode, os_.n_terms, os_.frequencies, os_.fit_weights = 1, fit[0], fit[1], fit[2]
-    o = oalg.execute(oracle.Cube(w, h, c, 1, weights), os_, o_res, o_model, psfs)
+    o = oalg.execute(oracle.Cube(*cube_args), os_, o_res, o_model, psfs)
 
     g_res, g_model = res.copy(), np.zeros_like(res)
     alg = rdl.GenericClean(use_sub_minor_optimization=sub_minor)
@@ -119,9 +122,11 @@ def _run_both(rdl, oracle, res, psfs, weights, settings, sub_minor=False, device
               trace_capacity=1 << 20)
     if "clean_mask" in settings:
         alg.set_clean_mask(settings["clean_mask"])
+    if settings.get("rms_factor") is not None:
+        alg.set_rms_factor_image(settings["rms_factor"])
     if fit:
-        alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, fit[0], fit[1], fit[2], 1)
-    cube = rdl.Cube(w, h, c, 1, weights)
+        alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, fit[0], fit[1], fit[2], n_pol)
+    cube = rdl.Cube(*cube_args)
     if device_resident:
         import torch
         d_res, d_model = torch.from_numpy(g_res).cuda(), torch.from_numpy(g_model).cuda()

@@ -17,10 +17,14 @@ NEAR_TIE_IMAGE_TOL = 2e-3  # image tolerance once a tie was broken differently
 
 
 def run_both(rdl, oracle, res, psfs, weights, settings, beam=6.0, ms_kwargs=None, fit=None,
-             automask=None, device_resident=True, algs=None):
+             automask=None, device_resident=True, algs=None, n_pol=1, pol_norm=1.0,
+             squared_joins=False):
     import torch
     ms_kwargs = ms_kwargs or {}
     c, h, w = res.shape
+    n_img = c
+    c //= n_pol
+    cube_args = (w, h, c, n_pol, weights, None, pol_norm, squared_joins)
     if algs is None:
         oalg = oracle.MultiScale(beam_size=beam, pixel_scale=1.0, **ms_kwargs)
         galg = rdl.MultiScaleAlgorithm(beam, 1.0, **ms_kwargs)
@@ -33,7 +37,7 @@ def run_both(rdl, oracle, res, psfs, weights, settings, beam=6.0, ms_kwargs=None
         oalg.set_automask_mode(*automask)
         galg.set_auto_mask_mode(*automask)
     o_res, o_model = res.copy(), np.zeros_like(res)
-    o = oalg.execute(oracle.Cube(w, h, c, 1, weights), os_, o_res, o_model, psfs)
+    o = oalg.execute(oracle.Cube(*cube_args), os_, o_res, o_model, psfs)
 
     galg.apply(threshold=settings.get("threshold", 0.0),
                minor_loop_gain=settings.get("minor_loop_gain", 0.1),
@@ -47,11 +51,13 @@ def run_both(rdl, oracle, res, psfs, weights, settings, beam=6.0, ms_kwargs=None
                trace_capacity=1 << 20)
     if "clean_mask" in settings:
         galg.set_clean_mask(settings["clean_mask"])
+    if settings.get("rms_factor") is not None:
+        galg.set_rms_factor_image(settings["rms_factor"])
     if fit:
-        galg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, fit[0], fit[1], fit[2], 1)
-    cube = rdl.Cube(w, h, c, 1, weights)
+        galg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, fit[0], fit[1], fit[2], n_pol)
+    cube = rdl.Cube(*cube_args)
     if device_resident:
-        d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, h, w), device="cuda")
+        d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((n_img, h, w), device="cuda")
         g = galg.execute_major_iteration(cube, d_res, d_model, torch.from_numpy(psfs).cuda())
         g_res, g_model = d_res.cpu().numpy(), d_model.cpu().numpy()
     else:

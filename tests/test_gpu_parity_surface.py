@@ -1,0 +1,186 @@
+"""GPU parity on the parts of the surface that round 1 left untested:
+
+* an RMS-factor image (generic_clean.cc:255-277, subminor_loop.cc:16-18,147-149,
+  threaded_deconvolution_tools.cc:52-107, multiscale_algorithm.cc:700-748) in GenericClean
+  path A / path B and in both multiscale minor-loop flavours;
+* cubes with n_pol > 1 inside a LOOP: SURVEY quirk 2 (first peak linear, later peaks
+  square-integrated, generic_clean.cc:71 vs :198), squared joins and the [channel][pol]
+  reshuffle of the spectral fit (deconvolution_algorithm.cc:29-46);
+* GenericClean path A at frame sizes whose padding even(ceil(1.1f*N)) contains a large prime
+  (generic_clean.cc:63-66; 1364 -> 1502 = 2 * 751, 4096 -> 4506 = 2 * 3 * 751).
+
+Checkers: the restated oracle for the peak trace (bit-exact positions and values) and the
+reference's OWN sources (oracle/_ref, `oracle.Reference`) for iteration counts and images."""
+import numpy as np
+import pytest
+
+from helpers import hogbom_case, multiscale_case
+from test_gpu_hogbom import _run_both, _assert_same
+from test_gpu_multiscale import check as ms_check
+from test_gpu_multiscale import run_both as ms_run_both
+from test_gpu_subminor import _check as path_a_check
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-5
+
+POLS = [(("XX", "YY"), 0.5), (("I", "Q", "U", "V"), 1.0), (("Q", "U"), 0.5)]
+
+
+def pol_case(n, c, pols, seed=1, multiscale=False):
+    """[channel][pol] cube: every polarisation is a scaled copy of the Stokes-I-like image plus
+    its own noise, so linear and square integration pick different peaks."""
+    res, psfs, weights, freqs = (multiscale_case if multiscale else hogbom_case)(n, c, seed=seed)
+    rng = np.random.default_rng(seed + 7)
+    n_pol = len(pols)
+    out = np.zeros((c * n_pol, n, n), np.float32)
+    for ch in range(c):
+        for p in range(n_pol):
+            f = [1.0, 0.3, -0.2, 0.6][p] if pols[0] == "I" else [1.0, 0.8, 0.1, -0.1][p]
+            out[ch * n_pol + p] = res[ch] * np.float32(f) + \
+                rng.normal(0, 1e-3, (n, n)).astype(np.float32)
+    return out, psfs, weights, freqs
+
+
+def rms_image(n, seed=11, h=None):
+    """Smooth positive factor map (what math/rms_image.cc produces: 1 / local rms, normalised)."""
+    h = n if h is None else h
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:n].astype(np.float32)
+    a = 1.0 + 0.4 * np.sin(x / n * 5.0 + rng.uniform(0, 3)) * np.cos(y / h * 3.0 + rng.uniform(0, 3))
+    return (a + rng.uniform(0.0, 0.05, (h, n))).astype(np.float32)
+
+
+def reference_run(oracle, algorithm, res, psfs, weights, freqs, pols=("I",), rms=None, mask=None,
+                  fit=0, squared_joins=False, **kw):
+    if oracle.ref_lib() is None:
+        return None
+    n_img, h, w = res.shape
+    r = oracle.Reference(algorithm, w, h, n_img // len(pols), pols=pols, weights=weights,
+                         frequencies=freqs, fit_terms=fit, squared_joins=squared_joins, **kw)
+    if rms is not None:
+        r.set_rms_factor_image(rms)
+    if mask is not None:
+        r.set_clean_mask(mask)
+    a, m = res.copy(), np.zeros_like(res)
+    out = r.execute(a, m, psfs)
+    return out, a, m
+
+
+def rel(a, b):
+    return float(np.abs(a.astype(np.float64) - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+# ---- RMS factor image ------------------------------------------------------------------------
+@pytest.mark.parametrize("sub_minor", [False, True])
+@pytest.mark.parametrize("n,c", [(256, 1), (200, 3)])
+def test_generic_clean_with_rms_factor(rdl, oracle, torch_cuda, sub_minor, n, c):
+    res, psfs, weights, freqs = hogbom_case(n, c)
+    rms = rms_image(n)
+    rng = np.random.default_rng(4)
+    mask = (rng.uniform(size=(n, n)) < 0.8).astype(np.uint8)
+    for extra in [dict(), dict(clean_mask=mask, clean_border_ratio=0.04),
+                  dict(allow_negative=False)]:
+        st = dict(max_iterations=400, clean_border_ratio=0.0, major_loop_gain=0.9, rms_factor=rms)
+        st.update(extra)
+        o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, weights, st, sub_minor=sub_minor,
+                                      device_resident=True)
+        assert o.iteration_number > 20
+        (path_a_check if sub_minor else _assert_same)(o, oi, g, gi, alg)
+        ref = reference_run(oracle, "generic", res, psfs, weights, freqs, rms=rms,
+                            mask=extra.get("clean_mask"), use_sub_minor_optimization=sub_minor,
+                            max_iterations=400, major_loop_gain=0.9,
+                            clean_border_ratio=st["clean_border_ratio"],
+                            allow_negative=st.get("allow_negative", True))
+        if ref:
+            out, a, m = ref
+            assert out.iteration_number == g.iteration_number
+            assert out.final_peak_value == g.final_peak_value
+            assert rel(gi[0], a) <= REL_TOL and rel(gi[1], m) <= REL_TOL
+            if not sub_minor:
+                assert np.array_equal(gi[0], a) and np.array_equal(gi[1], m)
+
+
+@pytest.mark.parametrize("fast", [True, False])
+def test_multiscale_with_rms_factor(rdl, oracle, torch_cuda, fast):
+    n, c = 192, 2
+    res, psfs, weights, freqs = multiscale_case(n, c)
+    rms = rms_image(n)
+    st = dict(max_iterations=600 if fast else 150, clean_border_ratio=0.0,
+              major_loop_gain=0.85 if fast else 0.97, rms_factor=rms)
+    msk = dict(max_scales=3, fast_sub_minor_loop=fast)
+    o, oi, g, gi, algs = ms_run_both(rdl, oracle, res, psfs, weights, st, ms_kwargs=msk)
+    assert o.iteration_number > 20
+    ms_check(o, oi, g, gi, algs)
+    ref = reference_run(oracle, "multiscale", res, psfs, weights, freqs, rms=rms, beam_size=6.0,
+                        max_iterations=st["max_iterations"], major_loop_gain=st["major_loop_gain"],
+                        **msk)
+    if ref:
+        out, a, m = ref
+        assert out.iteration_number == g.iteration_number
+        assert out.final_peak_value == pytest.approx(g.final_peak_value, rel=2e-4)
+
+
+# ---- several polarisations in a loop -------------------------------------------------------------
+@pytest.mark.parametrize("sub_minor", [False, True])
+@pytest.mark.parametrize("pols,pol_norm", POLS)
+def test_generic_clean_multi_polarisation_loop(rdl, oracle, torch_cuda, sub_minor, pols, pol_norm):
+    n, c = 160, 3
+    res, psfs, weights, freqs = pol_case(n, c, pols)
+    n_pol = len(pols)
+    for squared in (False, True):
+        for fit in (None, (2, freqs, weights)):
+            st = dict(max_iterations=300, clean_border_ratio=0.0, major_loop_gain=0.97)
+            o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, weights, st, sub_minor=sub_minor,
+                                          device_resident=True, fit=fit, n_pol=n_pol,
+                                          pol_norm=pol_norm, squared_joins=squared)
+            assert o.iteration_number > 30
+            (path_a_check if sub_minor else _assert_same)(o, oi, g, gi, alg)
+            ref = reference_run(oracle, "generic", res, psfs, weights, freqs, pols=pols,
+                                fit=2 if fit else 0, squared_joins=squared,
+                                use_sub_minor_optimization=sub_minor, max_iterations=300,
+                                major_loop_gain=0.97)
+            if ref:
+                out, a, m = ref
+                assert out.iteration_number == g.iteration_number
+                assert out.final_peak_value == g.final_peak_value
+                assert rel(gi[0], a) <= REL_TOL and rel(gi[1], m) <= REL_TOL
+
+
+@pytest.mark.parametrize("pols,pol_norm", POLS[:2])
+@pytest.mark.parametrize("fast", [True, False])
+def test_multiscale_multi_polarisation_loop(rdl, oracle, torch_cuda, pols, pol_norm, fast):
+    n, c = 160, 2
+    res, psfs, weights, freqs = pol_case(n, c, pols, multiscale=True)
+    for squared, fit in [(False, None), (True, (2, freqs, weights))]:
+        st = dict(max_iterations=400 if fast else 120, clean_border_ratio=0.0,
+                  major_loop_gain=0.85 if fast else 0.97)
+        msk = dict(max_scales=3, fast_sub_minor_loop=fast)
+        o, oi, g, gi, algs = ms_run_both(rdl, oracle, res, psfs, weights, st, ms_kwargs=msk,
+                                         fit=fit, n_pol=len(pols), pol_norm=pol_norm,
+                                         squared_joins=squared)
+        assert o.iteration_number > 20
+        ms_check(o, oi, g, gi, algs)
+
+
+# ---- path A where the padded frame has a large prime factor --------------------------------------
+@pytest.mark.parametrize("n,c,iters", [(238, 2, 300), (1364, 1, 3000), (4096, 1, 20000)])
+def test_path_a_large_prime_padding(rdl, oracle, torch_cuda, n, c, iters):
+    res, psfs, weights, freqs = hogbom_case(n, c)
+    st = dict(threshold=0.0, max_iterations=iters, clean_border_ratio=0.0, major_loop_gain=0.9)
+    o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, weights, st, sub_minor=True,
+                                  device_resident=True)
+    assert o.iteration_number > 10
+    path_a_check(o, oi, g, gi, alg)
+
+
+def test_path_a_odd_frame(rdl, oracle, torch_cuda):
+    # odd width and height: the padded frame is made even, the image itself is not
+    h, w = 131, 151
+    res, psfs, _, _ = hogbom_case(160, 1)
+    res = np.ascontiguousarray(res[:, :h, :w])
+    from helpers import gaussian_psf
+    psfs = gaussian_psf(w, h=h)[None]
+    st = dict(threshold=0.0, max_iterations=300, clean_border_ratio=0.0, major_loop_gain=0.9)
+    o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, None, st, sub_minor=True)
+    assert o.iteration_number > 10
+    path_a_check(o, oi, g, gi, alg)
