@@ -33,6 +33,7 @@
 // smooth and the native engine is used. The result is the reference's circular convolution at P
 // (including its wrap-around), evaluated at FFT round-off like every other convolution here.
 #include "fft.cuh"
+#include "fft_fast_plan.h"
 
 #include <algorithm>
 #include <cmath>
@@ -759,6 +760,50 @@ __global__ void PreparePsfKernelKernel(float* dst, int w, int h, const float* ps
   }
 }
 
+// ---- register-radix engine (fft_fast.cuh): 2-3-5-7-smooth frames ---------------------------------
+__global__ void __launch_bounds__(128, 4)
+    FastRowForwardKernel(const __grid_constant__ fast::RowPlan p, const __grid_constant__ fast::RowIo io) {
+  extern __shared__ __align__(16) float2 smem[];
+  fast::RowForwardPhase<0>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+  __syncthreads();
+  fast::RowForwardPhase<1>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+  __syncthreads();
+  fast::RowForwardPhase<2>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+__global__ void __launch_bounds__(128, 4)
+    FastRowInverseKernel(const __grid_constant__ fast::RowPlan p, const __grid_constant__ fast::RowIo io) {
+  extern __shared__ __align__(16) float2 smem[];
+  fast::RowInversePhase<0>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+  __syncthreads();
+  fast::RowInversePhase<1>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+  __syncthreads();
+  fast::RowInversePhase<2>(p, io, smem, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+// grid: (column tiles of a band, row groups); tile0 = first tile of the band
+template <bool INV>
+__global__ void __launch_bounds__(fast::kTile * fast::kStridedRows)
+    FastColumnStridedKernel(const __grid_constant__ fast::ColPlan p, const __grid_constant__ fast::ColIo io,
+                            int tile0) {
+  fast::ColumnStridedThread<INV>(p, io, tile0 + blockIdx.x, blockIdx.y, threadIdx.x);
+}
+
+// grid: (column tiles of a band, H2 row blocks)
+template <bool CONVOLVE>
+__global__ void __launch_bounds__(256, 2)
+    FastColumnBlockKernel(const __grid_constant__ fast::ColPlan p, const __grid_constant__ fast::ColIo io,
+                          int tile0) {
+  extern __shared__ __align__(16) float2 smem[];
+  const int tile = tile0 + blockIdx.x;
+  fast::ColumnBlockPhase<0, CONVOLVE>(p, io, smem, tile, blockIdx.y, threadIdx.x, blockDim.x);
+  __syncthreads();
+  fast::ColumnBlockPhase<1, CONVOLVE>(p, io, smem, tile, blockIdx.y, threadIdx.x, blockDim.x);
+  if (!CONVOLVE) return;
+  __syncthreads();
+  fast::ColumnBlockPhase<2, CONVOLVE>(p, io, smem, tile, blockIdx.y, threadIdx.x, blockDim.x);
+}
+
 struct HostPlan {
   Plan plan{};
   DeviceBuffer<float2> tw;
@@ -839,6 +884,26 @@ struct FftConvolver::Impl {
   int rows_per_cta = 1, row_threads = 256, row_stride = 0;
   int threads1 = 256, threads2 = 256;
   size_t row_smem = 0, smem1 = 0, smem2 = 0;
+  // register-radix engine (2-3-5-7-smooth frames)
+  bool use_fast = false;
+  fast::HostFastPlan fp;
+  fast::RowPlan frp{};
+  fast::ColPlan fcp{};
+  DeviceBuffer<float2> f_tw_row, f_split, f_tw_h1, f_tw_h;
+  DeviceBuffer<uint4> f_pairs;
+  int band_tiles = 0;  // column tiles per band of the column passes (L2-resident bands)
+
+  fast::ColIo MakeFastColIo() const {
+    fast::ColIo c{};
+    c.spec = work.get();
+    c.pitch = pitch;
+    c.y0 = 0;
+    c.y1 = H;
+    c.out_y0 = 0;
+    c.out_y1 = H;
+    c.scale = 1.0f;
+    return c;
+  }
 
   ColParams MakeColParams() const {
     ColParams c{};
@@ -930,6 +995,40 @@ FftConvolver::FftConvolver(size_t width, size_t height, size_t content_width, si
     d.n = d.W / 2;
     // whole 128-byte lines per spectrum row: the column passes work on 16-column tiles
     d.pitch = (d.n + 1 + kTileCols - 1) / kTileCols * kTileCols;
+    const char* engine = std::getenv("RDL_FFT_ENGINE");
+    if (!engine || std::string(engine) != "classic") d.fp.Build(d.W, d.H);
+    if (d.fp.ok) {
+      auto upload = [](auto& buf, const auto& host) {
+        buf.Resize(host.size());
+        RDL_CUDA(cudaMemcpy(buf.get(), host.data(), host.size() * sizeof(host[0]), cudaMemcpyHostToDevice));
+      };
+      upload(d.f_tw_row, d.fp.tw_row);
+      upload(d.f_split, d.fp.tw_split);
+      upload(d.f_tw_h1, d.fp.tw_h1);
+      upload(d.f_tw_h, d.fp.tw_h);
+      upload(d.f_pairs, d.fp.pairs);
+      d.frp = d.fp.MakeRowPlan(d.f_tw_row.get(), d.f_split.get(), d.f_pairs.get());
+      d.fcp = d.fp.MakeColPlan(d.f_tw_h1.get(), d.f_tw_h.get());
+      const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+      const int smem_max = int(kMaxSmemBytes);
+      RDL_CUDA(cudaFuncSetAttribute(FastRowForwardKernel, attr, smem_max));
+      RDL_CUDA(cudaFuncSetAttribute(FastRowInverseKernel, attr, smem_max));
+      RDL_CUDA(cudaFuncSetAttribute(FastColumnBlockKernel<true>, attr, smem_max));
+      RDL_CUDA(cudaFuncSetAttribute(FastColumnBlockKernel<false>, attr, smem_max));
+      // Column passes run band by band so that the three passes of a band find it in L2
+      // (126 MB): about 40 MB of spectrum per band. RDL_FFT_BAND_MB=0 switches banding off.
+      double band_mb = 40.0;
+      if (const char* e = std::getenv("RDL_FFT_BAND_MB")) band_mb = std::atof(e);
+      const int tiles = d.pitch / kTileCols;
+      const double tile_mb = double(d.H) * kTileCols * sizeof(float2) / 1.0e6;
+      d.band_tiles = tiles;
+      if (band_mb > 0.0 && d.fcp.H2 > 1 && tile_mb * tiles > 1.5 * band_mb)
+        d.band_tiles = std::max(1, int(band_mb / tile_mb));
+      d.use_fast = true;
+      d.work.Resize(size_t(d.H) * d.pitch);
+      RDL_CUDA(cudaMemset(d.work.get(), 0, size_t(d.H) * d.pitch * sizeof(float2)));
+      return;
+    }
     d.row.Build(d.n);
     d.col.Build(d.H);  // validates the factors and holds the exp(-2 pi i t / H) table
     std::vector<uint32_t> perm(d.n);
@@ -1040,6 +1139,20 @@ void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, size_t ox
   Impl& d = *impl_;
   if (ox + sw > size_t(d.W) || oy + sh > size_t(d.H))
     throw std::invalid_argument("source larger than the FFT frame");
+  if (d.use_fast) {
+    fast::RowIo io{};
+    io.src = src;
+    io.sw = int(sw);
+    io.sh = int(sh);
+    io.ox = int(ox);
+    io.oy = int(oy);
+    io.spec = d.work.get();
+    io.pitch = d.pitch;
+    const int grid = (int(sh) + d.fp.rows_per_cta - 1) / d.fp.rows_per_cta;
+    FastRowForwardKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, io);
+    ++launches_;
+    return;
+  }
   RowParams p{};
   p.src = src;
   p.sw = int(sw);
@@ -1076,6 +1189,25 @@ void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectru
     return;
   }
   ForwardRows(kernel_image, d.W, d.H, 0, 0, stream);
+  if (d.use_fast) {
+    fast::ColIo io = d.MakeFastColIo();
+    io.kspec_out = spectrum_out;
+    io.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
+    const int tiles = d.pitch / kTileCols;
+    const int groups = (d.fcp.H1 + fast::kStridedRows - 1) / fast::kStridedRows;
+    for (int t0 = 0; t0 < tiles; t0 += d.band_tiles) {
+      const int nt = std::min(d.band_tiles, tiles - t0);
+      if (d.fcp.H2 > 1) {
+        FastColumnStridedKernel<false><<<dim3(nt, groups), fast::kTile * fast::kStridedRows, 0, stream>>>(
+            d.fcp, io, t0);
+        ++launches_;
+      }
+      FastColumnBlockKernel<false><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
+          d.fcp, io, t0);
+      ++launches_;
+    }
+    return;
+  }
   ColParams c = d.MakeColParams();
   c.kspec_out = spectrum_out;
   c.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
@@ -1147,6 +1279,44 @@ void FftConvolver::ConvolveAt(const float* src, size_t sw, size_t sh, size_t sox
   if (dox + dw > size_t(d.W) || doy + dh > size_t(d.H))
     throw std::invalid_argument("destination larger than the FFT frame");
   ForwardRows(src, sw, sh, sox, soy, stream);
+  if (d.use_fast) {
+    fast::ColIo io = d.MakeFastColIo();
+    io.kspec = kernel_spectrum;
+    io.y0 = int(soy);
+    io.y1 = io.y0 + int(sh);
+    io.out_y0 = int(doy);
+    io.out_y1 = io.out_y0 + int(dh);
+    const int tiles = d.pitch / kTileCols;
+    const int groups = (d.fcp.H1 + fast::kStridedRows - 1) / fast::kStridedRows;
+    const int strided_threads = fast::kTile * fast::kStridedRows;
+    for (int t0 = 0; t0 < tiles; t0 += d.band_tiles) {
+      const int nt = std::min(d.band_tiles, tiles - t0);
+      if (d.fcp.H2 > 1) {
+        FastColumnStridedKernel<false><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
+        ++launches_;
+      }
+      FastColumnBlockKernel<true><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
+          d.fcp, io, t0);
+      ++launches_;
+      if (d.fcp.H2 > 1) {
+        FastColumnStridedKernel<true><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
+        ++launches_;
+      }
+    }
+    fast::RowIo rio{};
+    rio.dst = dst;
+    rio.sw = int(dw);
+    rio.sh = int(dh);
+    rio.ox = int(dox);
+    rio.oy = int(doy);
+    rio.spec = d.work.get();
+    rio.pitch = d.pitch;
+    rio.mode = mode;
+    const int grid = (int(dh) + d.fp.rows_per_cta - 1) / d.fp.rows_per_cta;
+    FastRowInverseKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, rio);
+    ++launches_;
+    return;
+  }
   ColParams c = d.MakeColParams();
   c.kspec = kernel_spectrum;
   c.y0 = int(soy);
