@@ -321,6 +321,14 @@ rdl_status rdl_iuwt_smooth(rdl_handle* h, const float* device_in, float* device_
 rdl_status rdl_iuwt_decompose(rdl_handle* h, const float* device_input, uint64_t width,
                               uint64_t height, int32_t n_scales, int32_t include_largest,
                               float* device_coefficients, void* stream);
+/* IuwtDecomposition::Decompose(x, x, false): the input aliased to the scratch image, which is
+ * how IuwtDeconvolutionAlgorithm calls it (iuwt_deconvolution_algorithm.cc:344,385,685,780) and
+ * which changes scale 0 (iuwt_decomposition.cc:19-26,58-61: a recursive row pass, and the
+ * difference taken against the scratch content). n_scales planes; device_x is clobbered. */
+rdl_status rdl_iuwt_decompose_aliased(rdl_handle* h, float* device_x, uint64_t width,
+                                      uint64_t height, int32_t n_scales,
+                                      float* device_coefficients, void* stream);
+
 /* IuwtDecomposition::ApplyMask (iuwt_decomposition.h:162-169; device_masks = n_scales planes of
  * width*height bytes, NULL = no mask) followed by Recompose (iuwt_decomposition.h:121-147). */
 rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, uint64_t width,

@@ -546,6 +546,17 @@ def ref_iuwt_decompose(image, n_scales, include_largest=True):
     return out
 
 
+def ref_iuwt_decompose_aliased(image, n_scales):
+    """IuwtDecomposition::Decompose(x, x, false) of the reference's own source: input aliased to
+    the scratch image, as IuwtDeconvolutionAlgorithm calls it."""
+    a = _f32(image).copy()
+    out = np.zeros((n_scales,) + a.shape, np.float32)
+    f = ref_lib().ref_iuwt_decompose_aliased
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_void_p]
+    f(_ptr(a), a.shape[1], a.shape[0], n_scales, _ptr(out))
+    return out
+
+
 def ref_iuwt_recompose(coefficients, n_scales, include_largest=True, masks=None):
     c = _f32(coefficients)
     if c.shape[0] == n_scales:  # the wrapper reads n_scales + 1 planes

@@ -152,6 +152,15 @@ void ref_iuwt_decompose(const float* input, uint64_t w, uint64_t h, int n_scales
   for (int s = 0; s != n_scales + (include_largest ? 1 : 0); ++s)
     std::copy_n(d[s].Coefficients().Data(), w * h, coefficients + size_t(s) * w * h);
 }
+// Decompose(x, x, false): the call IuwtDeconvolutionAlgorithm makes with the input aliased to the
+// scratch image (iuwt_deconvolution_algorithm.cc:344,385,685,780). n_scales planes.
+void ref_iuwt_decompose_aliased(float* x, uint64_t w, uint64_t h, int n_scales,
+                                float* coefficients) {
+  algorithms::iuwt::IuwtDecomposition d(n_scales, w, h);
+  d.Decompose(x, x, false);
+  for (int s = 0; s != n_scales; ++s)
+    std::copy_n(d[s].Coefficients().Data(), w * h, coefficients + size_t(s) * w * h);
+}
 // masks (optional): n_scales planes of w*h bytes, applied with ApplyMask before Recompose.
 void ref_iuwt_recompose(const float* coefficients, uint64_t w, uint64_t h, int n_scales,
                         int include_largest, const uint8_t* masks, float* out) {

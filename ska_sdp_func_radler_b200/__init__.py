@@ -92,7 +92,7 @@ EXPORTED_SYMBOLS = [
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
-    "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_recompose",
+    "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
@@ -558,6 +558,14 @@ class DeconvolutionAlgorithm:
         assert coefficients.shape[0] >= n_scales + (1 if include_largest else 0)
         self._check(lib().rdl_iuwt_decompose(self._h, image.data_ptr(), w, h, n_scales,
                                              int(include_largest), coefficients.data_ptr(), stream))
+
+    def iuwt_decompose_aliased(self, x, coefficients, n_scales, stream=None):
+        """IuwtDecomposition::Decompose(x, x, false) (input aliased to the scratch image)."""
+        h, w = x.shape
+        f = lib().rdl_iuwt_decompose_aliased
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int32, C.c_void_p,
+                      C.c_void_p]
+        self._check(f(self._h, x.data_ptr(), w, h, n_scales, coefficients.data_ptr(), stream))
 
     def iuwt_recompose(self, coefficients, out, n_scales, include_largest=True, masks=None,
                        stream=None):

@@ -769,6 +769,17 @@ rdl_status rdl_iuwt_decompose(rdl_handle* h, const float* device_input, uint64_t
   });
 }
 
+rdl_status rdl_iuwt_decompose_aliased(rdl_handle* h, float* device_x, uint64_t width,
+                                      uint64_t height, int32_t n_scales,
+                                      float* device_coefficients, void* stream_v) {
+  if (!h || !device_x || !device_coefficients) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    IuwtDecomposeAliased(*h, device_x, width, height, n_scales, device_coefficients,
+                         StreamOf(h, stream_v));
+  });
+}
+
 rdl_status rdl_iuwt_recompose(rdl_handle* h, const float* device_coefficients, uint64_t width,
                               uint64_t height, int32_t n_scales, int32_t include_largest,
                               const uint8_t* device_masks, float* device_out, void* stream_v) {

@@ -783,7 +783,7 @@ __global__ void __launch_bounds__(128, 4)
 
 // grid: (column tiles of a band, row groups); tile0 = first tile of the band
 template <bool INV>
-__global__ void __launch_bounds__(fast::kTile * fast::kStridedRows)
+__global__ void __launch_bounds__(fast::kTile * fast::kStridedRows, 4)
     FastColumnStridedKernel(const __grid_constant__ fast::ColPlan p, const __grid_constant__ fast::ColIo io,
                             int tile0) {
   fast::ColumnStridedThread<INV>(p, io, tile0 + blockIdx.x, blockIdx.y, threadIdx.x);
@@ -889,7 +889,7 @@ struct FftConvolver::Impl {
   fast::HostFastPlan fp;
   fast::RowPlan frp{};
   fast::ColPlan fcp{};
-  DeviceBuffer<float2> f_tw_row, f_split, f_tw_h1, f_tw_h;
+  DeviceBuffer<float2> f_tw_row, f_tw_row2, f_split, f_tw_h1, f_tw_h;
   DeviceBuffer<uint4> f_pairs;
   int band_tiles = 0;  // column tiles per band of the column passes (L2-resident bands)
 
@@ -1002,12 +1002,13 @@ FftConvolver::FftConvolver(size_t width, size_t height, size_t content_width, si
         buf.Resize(host.size());
         RDL_CUDA(cudaMemcpy(buf.get(), host.data(), host.size() * sizeof(host[0]), cudaMemcpyHostToDevice));
       };
-      upload(d.f_tw_row, d.fp.tw_row);
+      upload(d.f_tw_row, d.fp.tw_row1);
+      upload(d.f_tw_row2, d.fp.tw_row2);
       upload(d.f_split, d.fp.tw_split);
       upload(d.f_tw_h1, d.fp.tw_h1);
       upload(d.f_tw_h, d.fp.tw_h);
       upload(d.f_pairs, d.fp.pairs);
-      d.frp = d.fp.MakeRowPlan(d.f_tw_row.get(), d.f_split.get(), d.f_pairs.get());
+      d.frp = d.fp.MakeRowPlan(d.f_tw_row.get(), d.f_tw_row2.get(), d.f_split.get(), d.f_pairs.get());
       d.fcp = d.fp.MakeColPlan(d.f_tw_h1.get(), d.f_tw_h.get());
       const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
       const int smem_max = int(kMaxSmemBytes);

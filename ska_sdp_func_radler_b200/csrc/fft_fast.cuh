@@ -256,7 +256,10 @@ struct RowPlan {
   int pitch_l2;  // l2 + pad
   int n_pairs;
   int rows_per_cta, row_stride;  // shared-memory elements per row
-  const float2* tw;        // exp(-2 pi i t / n), t in [0, n)
+  // twiddles by (output index q, butterfly j) so that neighbouring threads (j) read neighbouring
+  // entries: tw1[(q - 1) * l2 + j] = exp(-2 pi i j q / n), tw2[(q - 1) * rc + j] = exp(-2 pi i j q / l2)
+  const float2* tw1;
+  const float2* tw2;
   const float2* split_tw;  // exp(-2 pi i k / (2 n)), k in [0, n]
   const uint4* pairs;      // last pass: (offset A, offset B, k_low A, k_low B); entry 0 = block 0
 };
@@ -315,7 +318,7 @@ RDL_HD void RowForwardPass1(const RowPlan& p, const RowIo& io, float2* smem, int
     s[0] = v[0];
     StaticFor<RA - 1>([&](auto qq) {
       constexpr int q = decltype(qq)::value + 1;
-      s[q * p.pitch_l2] = CMulF(v[q], RDL_LDG(p.tw + j * q));
+      s[q * p.pitch_l2] = CMulF(v[q], RDL_LDG(p.tw1 + (q - 1) * p.l2 + j));
     });
   }
 }
@@ -333,7 +336,7 @@ RDL_HD void RowForwardPass2(const RowPlan& p, float2* smem, int n_rows, int tid,
     s[0] = v[0];
     StaticFor<RB - 1>([&](auto qq) {
       constexpr int q = decltype(qq)::value + 1;
-      s[q * p.rc] = CMulF(v[q], RDL_LDG(p.tw + j * q * p.ra));
+      s[q * p.rc] = CMulF(v[q], RDL_LDG(p.tw2 + (q - 1) * p.rc + j));
     });
   }
 }
@@ -433,7 +436,7 @@ RDL_HD void RowInversePass2(const RowPlan& p, float2* smem, int n_rows, int tid,
     v[0] = s[0];
     StaticFor<RB - 1>([&](auto qq) {
       constexpr int q = decltype(qq)::value + 1;
-      v[q] = CMulConj(s[q * p.rc], RDL_LDG(p.tw + j * q * p.ra));
+      v[q] = CMulConj(s[q * p.rc], RDL_LDG(p.tw2 + (q - 1) * p.rc + j));
     });
     Dft<RB, true>::Run(v);
     StaticFor<RB>([&](auto q) { s[q * p.rc] = v[q]; });
@@ -452,7 +455,7 @@ RDL_HD void RowInversePass3(const RowPlan& p, const RowIo& io, const float2* sme
     v[0] = s[0];
     StaticFor<RA - 1>([&](auto qq) {
       constexpr int q = decltype(qq)::value + 1;
-      v[q] = CMulConj(s[q * p.pitch_l2], RDL_LDG(p.tw + j * q));
+      v[q] = CMulConj(s[q * p.pitch_l2], RDL_LDG(p.tw1 + (q - 1) * p.l2 + j));
     });
     Dft<RA, true>::Run(v);
     float* row = io.dst + size_t(row0 + r) * io.sw;
@@ -639,7 +642,7 @@ RDL_HD void RowInversePhase(const RowPlan& p, const RowIo& io, float2* smem, int
   }
 }
 
-constexpr int kStridedRows = 16;  // r values per CTA of the strided pass (x kTile columns)
+constexpr int kStridedRows = 8;  // r values per CTA of the strided pass (x kTile columns)
 
 template <bool INV>
 RDL_HD void ColumnStridedThread(const ColPlan& p, const ColIo& io, int tile, int row_group, int tid) {

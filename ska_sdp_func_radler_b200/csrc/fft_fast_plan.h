@@ -64,7 +64,7 @@ inline ColChoice ChooseColRadices(int H) {
   for (int h2 : kRadices) {
     if (H % h2 != 0) continue;
     const int h1 = H / h2;
-    if (size_t(h1) * kTile * sizeof(float2) > size_t(96) * 1024) continue;
+    if (size_t(h1) * kTile * sizeof(float2) > size_t(160) * 1024) continue;
     for (int rb : kRadices) {
       if (h1 % rb != 0) continue;
       const int ra = h1 / rb;
@@ -120,7 +120,7 @@ struct HostFastPlan {
   size_t row_smem = 0;
   int block_threads = 128;
   size_t block_smem = 0;
-  std::vector<float2> tw_row, tw_split, tw_h1, tw_h;
+  std::vector<float2> tw_row1, tw_row2, tw_split, tw_h1, tw_h;
   std::vector<uint4> pairs;
 
   void Build(int width, int height) {
@@ -146,7 +146,19 @@ struct HostFastPlan {
     if (row_smem > size_t(200) * 1024) return;
     const int max_tasks = rows_per_cta * std::max(l2, std::max(row.ra * row.rc, int(pairs.size())));
     row_threads = std::clamp(RoundUp32(max_tasks), 64, 128);
-    tw_row = TwiddleTable(n, n, double(n));
+    // stage twiddles by (q, j): see RowPlan
+    auto stage_table = [](int radix, int m, int length) {
+      std::vector<float2> t(size_t(std::max(radix - 1, 0)) * m);
+      for (int q = 1; q < radix; ++q)
+        for (int j = 0; j < m; ++j) {
+          const double a = -2.0 * M_PI * double(j) * double(q) / double(length);
+          t[size_t(q - 1) * m + j] = make_float2(float(std::cos(a)), float(std::sin(a)));
+        }
+      if (t.empty()) t.push_back(make_float2(1.0f, 0.0f));
+      return t;
+    };
+    tw_row1 = stage_table(row.ra, l2, n);
+    tw_row2 = stage_table(row.rb, row.rc, l2);
     tw_split = TwiddleTable(n, n + 1, double(W));
     const int h1 = H / col.h2;
     tw_h1 = TwiddleTable(h1, h1, double(h1));
@@ -156,7 +168,8 @@ struct HostFastPlan {
     ok = true;
   }
 
-  RowPlan MakeRowPlan(const float2* d_tw, const float2* d_split, const uint4* d_pairs) const {
+  RowPlan MakeRowPlan(const float2* d_tw1, const float2* d_tw2, const float2* d_split,
+                      const uint4* d_pairs) const {
     RowPlan p{};
     p.n = n;
     p.ra = row.ra;
@@ -167,7 +180,8 @@ struct HostFastPlan {
     p.n_pairs = int(pairs.size());
     p.rows_per_cta = rows_per_cta;
     p.row_stride = row_stride;
-    p.tw = d_tw;
+    p.tw1 = d_tw1;
+    p.tw2 = d_tw2;
     p.split_tw = d_split;
     p.pairs = d_pairs;
     return p;

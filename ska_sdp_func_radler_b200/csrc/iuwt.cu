@@ -173,6 +173,78 @@ __global__ void MaskCopyKernel(float* out, const float* in, const uint8_t* mask,
     out[i] = (mask == nullptr || mask[i]) ? in[i] : 0.0f;
 }
 
+// One pass of the separable smoothing on its own (convolveHorizontalFast / convolveVerticalPartialFast,
+// iuwt_decomposition.cc:78-237): only the aliased decomposition below needs the passes apart.
+template <bool VERTICAL>
+__global__ void IuwtSinglePassKernel(const float* __restrict__ in, float* __restrict__ out, int W, int H,
+                                     int d) {
+  const size_t n = size_t(W) * H;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const int y = int(i / W), x = int(i - size_t(y) * W);
+    float v[5];
+    unsigned present = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const long xx = VERTICAL ? x : long(x) + long(k - 2) * d;
+      const long yy = VERTICAL ? long(y) + long(k - 2) * d : y;
+      const bool ok = xx >= 0 && xx < W && yy >= 0 && yy < H;
+      v[k] = ok ? __ldg(in + size_t(yy) * W + xx) : 0.0f;
+      present |= ok ? (1u << k) : 0u;
+    }
+    out[i] = Taps<false, !VERTICAL>(v, present);
+  }
+}
+
+// convolveHorizontalFast at step 1 with output == input, which is what
+// `iuwt.Decompose(scratch.Data(), scratch.Data(), false)` does to its first smoothing
+// (iuwt_deconvolution_algorithm.cc:344,385,685,780 -> iuwt_decomposition.cc:19,58-61): pixel x is
+// written before pixel x + 1 is computed, so the two LEFT taps read values that were already
+// smoothed -- a recursive filter along the row. One lane per row, 32-column tiles through shared
+// memory so that global accesses stay coalesced.
+__global__ void __launch_bounds__(128) IuwtAliasedRowPassKernel(float* img, int W, int H) {
+  __shared__ float tile[4][32][35];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = (blockIdx.x * 4 + warp) * 32;
+  if (row0 >= H) return;
+  float (*t)[35] = tile[warp];
+  float n1 = 0.0f, n2 = 0.0f;  // the new values of pixels x - 1 and x - 2
+  const int row = row0 + lane;
+  for (int x0 = 0; x0 < W; x0 += 32) {
+    for (int r = 0; r < 32; ++r) {
+      const int y = row0 + r;
+      if (y < H) {
+        if (x0 + lane < W) t[r][lane] = img[size_t(y) * W + x0 + lane];
+        if (lane < 2 && x0 + 32 + lane < W) t[r][32 + lane] = img[size_t(y) * W + x0 + 32 + lane];
+      }
+    }
+    __syncwarp();
+    if (row < H) {
+      for (int c = 0; c < 32 && x0 + c < W; ++c) {
+        const int x = x0 + c;
+        float v[5];
+        unsigned present = 4u;
+        v[2] = t[lane][c];
+        v[1] = n1;
+        v[0] = n2;
+        v[3] = x + 1 < W ? t[lane][c + 1] : 0.0f;
+        v[4] = x + 2 < W ? t[lane][c + 2] : 0.0f;
+        present |= (x >= 1 ? 2u : 0u) | (x >= 2 ? 1u : 0u) | (x + 1 < W ? 8u : 0u) | (x + 2 < W ? 16u : 0u);
+        const float o = Taps<false, true>(v, present);
+        t[lane][c] = o;
+        n2 = n1;
+        n1 = o;
+      }
+    }
+    __syncwarp();
+    for (int r = 0; r < 32; ++r) {
+      const int y = row0 + r;
+      if (y < H && x0 + lane < W) img[size_t(y) * W + x0 + lane] = t[r][lane];
+    }
+    __syncwarp();
+  }
+}
+
 template <bool SIMPLE, int EPI>
 void LaunchSmooth(rdl_handle& h, const float* in, float* out, const float* other,
                   const uint8_t* mask, size_t width, size_t height, int scale, cudaStream_t stream) {
@@ -215,6 +287,14 @@ void IuwtSmooth(rdl_handle& h, const float* in, float* out, size_t width, size_t
     LaunchSmooth<false, 0>(h, in, out, nullptr, nullptr, width, height, scale, stream);
 }
 
+namespace {
+// scales first_scale .. n_scales - 1 of DecomposeMt, starting from the smooth image i0; `next`
+// tells which of the two ping-pong planes is free
+void DecomposeFrom(rdl_handle& h, const float* i0, int first_scale, int next, size_t width,
+                   size_t height, int n_scales, bool include_largest, float* coefficients,
+                   cudaStream_t stream);
+}  // namespace
+
 void IuwtDecompose(rdl_handle& h, const float* input, size_t width, size_t height, int n_scales,
                    bool include_largest, float* coefficients, cudaStream_t stream) {
   if (n_scales < 1) throw std::invalid_argument("IUWT needs at least one scale");
@@ -222,10 +302,43 @@ void IuwtDecompose(rdl_handle& h, const float* input, size_t width, size_t heigh
   const size_t a = width * height;
   h.iuwt_a.Reserve(a);
   h.iuwt_b.Reserve(a);
-  const float* i0 = input;
+  DecomposeFrom(h, input, 0, 0, width, height, n_scales, include_largest, coefficients, stream);
+}
+
+// IuwtDecomposition::Decompose(x, x, false): input and scratch are the SAME buffer. What the
+// reference's code then computes (and what is reproduced here) is, for scale 0,
+//   x  <- recursive row pass of x          (convolveHorizontalPartial(scratch = x, image = x))
+//   i1 <- column pass of x
+//   x  <- row pass of i1                   (scratch of the second convolveMT)
+//   w0 <- x - B(i1)                        (differenceMT reads `input`, which is x)
+// and the ordinary decomposition of i1 for the scales above. x is left holding scratch data.
+void IuwtDecomposeAliased(rdl_handle& h, float* x, size_t width, size_t height, int n_scales,
+                          float* coefficients, cudaStream_t stream) {
+  if (n_scales < 1) throw std::invalid_argument("IUWT needs at least one scale");
+  CheckScale(width, height, n_scales);
+  const size_t a = width * height;
+  h.iuwt_a.Reserve(a);
+  h.iuwt_b.Reserve(a);
+  float* i1 = h.iuwt_a.get();
+  const int W = int(width), H = int(height);
+  IuwtAliasedRowPassKernel<<<(H + 127) / 128, 128, 0, stream>>>(x, W, H);
+  const int grid = int(std::min<size_t>((a + 255) / 256, size_t(kSmCount) * 16));
+  IuwtSinglePassKernel<true><<<grid, 256, 0, stream>>>(x, i1, W, H, 1);
+  IuwtSinglePassKernel<false><<<grid, 256, 0, stream>>>(i1, x, W, H, 1);
+  RDL_CUDA(cudaGetLastError());
+  h.launches += 3;
+  LaunchSmooth<false, 1>(h, i1, coefficients, x, nullptr, width, height, 1, stream);
+  if (n_scales > 1)
+    DecomposeFrom(h, i1, 1, 1, width, height, n_scales, false, coefficients, stream);
+}
+
+namespace {
+void DecomposeFrom(rdl_handle& h, const float* i0, int first_scale, int next, size_t width,
+                   size_t height, int n_scales, bool include_largest, float* coefficients,
+                   cudaStream_t stream) {
+  const size_t a = width * height;
   float* bufs[2] = {h.iuwt_a.get(), h.iuwt_b.get()};
-  int next = 0;
-  for (int s = 0; s != n_scales; ++s) {
+  for (int s = first_scale; s != n_scales; ++s) {
     const bool last = s + 1 == n_scales;
     // i1 = B(i0): the smooth remainder goes straight to its plane on the last scale
     float* i1 = (last && include_largest) ? coefficients + size_t(n_scales) * a : bufs[next];
@@ -237,6 +350,7 @@ void IuwtDecompose(rdl_handle& h, const float* input, size_t width, size_t heigh
     next ^= 1;
   }
 }
+}  // namespace
 
 void IuwtRecompose(rdl_handle& h, const float* coefficients, size_t width, size_t height,
                    int n_scales, bool include_largest, const uint8_t* masks, float* out,
@@ -261,17 +375,6 @@ void IuwtRecompose(rdl_handle& h, const float* coefficients, size_t width, size_
                           masks ? masks + size_t(s) * a : nullptr, width, height, s + 1, stream);
     cur ^= 1;
   }
-}
-
-// IuwtDeconvolution::ExecuteMajorIteration (iuwt_deconvolution.h:21-40 ->
-// IuwtDeconvolutionAlgorithm::PerformMajorIteration, iuwt_deconvolution_algorithm.cc:733-918).
-// The decomposition kernels above are in place; the structure search (SelectStructures flood
-// fill, conjugate-gradient deconvolution of the masked structure) is not yet on the device.
-// There is no CPU fallback in this library, so the call fails loudly instead.
-rdl_result RunIuwt(rdl_handle&, DeviceCube&, cudaStream_t) {
-  throw std::domain_error(
-      "IuwtDeconvolution::ExecuteMajorIteration is not implemented on the device yet; the IUWT "
-      "decomposition kernels are available through rdl_iuwt_decompose / rdl_iuwt_recompose");
 }
 
 }  // namespace rdl

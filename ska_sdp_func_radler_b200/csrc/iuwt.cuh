@@ -17,6 +17,10 @@ void IuwtSmooth(rdl_handle& h, const float* in, float* out, size_t width, size_t
 // IuwtDecomposition::DecomposeMt: coefficients = n_scales (+1 when include_largest) planes.
 void IuwtDecompose(rdl_handle& h, const float* input, size_t width, size_t height, int n_scales,
                    bool include_largest, float* coefficients, cudaStream_t stream);
+// IuwtDecomposition::Decompose(x, x, false) -- input aliased to the scratch image -- exactly as
+// the reference's code behaves (see iuwt.cu). n_scales planes; x is clobbered.
+void IuwtDecomposeAliased(rdl_handle& h, float* x, size_t width, size_t height, int n_scales,
+                          float* coefficients, cudaStream_t stream);
 // ApplyMask (masks != nullptr: n_scales byte planes) + Recompose.
 void IuwtRecompose(rdl_handle& h, const float* coefficients, size_t width, size_t height,
                    int n_scales, bool include_largest, const uint8_t* masks, float* out,

@@ -24,7 +24,7 @@ struct Engine {
   bool Build(int W, int H) {
     hp.Build(W, H);
     if (!hp.ok) return false;
-    rp = hp.MakeRowPlan(hp.tw_row.data(), hp.tw_split.data(), hp.pairs.data());
+    rp = hp.MakeRowPlan(hp.tw_row1.data(), hp.tw_row2.data(), hp.tw_split.data(), hp.pairs.data());
     cp = hp.MakeColPlan(hp.tw_h1.data(), hp.tw_h.data());
     work.assign(size_t(H) * hp.pitch, make_float2(0.0f, 0.0f));
     return true;
