@@ -176,6 +176,12 @@ uint64_t rdl_last_selected_count(const rdl_handle* h);
 uint64_t rdl_minor_iteration_count(const rdl_handle* h);
 /* number of kernels this handle has launched so far (bench.py "gpu_launches") */
 uint64_t rdl_kernel_launch_count(const rdl_handle* h);
+/* How many schaapcommon::math::Convolve calls the reference makes for the work of the last
+ * rdl_execute_major_iteration, by frame size: up to `capacity` (width, height, count) triples;
+ * returns the number of distinct sizes. (The device path caches kernel spectra and twice-convolved
+ * PSFs and runs fewer transforms; this is the count a CPU baseline has to be priced with,
+ * multiscale_algorithm.cc:29-88,331-354,432-461,578-634, subminor_loop.cc:195-218.) */
+uint64_t rdl_reference_convolutions(const rdl_handle* h, uint64_t* triples, uint64_t capacity);
 
 /* ---- the hot path: DeconvolutionAlgorithm::ExecuteMajorIteration ------------
  * (deconvolution_algorithm.h:69-71). residual[i], model[i] (i < n_channels*n_pol)

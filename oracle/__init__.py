@@ -750,6 +750,18 @@ POL = {"I": 0, "Q": 1, "U": 2, "V": 3, "RR": 4, "RL": 5, "LR": 6, "LL": 7, "XX":
        "YX": 10, "YY": 11}
 
 
+def ref_convolve_stats(reset=True):
+    """(sizes -> count of schaapcommon::math::Convolve calls, seconds spent in them) since the last
+    reset, for the reference's sources in oracle/_ref."""
+    L = _refa()
+    L.refa_convolve_stats.restype = C.c_uint64
+    L.refa_convolve_stats.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_double), C.c_int32]
+    buf = np.zeros(3 * 64, np.uint64)
+    sec = C.c_double()
+    n = L.refa_convolve_stats(_ptr(buf), 64, C.byref(sec), int(reset))
+    return {(int(buf[3 * i]), int(buf[3 * i + 1])): int(buf[3 * i + 2]) for i in range(min(n, 64))}, sec.value
+
+
 class Reference:
     """The reference's own GenericClean / MultiScaleAlgorithm / IuwtDeconvolution behind its
     ParallelDeconvolution, driven like Radler::InitializeDeconvolutionAlgorithm + Perform do

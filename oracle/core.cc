@@ -8,6 +8,9 @@
 #include <cassert>
 #include <cstring>
 #include <limits>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 
 namespace oracle {
@@ -32,11 +35,89 @@ static size_t g_threads = 1;
 void SetThreadCount(size_t n) { g_threads = std::max<size_t>(1, n); }
 size_t ThreadCount() { return g_threads; }
 
+// A persistent pool for top-level loops (the reference keeps an aocommon::ThreadPool alive for
+// the whole run, radler.cc:138-142): spawning 16-32 std::threads per loop costs about half a
+// millisecond, which is most of a small-frame Hogbom iteration. Loops started from inside a pool
+// task (facets -> per-facet row loops) fall back to short-lived threads.
+namespace {
+class Pool {
+ public:
+  static Pool& Get() {
+    static Pool p;
+    return p;
+  }
+  // runs task(t) for t in [0, n_tasks) on up to n_workers threads and waits
+  void Run(size_t n_tasks, size_t n_workers, const std::function<void(size_t)>& task) {
+    std::unique_lock<std::mutex> run_lock(run_mutex_);  // one top-level loop at a time
+    Grow(n_workers);
+    {
+      std::lock_guard<std::mutex> lk(m_);
+      task_ = &task;
+      n_tasks_ = n_tasks;
+      next_ = 0;
+      pending_ = n_tasks;
+      ++generation_;
+    }
+    cv_.notify_all();
+    std::unique_lock<std::mutex> lk(m_);
+    done_.wait(lk, [&] { return pending_ == 0; });
+    task_ = nullptr;
+  }
+  static thread_local bool inside;
+
+ private:
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> lk(m_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto& t : threads_) t.join();
+  }
+  void Grow(size_t n) {
+    while (threads_.size() < n) threads_.emplace_back([this] { Work(); });
+  }
+  void Work() {
+    inside = true;
+    uint64_t seen = 0;
+    std::unique_lock<std::mutex> lk(m_);
+    for (;;) {
+      cv_.wait(lk, [&] { return stop_ || (generation_ != seen && next_ < n_tasks_); });
+      if (stop_) return;
+      while (next_ < n_tasks_) {
+        const size_t t = next_++;
+        const std::function<void(size_t)>* task = task_;
+        lk.unlock();
+        (*task)(t);
+        lk.lock();
+        if (--pending_ == 0) done_.notify_all();
+      }
+      seen = generation_;
+    }
+  }
+  std::mutex m_, run_mutex_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> threads_;
+  const std::function<void(size_t)>* task_ = nullptr;
+  size_t n_tasks_ = 0, next_ = 0, pending_ = 0;
+  uint64_t generation_ = 0;
+  bool stop_ = false;
+};
+thread_local bool Pool::inside = false;
+}  // namespace
+
 void StaticFor(size_t begin, size_t end, const std::function<void(size_t, size_t)>& f) {
   const size_t n = end - begin;
   const size_t nt = std::min(g_threads, std::max<size_t>(n, 1));
   if (nt <= 1 || n == 0) {
     if (n) f(begin, end);
+    return;
+  }
+  if (!Pool::inside) {
+    Pool::Get().Run(nt, nt, [&](size_t t) {
+      const size_t lo = begin + n * t / nt, hi = begin + n * (t + 1) / nt;
+      if (lo != hi) f(lo, hi);
+    });
     return;
   }
   std::vector<std::thread> pool;
@@ -52,6 +133,10 @@ void DynamicFor(size_t begin, size_t end, const std::function<void(size_t)>& f) 
   const size_t nt = std::min(g_threads, n);
   if (nt <= 1) {
     for (size_t i = begin; i != end; ++i) f(i);
+    return;
+  }
+  if (!Pool::inside) {
+    Pool::Get().Run(n, nt, [&](size_t i) { f(begin + i); });
     return;
   }
   std::atomic<size_t> next{begin};

@@ -16,6 +16,8 @@
 #include <string>
 #include <vector>
 
+#include <schaapcommon/math/convolution.h>
+
 #include "algorithms/generic_clean.h"
 #include "algorithms/iuwt_deconvolution.h"
 #include "algorithms/multiscale_algorithm.h"
@@ -294,6 +296,29 @@ int refa_execute(void* handle, float* residual, float* model, const float* psfs,
     out->another_iteration_required = r.another_iteration_required;
     out->iteration_number = h->parallel->FirstAlgorithm().IterationNumber();
   });
+}
+
+// Convolution statistics since the last reset (oracle/ref_shim/schaapcommon/math/convolution.h):
+// up to `capacity` (width, height, count) triples, the seconds spent inside Convolve; returns the
+// number of distinct sizes.
+uint64_t refa_convolve_stats(uint64_t* triples, uint64_t capacity, double* seconds, int32_t reset) {
+  auto& s = schaapcommon::math::ConvolveStats::Get();
+  const std::lock_guard<std::mutex> lock(s.mutex);
+  uint64_t n = 0;
+  for (const auto& kv : s.calls) {
+    if (triples && n < capacity) {
+      triples[3 * n] = kv.first.first;
+      triples[3 * n + 1] = kv.first.second;
+      triples[3 * n + 2] = kv.second;
+    }
+    ++n;
+  }
+  if (seconds) *seconds = s.seconds;
+  if (reset) {
+    s.calls.clear();
+    s.seconds = 0.0;
+  }
+  return n;
 }
 
 uint64_t refa_iteration_number(void* handle) {

@@ -90,7 +90,7 @@ EXPORTED_SYMBOLS = [
     "rdl_set_rms_factor_image", "rdl_set_spectral_fitter", "rdl_set_auto_mask_mode",
     "rdl_set_trace_capacity", "rdl_iteration_number", "rdl_scale_count", "rdl_scale_info_get",
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
-    "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_execute_major_iteration",
+    "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_reference_convolutions", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
@@ -375,6 +375,15 @@ class DeconvolutionAlgorithm:
     @property
     def kernel_launch_count(self) -> int: return lib().rdl_kernel_launch_count(self._h)
     @property
+    def reference_convolutions(self) -> dict:
+        """{(width, height): count} of the Convolve calls the reference makes for the last call."""
+        f = lib().rdl_reference_convolutions
+        f.restype = C.c_uint64
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        buf = np.zeros(3 * 64, np.uint64)
+        n = f(self._h, buf.ctypes.data, 64)
+        return {(int(buf[3 * i]), int(buf[3 * i + 1])): int(buf[3 * i + 2]) for i in range(min(n, 64))}
+
     def scale_count(self) -> int: return lib().rdl_scale_count(self._h)
 
     def scale_infos(self):

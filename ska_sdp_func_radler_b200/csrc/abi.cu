@@ -331,6 +331,19 @@ uint64_t rdl_trace_get(const rdl_handle* h, rdl_trace_entry* out, uint64_t capac
 uint64_t rdl_last_selected_count(const rdl_handle* h) { return h ? h->last_selected : 0; }
 uint64_t rdl_minor_iteration_count(const rdl_handle* h) { return h ? h->minor_iterations : 0; }
 uint64_t rdl_kernel_launch_count(const rdl_handle* h) { return h ? h->launches : 0; }
+uint64_t rdl_reference_convolutions(const rdl_handle* h, uint64_t* triples, uint64_t capacity) {
+  if (!h) return 0;
+  uint64_t n = 0;
+  for (const auto& kv : h->reference_convolutions) {
+    if (triples && n < capacity) {
+      triples[3 * n] = kv.first.first;
+      triples[3 * n + 1] = kv.first.second;
+      triples[3 * n + 2] = kv.second;
+    }
+    ++n;
+  }
+  return n;
+}
 
 uint64_t rdl_scale_count(const rdl_handle* h) { return h && h->ms ? MultiScaleScaleCount(*h->ms) : 0; }
 rdl_status rdl_scale_info_get(const rdl_handle* h, uint64_t i, rdl_scale_info* out) {

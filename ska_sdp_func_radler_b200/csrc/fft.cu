@@ -1016,9 +1016,12 @@ FftConvolver::FftConvolver(size_t width, size_t height, size_t content_width, si
       RDL_CUDA(cudaFuncSetAttribute(FastRowInverseKernel, attr, smem_max));
       RDL_CUDA(cudaFuncSetAttribute(FastColumnBlockKernel<true>, attr, smem_max));
       RDL_CUDA(cudaFuncSetAttribute(FastColumnBlockKernel<false>, attr, smem_max));
-      // Column passes run band by band so that the three passes of a band find it in L2
-      // (126 MB): about 40 MB of spectrum per band. RDL_FFT_BAND_MB=0 switches banding off.
-      double band_mb = 40.0;
+      // The column passes can run band by band so that the three passes of a band find it in L2
+      // (RDL_FFT_BAND_MB = spectrum megabytes per band). Measured on B200 (profiles/
+      // r02_fft_bench_bands.jsonl): 8192^2 1.02 ms unbanded, 1.09 / 1.16 / 1.27 ms with 70 / 40 /
+      // 20 MB bands -- the extra launches and tails cost more than the L2 hits save, so the default
+      // is one band.
+      double band_mb = 0.0;
       if (const char* e = std::getenv("RDL_FFT_BAND_MB")) band_mb = std::atof(e);
       const int tiles = d.pitch / kTileCols;
       const double tile_mb = double(d.H) * kTileCols * sizeof(float2) / 1.0e6;

@@ -166,6 +166,10 @@ struct rdl_handle {
   rdl::DeviceBuffer<unsigned long long> key;
   uint64_t last_selected = 0;
   uint64_t minor_iterations = 0;
+  // schaapcommon::math::Convolve calls the REFERENCE would make for the work of the last call,
+  // by frame size (the device path caches spectra and twice-convolved PSFs, so it runs fewer):
+  // bench.py prices the CPU side with it
+  std::map<std::pair<size_t, size_t>, uint64_t> reference_convolutions;
 
   // staging for RDL_MEM_HOST calls
   rdl::DeviceBuffer<float> stage_residual, stage_model, stage_psf;

@@ -369,6 +369,7 @@ void MultiScaleRun::ConvolvePsfs(size_t slot, const float* psf, bool is_integrat
     if (e.scale != 0.0f) {
       DeviceBuffer<float>& dst = convolved_psfs_[slot * n_scales + si];
       dst.Reserve(n_);
+      ++h_.reference_convolutions[{width_, height_}];
       conv_.ConvolveWith(psf, width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0, stream_);
       convolved = dst.get();
     }
@@ -424,6 +425,7 @@ void MultiScaleRun::FindActiveScaleConvolvedMaxima(bool report_rms) {
       if (report_rms) e.rms = RmsOf(integrated_.get());
       continue;
     }
+    ++h_.reference_convolutions[{width_, height_}];
     conv_.ConvolveWith(integrated_.get(), width_, height_, ScaleSpectrum(si), scratch_.get(), width_,
                        height_, 0, stream_);
     const size_t border_scale = size_t(std::ceil(e.scale * 0.5));
@@ -571,6 +573,7 @@ bool MultiScaleRun::RunWithoutSubMinorLoop(size_t swp, float first_sub_iteration
 // The reference recomputes it in every minor iteration that selects the scale; the PSFs do not
 // change during a call, so it is kept while HBM allows (K4: 16 PSFs x 4 scales x 268 MB).
 const float* MultiScaleRun::TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum) {
+  ++h_.reference_convolutions[{width_, height_}];  // the reference transforms it again every time
   const auto key = std::make_pair(p, si);
   auto it = twice_cache_.find(key);
   if (it != twice_cache_.end()) return it->second.get();
@@ -701,6 +704,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       for (size_t p = 0; p != n_psfs; ++p) twice[p] = TwiceConvolvedPsf(p, swp, spectrum);
       for (size_t i = 0; i != cube_.n_images; ++i) {
         individual_convolved_[i].Reserve(n_);
+        ++h.reference_convolutions[{width_, height_}];
         conv_.ConvolveWith(cube_.residual.p[i], width_, height_, spectrum, individual_convolved_[i].get(),
                            width_, height_, 0, stream_);
         conv_residual.p[i] = individual_convolved_[i].get();
@@ -785,6 +789,8 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       const float2* psf_spectrum = PsfSpectrum(cube_.PsfIndex(i), swp, padded);
       SubMinorScatterModel(h, int(i), scratch_.get(), n_, stream_);
       // CorrectResidualDirty (subminor_loop.cc:195-218): residual -= Trim(Convolve(Untrim(model)))
+      ++h.reference_convolutions[{conv_w, conv_h}];
+      if (S[swp].scale != 0.0f) ++h.reference_convolutions[{width_, height_}];
       padded.ConvolveWith(scratch_.get(), width_, height_, psf_spectrum, cube_.residual.p[i], width_,
                           height_, 1, stream_);
       if (i == 0 && h.track_per_scale_masks)
@@ -827,6 +833,7 @@ rdl_result RunMultiScale(rdl_handle& h, DeviceCube& cube, cudaStream_t stream) {
   if (!h.ms) h.ms = std::make_shared<MultiScaleState>();
   h.trace_host.clear();
   h.minor_iterations = 0;
+  h.reference_convolutions.clear();
   MultiScaleRun run(h, cube, stream);
   return run.Execute();
 }

@@ -571,6 +571,7 @@ void SubMinorCollectTrace(rdl_handle& h, cudaStream_t stream) {
 rdl_result RunGenericCleanSubMinor(rdl_handle& h, DeviceCube& cube, cudaStream_t stream) {
   const size_t width = cube.width, height = cube.height, n = cube.Pixels();
   const uint64_t iteration_at_start = h.iteration_number;
+  h.reference_convolutions.clear();
   // generic_clean.cc:63-66: float 1.1f padding, rounded up to even (NOT the 2357-smooth size)
   const float padding = 1.1f;
   size_t conv_w = size_t(std::ceil(padding * float(width)));
@@ -656,6 +657,7 @@ rdl_result RunGenericCleanSubMinor(rdl_handle& h, DeviceCube& cube, cudaStream_t
       spectrum_of_psf = p;
     }
     SubMinorScatterModel(h, int(i), h.fft_scratch.get(), n, stream);
+    ++h.reference_convolutions[{conv_w, conv_h}];
     conv.ConvolveWith(h.fft_scratch.get(), width, height, h.fft_spectrum.get(),
                       cube.residual.p[i], width, height, 1, stream);
     SubMinorAddModelTo(h, int(i), cube.model.p[i], stream);

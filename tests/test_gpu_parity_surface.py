@@ -184,3 +184,32 @@ def test_path_a_odd_frame(rdl, oracle, torch_cuda):
     o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, None, st, sub_minor=True)
     assert o.iteration_number > 10
     path_a_check(o, oi, g, gi, alg)
+
+
+# ---- the convolution count bench.py prices the CPU side with --------------------------------------
+@pytest.mark.parametrize("c,iters,mgain", [(2, 1, 0.8), (3, 400, 0.8)])
+def test_reference_convolution_count_matches_the_reference(rdl, oracle, torch_cuda, c, iters, mgain):
+    """rdl_reference_convolutions = the schaapcommon::math::Convolve calls the reference's own
+    MultiScaleAlgorithm makes for the same major iteration, size by size (counted inside the
+    reference run by the stand-in of schaapcommon/math/convolution.h)."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n = 256
+    res, psfs, weights, freqs = multiscale_case(n, c)
+    kw = dict(max_iterations=iters, major_loop_gain=mgain, clean_border_ratio=0.0)
+    oracle.ref_convolve_stats(reset=True)
+    ref = oracle.Reference("multiscale", n, n, c, weights=weights, frequencies=freqs, beam_size=6.0,
+                           max_scales=4, fit_terms=2, **kw)
+    a, m = res.copy(), np.zeros_like(res)
+    w = ref.execute(a, m, psfs)
+    want, seconds = oracle.ref_convolve_stats(reset=True)
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4)
+    alg.apply(**kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, freqs, weights, 1)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, n, n), device="cuda")
+    g = alg.execute_major_iteration(rdl.Cube(n, n, c, 1, weights), d_res, d_model,
+                                    torch.from_numpy(psfs).cuda())
+    assert g.iteration_number == w.iteration_number
+    assert alg.reference_convolutions() == want
+    assert seconds > 0
