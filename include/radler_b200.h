@@ -143,6 +143,19 @@ rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t 
 rdl_status rdl_set_spectral_fitter(rdl_handle* h, int32_t mode, uint64_t n_terms,
                                    const double* frequencies, const float* weights,
                                    uint64_t n_channels, uint64_t n_polarizations);
+
+/* RDL_MEM_HOST calls only. Radler passes the same psf_images to every major iteration of a run
+ * (radler.cc:175-268): with rdl_set_psfs_constant(h, 1) the caller promises that PSF planes
+ * passed again under the same pointers are unchanged, and they are copied to the device once
+ * instead of on every call. Any other pointer, plane size or plane count uploads again. */
+rdl_status rdl_set_psfs_constant(rdl_handle* h, int32_t constant);
+/* RDL_MEM_HOST calls only. With rdl_set_pin_host_buffers(h, 1) the caller's residual / model /
+ * PSF planes are registered (cudaHostRegister) the first time they are seen, so that pageable
+ * aocommon::Image buffers are copied at PCIe rate; they are unregistered by rdl_destroy or by
+ * switching the option off. Planes that cannot be registered are copied as they are. The caller
+ * must keep a registered plane allocated until then. */
+rdl_status rdl_set_pin_host_buffers(rdl_handle* h, int32_t enable);
+
 /* MultiScaleAlgorithm::SetAutoMaskMode (multiscale_algorithm.h:41-45) */
 rdl_status rdl_set_auto_mask_mode(rdl_handle* h, int32_t track_per_scale_masks,
                                   int32_t use_per_scale_masks);

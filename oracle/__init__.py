@@ -694,12 +694,39 @@ class _RefResult(C.Structure):
 _refa_ready = False
 
 
+_ADAPTER_PATH = os.path.join(_HERE, "_ref", "libradler_ref_adapter.so")
+_adapter = None
+
+
+def adapter_lib():
+    """oracle/_ref/libradler_ref_adapter.so: the reference's own sources again, plus
+    include/cuda_deconvolution.h (the adapter a Radler maintainer adds) so that the algorithm
+    behind the reference's ParallelDeconvolution can be the CUDA library. Built by `make -C oracle
+    adapter` where /root/reference exists; None when it was never built."""
+    global _adapter
+    if _adapter is None:
+        if not os.path.exists(_ADAPTER_PATH):
+            if not os.path.isdir(os.path.join(_REFERENCE_ROOT, "cpp")):
+                return None
+            subprocess.run(["make", "-C", _HERE, "-s", "adapter"], check=True)
+        _adapter = C.CDLL(_ADAPTER_PATH)
+        _bind_refa(_adapter)
+    return _adapter
+
+
 def _refa():
     global _refa_ready
     L = ref_lib()
     if L is None:
         return None
     if not _refa_ready:
+        _bind_refa(L)
+        _refa_ready = True
+    return L
+
+
+def _bind_refa(L):
+    if True:
         vp, u64 = C.c_void_p, C.c_uint64
         L.refa_last_error.restype = C.c_char_p
         L.refa_last_error.argtypes = [vp]
@@ -733,8 +760,6 @@ def _refa():
         L.refa_parallel_scale_mask_count.restype = u64
         L.refa_parallel_scale_mask_count.argtypes = [vp]
         L.refa_parallel_scale_mask.argtypes = [vp, u64, u64, u64, vp]
-        _refa_ready = True
-    return L
 
 
 @dataclass
@@ -774,13 +799,18 @@ class Reference:
                  stop_on_negative=False, fast_sub_minor_loop=True, sub_minor_loop_gain=0.2,
                  scale_bias=0.6, max_scales=0, convolution_padding=1.1, scale_list=None, shape=0,
                  beam_size=0.0, pixel_scale=1.0, track_components=False, fit_terms=0,
-                 grid=(1, 1), threads=0, squared_joins=False):
-        L = _refa()
+                 grid=(1, 1), threads=0, squared_joins=False, adapter=False):
+        """adapter=True: the same driver with radler::algorithms::CudaDeconvolution
+        (include/cuda_deconvolution.h) as the algorithm behind the reference's
+        ParallelDeconvolution instead of the reference's CPU algorithm."""
+        L = adapter_lib() if adapter else _refa()
         if L is None:
-            raise RuntimeError("oracle/_ref/libradler_ref.so is not built")
+            raise RuntimeError("oracle/_ref is not built")
+        self._L = L
         sl = np.ascontiguousarray(scale_list if scale_list else [], np.float64)
         cfg = _RefConfig(
-            {"generic": 0, "multiscale": 1, "iuwt": 2}[algorithm], int(use_sub_minor_optimization),
+            {"generic": 0, "multiscale": 1, "iuwt": 2}[algorithm] + (10 if adapter else 0),
+            int(use_sub_minor_optimization),
             threshold, minor_loop_gain, major_loop_gain, clean_border_ratio, divergence_limit,
             max_iterations, int(allow_negative), int(stop_on_negative), int(fast_sub_minor_loop),
             sub_minor_loop_gain, scale_bias, max_scales, convolution_padding,
@@ -795,34 +825,34 @@ class Reference:
         self._h = L.refa_create(C.byref(cfg), width, height, n_channels, len(pols), _ptr(p),
                                 _ptr(w), _ptr(f))
         if not self._h:
-            raise RuntimeError(L.refa_last_error(None).decode())
+            raise RuntimeError(self._L.refa_last_error(None).decode())
 
     def __del__(self):
-        if getattr(self, "_h", None) and _ref is not None:
-            _ref.refa_destroy(self._h)
+        if getattr(self, "_h", None) and getattr(self, "_L", None) is not None:
+            self._L.refa_destroy(self._h)
             self._h = None
 
     def _check(self, rc):
         if rc != 0:
-            raise RuntimeError(_ref.refa_last_error(self._h).decode())
+            raise RuntimeError(self._L.refa_last_error(self._h).decode())
 
-    def set_threshold(self, v): self._check(_ref.refa_set_threshold(self._h, v))
-    def set_minor_loop_gain(self, v): self._check(_ref.refa_set_minor_loop_gain(self._h, v))
+    def set_threshold(self, v): self._check(self._L.refa_set_threshold(self._h, v))
+    def set_minor_loop_gain(self, v): self._check(self._L.refa_set_minor_loop_gain(self._h, v))
     def set_major_loop_gain(self, v): self._major_loop_gain = v
     def set_auto_mask_mode(self, track, use):
-        self._check(_ref.refa_set_auto_mask_mode(self._h, int(track), int(use)))
-    def set_iteration_number(self, n): self._check(_ref.refa_set_iteration_number(self._h, n))
-    def set_max_iterations(self, n): self._check(_ref.refa_set_max_iterations(self._h, n))
+        self._check(self._L.refa_set_auto_mask_mode(self._h, int(track), int(use)))
+    def set_iteration_number(self, n): self._check(self._L.refa_set_iteration_number(self._h, n))
+    def set_max_iterations(self, n): self._check(self._L.refa_set_max_iterations(self._h, n))
     def set_major_iteration_threshold(self, v):
-        self._check(_ref.refa_set_major_iteration_threshold(self._h, v))
+        self._check(self._L.refa_set_major_iteration_threshold(self._h, v))
 
     def set_clean_mask(self, mask):
         m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
-        self._check(_ref.refa_set_clean_mask(self._h, _ptr(m)))
+        self._check(self._L.refa_set_clean_mask(self._h, _ptr(m)))
 
     def set_rms_factor_image(self, image):
         a = None if image is None else _f32(image)
-        self._check(_ref.refa_set_rms_factor_image(self._h, _ptr(a)))
+        self._check(self._L.refa_set_rms_factor_image(self._h, _ptr(a)))
 
     def execute(self, residual, model, psfs, psf_offsets=None) -> RefResult:
         """residual/model [n_images,H,W] updated in place; psfs [n_channels,h,w] or
@@ -838,34 +868,34 @@ class Reference:
             ox = np.ascontiguousarray([o[0] for o in psf_offsets], np.int64)
             oy = np.ascontiguousarray([o[1] for o in psf_offsets], np.int64)
         out = _RefResult()
-        self._check(_ref.refa_execute(self._h, _ptr(residual), _ptr(model), _ptr(psfs), n_dd, pw,
+        self._check(self._L.refa_execute(self._h, _ptr(residual), _ptr(model), _ptr(psfs), n_dd, pw,
                                       ph, _ptr(ox), _ptr(oy), self._major_loop_gain,
                                       C.byref(out)))
         return RefResult(out.start_peak if out.has_start_peak else None, out.end_peak,
                          bool(out.another_iteration_required), out.iteration_number)
 
     @property
-    def iteration_number(self): return _ref.refa_iteration_number(self._h)
+    def iteration_number(self): return self._L.refa_iteration_number(self._h)
 
     def scale_sizes(self):
-        return [_ref.refa_scale_size(self._h, i) for i in range(_ref.refa_scale_count(self._h))]
+        return [self._L.refa_scale_size(self._h, i) for i in range(self._L.refa_scale_count(self._h))]
 
     def scale_mask(self, i):
         m = np.zeros((self.height, self.width), np.uint8)
-        self._check(_ref.refa_scale_mask(self._h, i, _ptr(m)))
+        self._check(self._L.refa_scale_mask(self._h, i, _ptr(m)))
         return m
 
     def component_list(self, n_images):
         """MultiScaleAlgorithm::GetComponentList() after MergeDuplicates: per scale
         (x[n], y[n], values[n, n_images])."""
         out = []
-        for scale in range(_ref.refa_component_scales(self._h)):
-            n = _ref.refa_component_count(self._h, scale)
+        for scale in range(self._L.refa_component_scales(self._h)):
+            n = self._L.refa_component_count(self._h, scale)
             x, y = np.zeros(n, np.uint64), np.zeros(n, np.uint64)
             v = np.zeros((n, n_images), np.float32)
             cx, cy = C.c_uint64(), C.c_uint64()
             for i in range(n):
-                self._check(_ref.refa_component_get(self._h, scale, i, C.byref(cx), C.byref(cy),
+                self._check(self._L.refa_component_get(self._h, scale, i, C.byref(cx), C.byref(cy),
                                                     _ptr(v[i])))
                 x[i], y[i] = cx.value, cy.value
             out.append((x, y, v))
@@ -874,8 +904,8 @@ class Reference:
     def parallel_scale_masks(self):
         """ParallelDeconvolution's frame-sized per-scale masks (facet runs)."""
         out = []
-        for i in range(_ref.refa_parallel_scale_mask_count(self._h)):
+        for i in range(self._L.refa_parallel_scale_mask_count(self._h)):
             m = np.zeros((self.height, self.width), np.uint8)
-            self._check(_ref.refa_parallel_scale_mask(self._h, i, self.width, self.height, _ptr(m)))
+            self._check(self._L.refa_parallel_scale_mask(self._h, i, self.width, self.height, _ptr(m)))
             out.append(m)
         return out

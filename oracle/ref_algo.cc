@@ -28,6 +28,11 @@
 #include "image_set.h"
 #include "settings.h"
 #include "work_table.h"
+#ifdef RDL_WITH_ADAPTER
+// the adapter library (oracle/Makefile target `adapter`): algorithm codes 10 / 11 / 12 put
+// radler::algorithms::CudaDeconvolution behind the reference's ParallelDeconvolution
+#include "cuda_deconvolution.h"
+#endif
 
 using namespace radler;
 
@@ -140,9 +145,11 @@ void* refa_create(const refa_config* c, uint64_t width, uint64_t height, uint64_
                                   ? schaapcommon::fitters::SpectralFittingMode::kPolynomial
                                   : schaapcommon::fitters::SpectralFittingMode::kNoFitting;
     s.spectral_fitting.terms = c->fit_terms;
-    s.algorithm_type = c->algorithm == 0   ? AlgorithmType::kGenericClean
-                       : c->algorithm == 1 ? AlgorithmType::kMultiscale
-                                           : AlgorithmType::kIuwt;
+    const int32_t algorithm_code = c->algorithm % 10;
+    const bool use_adapter = c->algorithm >= 10;
+    s.algorithm_type = algorithm_code == 0   ? AlgorithmType::kGenericClean
+                       : algorithm_code == 1 ? AlgorithmType::kMultiscale
+                                             : AlgorithmType::kIuwt;
     h->width = width;
     h->height = height;
     h->n_channels = n_channels;
@@ -169,6 +176,29 @@ void* refa_create(const refa_config* c, uint64_t width, uint64_t height, uint64_
 
     // Radler::InitializeDeconvolutionAlgorithm, radler.cc:348-388
     std::unique_ptr<algorithms::DeconvolutionAlgorithm> algorithm;
+    if (use_adapter) {
+#ifdef RDL_WITH_ADAPTER
+      // what INTEGRATION.md adds to Radler::InitializeDeconvolutionAlgorithm (radler.cc:348-375)
+      rdl_config rc;
+      rdl_config_default(&rc);
+      rc.algorithm = algorithm_code == 0 ? RDL_GENERIC_CLEAN
+                                         : (algorithm_code == 1 ? RDL_MULTISCALE : RDL_IUWT);
+      rc.use_sub_minor_optimization = s.generic.use_sub_minor_optimization;
+      rc.ms_fast_sub_minor_loop = s.multiscale.fast_sub_minor_loop;
+      rc.ms_sub_minor_loop_gain = s.multiscale.sub_minor_loop_gain;
+      rc.ms_scale_bias = s.multiscale.scale_bias;
+      rc.ms_max_scales = s.multiscale.max_scales;
+      rc.ms_convolution_padding = s.multiscale.convolution_padding;
+      rc.ms_scale_list = s.multiscale.scale_list.data();
+      rc.ms_n_scale_list = s.multiscale.scale_list.size();
+      rc.ms_shape = c->ms_shape;
+      rc.beam_size = c->beam_size;
+      rc.pixel_scale_x = rc.pixel_scale_y = s.pixel_scale.x;
+      algorithm = std::make_unique<algorithms::CudaDeconvolution>(rc);
+#else
+      throw std::runtime_error("this library was built without the CUDA adapter");
+#endif
+    } else
     switch (s.algorithm_type) {
       case AlgorithmType::kGenericClean:
         algorithm =

@@ -88,6 +88,7 @@ EXPORTED_SYMBOLS = [
     "rdl_set_stop_on_negative_components", "rdl_set_clean_border_ratio",
     "rdl_set_divergence_limit", "rdl_set_iteration_number", "rdl_set_clean_mask",
     "rdl_set_rms_factor_image", "rdl_set_spectral_fitter", "rdl_set_auto_mask_mode",
+    "rdl_set_psfs_constant", "rdl_set_pin_host_buffers",
     "rdl_set_trace_capacity", "rdl_iteration_number", "rdl_scale_count", "rdl_scale_info_get",
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_reference_convolutions", "rdl_execute_major_iteration",
@@ -149,6 +150,8 @@ def lib():
                  "rdl_kernel_launch_count"]:
         getattr(L, name).argtypes = [vp]
         getattr(L, name).restype = u64
+    L.rdl_set_psfs_constant.argtypes = [vp, i32]
+    L.rdl_set_pin_host_buffers.argtypes = [vp, i32]
     L.rdl_scale_info_get.argtypes = [vp, u64, C.POINTER(_ScaleInfo)]
     L.rdl_scale_mask_get.argtypes = [vp, u64, vp]
     L.rdl_trace_get.argtypes = [vp, vp, u64]
@@ -355,6 +358,14 @@ class DeconvolutionAlgorithm:
         self._check(lib().rdl_set_spectral_fitter(
             self._h, mode, n_terms, None if fr is None else fr.ctypes.data,
             None if w is None else w.ctypes.data, 0 if fr is None else len(fr), n_pol))
+
+    def set_psfs_constant(self, constant: bool):
+        """Host buffers: PSF planes passed again under the same pointers are not uploaded again."""
+        self._check(lib().rdl_set_psfs_constant(self._h, int(constant)))
+
+    def set_pin_host_buffers(self, enable: bool):
+        """Host buffers: register the caller's planes with cudaHostRegister on first use."""
+        self._check(lib().rdl_set_pin_host_buffers(self._h, int(enable)))
 
     def set_auto_mask_mode(self, track: bool, use: bool):
         self._check(lib().rdl_set_auto_mask_mode(self._h, int(track), int(use)))

@@ -103,6 +103,28 @@ void SetVec(DeviceCube& cube) {
   cube.vec = ok ? 4 : 1;
 }
 
+// cudaHostRegister a caller's plane once, so that its copies run at PCIe rate and overlap; a plane
+// that cannot be registered (already pinned by the caller, not mappable) is simply copied as it is
+void PinPlane(rdl_handle* h, const void* p, size_t bytes) {
+  if (!h->pin_host_buffers || !p) return;
+  auto it = h->pinned.find(p);
+  if (it != h->pinned.end() && it->second >= bytes) return;
+  if (it != h->pinned.end()) {
+    cudaHostUnregister(const_cast<void*>(p));
+    h->pinned.erase(it);
+  }
+  if (cudaHostRegister(const_cast<void*>(p), bytes, cudaHostRegisterDefault) == cudaSuccess)
+    h->pinned[p] = bytes;
+  else
+    cudaGetLastError();
+}
+
+void UnpinAll(rdl_handle* h) {
+  for (const auto& kv : h->pinned) cudaHostUnregister(const_cast<void*>(kv.first));
+  cudaGetLastError();
+  h->pinned.clear();
+}
+
 cudaStream_t StreamOf(rdl_handle* h, void* stream) {
   return stream ? static_cast<cudaStream_t>(stream) : h->own_stream;
 }
@@ -214,6 +236,7 @@ void rdl_destroy(rdl_handle* h) {
     NcclDestroy(h->dist);
   } catch (...) {
   }
+  UnpinAll(h);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
   // the last handle takes the cached device memory with it
@@ -246,6 +269,10 @@ RDL_SETTER(rdl_set_clean_border_ratio(rdl_handle* h, float v), h->settings.clean
 RDL_SETTER(rdl_set_divergence_limit(rdl_handle* h, float v), h->settings.divergence_limit = v)
 RDL_SETTER(rdl_set_iteration_number(rdl_handle* h, uint64_t n), h->iteration_number = n)
 RDL_SETTER(rdl_set_trace_capacity(rdl_handle* h, uint64_t n), h->trace_capacity = n)
+RDL_SETTER(rdl_set_psfs_constant(rdl_handle* h, int32_t v),
+           (h->psfs_constant = v != 0, h->staged_psf_ptrs.clear()))
+RDL_SETTER(rdl_set_pin_host_buffers(rdl_handle* h, int32_t v),
+           (h->pin_host_buffers = v != 0, (v == 0 ? UnpinAll(h) : void())))
 RDL_SETTER(rdl_set_auto_mask_mode(rdl_handle* h, int32_t track, int32_t use),
            (h->track_per_scale_masks = track != 0, h->use_per_scale_masks = use != 0))
 #undef RDL_SETTER
@@ -447,14 +474,26 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
       for (size_t i = 0; i != cube.n_images; ++i) {
         cube.residual.p[i] = h->stage_residual.get() + i * n;
         cube.model.p[i] = h->stage_model.get() + i * n;
+        PinPlane(h, residual[i], bytes);
+        PinPlane(h, model[i], bytes);
         RDL_CUDA(cudaMemcpyAsync(cube.residual.p[i], residual[i], bytes, cudaMemcpyHostToDevice, stream));
         RDL_CUDA(cudaMemcpyAsync(cube.model.p[i], model[i], bytes, cudaMemcpyHostToDevice, stream));
       }
+      // the PSFs do not change between the major iterations of a run (radler.cc:175-268 passes the
+      // same psf_images every time): with rdl_set_psfs_constant they cross PCIe once
+      bool staged = h->psfs_constant && h->staged_psf_pixels == psf_n &&
+                    h->staged_psf_ptrs.size() == cube.n_channels;
+      for (size_t i = 0; staged && i != cube.n_channels; ++i) staged = h->staged_psf_ptrs[i] == psfs[i];
       for (size_t i = 0; i != cube.n_channels; ++i) {
         float* dst = h->stage_psf.get() + i * psf_n;
-        RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], psf_bytes, cudaMemcpyHostToDevice, stream));
+        if (!staged) {
+          PinPlane(h, psfs[i], psf_bytes);
+          RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], psf_bytes, cudaMemcpyHostToDevice, stream));
+        }
         cube.psf.p[i] = dst;
       }
+      h->staged_psf_ptrs.assign(psfs, psfs + cube.n_channels);
+      h->staged_psf_pixels = psf_n;
     } else {
       for (size_t i = 0; i != cube.n_images; ++i) {
         cube.residual.p[i] = residual[i];

@@ -20,6 +20,12 @@ struct NcclApi {
                             cudaStream_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                             cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -45,6 +51,11 @@ const NcclApi& Api() {
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
     api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
     api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+    api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(sym("ncclBroadcast"));
+    api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+    api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+    api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+    api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
   });
   if (!error.empty()) throw CudaError(error);
@@ -89,6 +100,28 @@ void NcclAllGatherBytes(DistContext& ctx, const void* send, void* recv, size_t b
   Check(Api().AllGather(send, recv, bytes_per_rank, ncclChar, static_cast<ncclComm_t>(ctx.comm),
                         stream),
         "ncclAllGather");
+}
+
+void NcclBroadcastPlanes(DistContext& ctx, float* const* planes, const int* roots, size_t n_planes,
+                         size_t count, cudaStream_t stream) {
+  if (!ctx.comm) throw std::invalid_argument("rdl_dist_init was not called on this handle");
+  if (n_planes == 0) return;
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx.comm);
+  Check(Api().GroupStart(), "ncclGroupStart");
+  for (size_t i = 0; i != n_planes; ++i)
+    Check(Api().Broadcast(planes[i], planes[i], count, ncclFloat, roots[i], comm, stream),
+          "ncclBroadcast");
+  Check(Api().GroupEnd(), "ncclGroupEnd");
+}
+
+void NcclSendFloat(DistContext& ctx, const float* data, size_t count, int peer, cudaStream_t stream) {
+  if (!ctx.comm) throw std::invalid_argument("rdl_dist_init was not called on this handle");
+  Check(Api().Send(data, count, ncclFloat, peer, static_cast<ncclComm_t>(ctx.comm), stream), "ncclSend");
+}
+
+void NcclRecvFloat(DistContext& ctx, float* data, size_t count, int peer, cudaStream_t stream) {
+  if (!ctx.comm) throw std::invalid_argument("rdl_dist_init was not called on this handle");
+  Check(Api().Recv(data, count, ncclFloat, peer, static_cast<ncclComm_t>(ctx.comm), stream), "ncclRecv");
 }
 
 void NcclAllReduceSumFloat(DistContext& ctx, float* data, size_t count, cudaStream_t stream) {

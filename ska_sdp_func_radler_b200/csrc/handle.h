@@ -173,6 +173,14 @@ struct rdl_handle {
 
   // staging for RDL_MEM_HOST calls
   rdl::DeviceBuffer<float> stage_residual, stage_model, stage_psf;
+  // rdl_set_psfs_constant: the PSF planes staged by the previous host-memory call are reused when
+  // the caller passes the same pointers again
+  bool psfs_constant = false;
+  std::vector<const float*> staged_psf_ptrs;
+  size_t staged_psf_pixels = 0;
+  // rdl_set_pin_host_buffers: caller planes registered with cudaHostRegister (pointer -> bytes)
+  bool pin_host_buffers = false;
+  std::map<const void*, size_t> pinned;
 
   rdl::SubMinorBuffers sub;
   // FFT scratch: one W x H image, one kernel spectrum, one uploaded scale kernel

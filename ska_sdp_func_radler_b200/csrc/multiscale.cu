@@ -5,6 +5,19 @@
 // selection, activation) and drives device-resident work: every image, PSF, convolved PSF
 // and scale-kernel spectrum lives in HBM for the whole call; the only host traffic per
 // minor iteration is a handful of 8-byte peak records and the sub-minor loop's result.
+//
+// Several GPUs (rdl_dist_init on the handle, no row band): the CHANNELS are sharded. Every rank
+// holds the whole cube; rank r owns the contiguous channel block [r P / world, (r + 1) P / world)
+// and runs all per-image FFT convolutions of those channels (convolved / twice-convolved PSFs,
+// scale-convolved residuals, CorrectResidualDirty, the model convolution:
+// multiscale_algorithm.cc:331-354, 432-461) -- 90+ % of a major iteration. What a joined step
+// needs from the other channels travels as whole planes, broadcast by their owners over NCCL /
+// NVLink (the scale-convolved residuals before the sub-minor loop, the corrected residuals after
+// it, the twice-convolved PSFs once per scale, the model at the end). Everything joined --
+// integration over the channels in the reference's sequential order, scale selection, pixel
+// selection and the sub-minor loop on the compact sets -- is computed by every rank on identical
+// data, so the ranks take identical decisions without exchanging them, and the result is
+// bit-identical to the single-GPU run.
 #include "multiscale.cuh"
 
 #include <algorithm>
@@ -259,7 +272,13 @@ class MultiScaleRun {
  public:
   MultiScaleRun(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
       : h_(h), cube_(cube), stream_(stream), st_(*h.ms), width_(cube.width), height_(cube.height),
-        n_(cube.Pixels()), conv_(GetConvolver(h, cube.width, cube.height)) {}
+        n_(cube.Pixels()), conv_(GetConvolver(h, cube.width, cube.height)) {
+    if (h.dist.comm && h.dist.world > 1 && !h.dist.band_set && cube.n_channels > 1) {
+      sharded_ = true;
+      world_ = h.dist.world;
+      rank_ = h.dist.rank;
+    }
+  }
 
   rdl_result Execute();
 
@@ -287,7 +306,22 @@ class MultiScaleRun {
   const float2* PsfSpectrum(size_t p, size_t si, FftConvolver& padded);
   const float* TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum);
   void Sync() { RDL_CUDA(cudaStreamSynchronize(stream_)); }
+  // channel sharding over the ranks
+  int OwnerOfChannel(size_t channel) const {
+    return sharded_ ? int(channel * size_t(world_) / cube_.n_channels) : 0;
+  }
+  bool MineChannel(size_t channel) const { return !sharded_ || OwnerOfChannel(channel) == rank_; }
+  bool MineImage(size_t image) const { return MineChannel(cube_.PsfIndex(image)); }
+  // every plane goes from the rank that owns its channel to all the others
+  void ShareImagePlanes(float* const* planes) {  // one plane per image
+    if (!sharded_) return;
+    std::vector<int> roots(cube_.n_images);
+    for (size_t i = 0; i != cube_.n_images; ++i) roots[i] = OwnerOfChannel(cube_.PsfIndex(i));
+    NcclBroadcastPlanes(h_.dist, planes, roots.data(), cube_.n_images, n_, stream_);
+  }
 
+  bool sharded_ = false;
+  int world_ = 1, rank_ = 0;
   rdl_handle& h_;
   DeviceCube& cube_;
   cudaStream_t stream_;
@@ -367,9 +401,11 @@ void MultiScaleRun::ConvolvePsfs(size_t slot, const float* psf, bool is_integrat
     rdl_scale_info& e = Scales()[si];
     const float* convolved = psf;
     if (e.scale != 0.0f) {
+      ++h_.reference_convolutions[{width_, height_}];
+      // per-channel PSFs: only the owner of the channel ever uses its convolved PSFs
+      if (!is_integrated && !MineChannel(slot)) continue;
       DeviceBuffer<float>& dst = convolved_psfs_[slot * n_scales + si];
       dst.Reserve(n_);
-      ++h_.reference_convolutions[{width_, height_}];
       conv_.ConvolveWith(psf, width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0, stream_);
       convolved = dst.get();
     }
@@ -577,6 +613,23 @@ const float* MultiScaleRun::TwiceConvolvedPsf(size_t p, size_t si, const float2*
   const auto key = std::make_pair(p, si);
   auto it = twice_cache_.find(key);
   if (it != twice_cache_.end()) return it->second.get();
+  if (sharded_) {
+    // the sub-minor loop of every rank reads the twice-convolved PSFs of ALL channels: each is
+    // computed by its owner once per call and scale, and sent to the others
+    std::vector<float*> planes(cube_.n_channels);
+    std::vector<int> roots(cube_.n_channels);
+    for (size_t q = 0; q != cube_.n_channels; ++q) {
+      DeviceBuffer<float> buf(n_);
+      planes[q] = buf.get();
+      roots[q] = OwnerOfChannel(q);
+      if (MineChannel(q))
+        conv_.ConvolveWith(ConvolvedPsf(q, si), width_, height_, scale_spectrum, planes[q], width_,
+                           height_, 0, stream_);
+      twice_cache_.emplace(std::make_pair(q, si), std::move(buf));
+    }
+    NcclBroadcastPlanes(h_.dist, planes.data(), roots.data(), planes.size(), n_, stream_);
+    return twice_cache_.find(key)->second.get();
+  }
   const size_t free_bytes = DeviceAvailableBytes();
   float* out = nullptr;
   if (free_bytes > n_ * sizeof(float) * 4 + (size_t(16) << 30)) {
@@ -702,14 +755,18 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       const float2* spectrum = ScaleSpectrum(swp);
       std::vector<const float*> twice(n_psfs);
       for (size_t p = 0; p != n_psfs; ++p) twice[p] = TwiceConvolvedPsf(p, swp, spectrum);
+      std::vector<float*> shared_planes(cube_.n_images);
       for (size_t i = 0; i != cube_.n_images; ++i) {
         individual_convolved_[i].Reserve(n_);
         ++h.reference_convolutions[{width_, height_}];
-        conv_.ConvolveWith(cube_.residual.p[i], width_, height_, spectrum, individual_convolved_[i].get(),
-                           width_, height_, 0, stream_);
+        if (MineImage(i))
+          conv_.ConvolveWith(cube_.residual.p[i], width_, height_, spectrum,
+                             individual_convolved_[i].get(), width_, height_, 0, stream_);
         conv_residual.p[i] = individual_convolved_[i].get();
+        shared_planes[i] = individual_convolved_[i].get();
         psf_per_image.p[i] = twice[cube_.PsfIndex(i)];
       }
+      ShareImagePlanes(shared_planes.data());
       h.launches += conv_.TakeLaunchCount();
     } else {
       // scale 0: the "convolved" images are the images themselves; the sub-minor loop only
@@ -738,6 +795,8 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     }
 
     if (!h.config.ms_fast_sub_minor_loop) {
+      if (sharded_)
+        throw std::domain_error("channel-sharded multiscale needs the fast sub-minor loop");
       PtrTable convolved{};
       for (size_t i = 0; i != cube_.n_images; ++i) convolved.p[i] = individual_convolved_[i].get();
       diverging = RunWithoutSubMinorLoop(swp, first_sub_iteration_threshold, initial_peak_value,
@@ -785,18 +844,21 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     S[swp].total_flux_cleaned += o.flux_cleaned;
 
     FftConvolver& padded = GetConvolver(h, conv_w, conv_h);
+    // the reference updates the mask / component list inside the loop at image 0; both only read
+    // the compact model of the sub-minor run, which every rank holds
+    if (h.track_per_scale_masks)
+      SubMinorUpdateAutoMask(h, int(cube_.n_images), st_.scale_masks[swp].get(), stream_);
+    if (h.config.track_components)
+      SubMinorUpdateComponentList(h, int(cube_.n_images), swp, stream_);
     for (size_t i = 0; i != cube_.n_images; ++i) {
+      ++h.reference_convolutions[{conv_w, conv_h}];
+      if (S[swp].scale != 0.0f) ++h.reference_convolutions[{width_, height_}];
+      if (!MineImage(i)) continue;
       const float2* psf_spectrum = PsfSpectrum(cube_.PsfIndex(i), swp, padded);
       SubMinorScatterModel(h, int(i), scratch_.get(), n_, stream_);
       // CorrectResidualDirty (subminor_loop.cc:195-218): residual -= Trim(Convolve(Untrim(model)))
-      ++h.reference_convolutions[{conv_w, conv_h}];
-      if (S[swp].scale != 0.0f) ++h.reference_convolutions[{width_, height_}];
       padded.ConvolveWith(scratch_.get(), width_, height_, psf_spectrum, cube_.residual.p[i], width_,
                           height_, 1, stream_);
-      if (i == 0 && h.track_per_scale_masks)
-        SubMinorUpdateAutoMask(h, int(cube_.n_images), st_.scale_masks[swp].get(), stream_);
-      if (i == 0 && h.config.track_components)
-        SubMinorUpdateComponentList(h, int(cube_.n_images), swp, stream_);
       // model += Transform(full model, scale)  (multiscale_algorithm.cc:442-460)
       if (S[swp].scale != 0.0f)
         conv_.ConvolveWith(scratch_.get(), width_, height_, ScaleSpectrum(swp), cube_.model.p[i], width_,
@@ -805,15 +867,20 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
         SubMinorAddModelTo(h, int(i), cube_.model.p[i], stream_);
     }
     h.launches += padded.TakeLaunchCount() + conv_.TakeLaunchCount();
+    // the corrected residuals of every channel, for the joined peak search of all ranks
+    ShareImagePlanes(cube_.residual.p);
 
     ActivateScales(swp);
     FindActiveScaleConvolvedMaxima(false);
     if (!SelectMaximumScale(swp)) {
+      ShareImagePlanes(cube_.model.p);
+      Sync();
       result.iteration_number = h.iteration_number;
       result.another_iteration_required = 0;
       return result;
     }
   }
+  ShareImagePlanes(cube_.model.p);
 
   const bool max_iter_reached = h.iteration_number >= set.max_iterations;
   const bool negative_reached =

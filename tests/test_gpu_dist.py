@@ -91,3 +91,21 @@ def test_two_ranks_facets_sharded(torch_cuda):
                           "29519", os.path.join(HERE, "dist_facets_check.py")],
                          capture_output=True, text=True, timeout=900)
     assert "FACETS-OK 2" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_channel_sharded_multiscale_single_rank(torch_cuda):
+    """world = 1 with a distributed context: the channel-sharded code path must change nothing."""
+    out = subprocess.run([sys.executable, os.path.join(HERE, "dist_multiscale_check.py")],
+                         capture_output=True, text=True, timeout=900)
+    assert "MS-DIST-OK 1" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_two_ranks_channel_sharded_multiscale(torch_cuda):
+    torch = torch_cuda
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run tests/dist_multiscale_check.py under torchrun with gpurun --gpus 2)")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                          "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",
+                          "29521", os.path.join(HERE, "dist_multiscale_check.py")],
+                         capture_output=True, text=True, timeout=900)
+    assert "MS-DIST-OK 2" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
