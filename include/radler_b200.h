@@ -221,6 +221,18 @@ rdl_status rdl_parallel_execute_major_iteration(rdl_handle* h, uint64_t grid_wid
                                                 float* const* residual, float* const* model,
                                                 const float* const* psfs, void* stream,
                                                 rdl_result* out);
+/* The same with direction-dependent PSFs (ParallelDeconvolution::ExecuteMajorIteration's
+ * psf_images[dd][channel] + psf_offsets, parallel_deconvolution.cc:494-503): psfs holds
+ * n_dd * n_channels planes ordered [dd][channel], each psf_width x psf_height (not larger than
+ * the image), psf_offset_x/y[n_dd] the pixel each PSF set was made for. Every facet uses the set
+ * NearestPsfIndex picks for its centre (:34-55, :163), resized to the facet like
+ * aocommon::Image::Resize (:329); a 1 x 1 grid uses the set nearest to the image centre, padded to
+ * the image size (:518-546). */
+rdl_status rdl_parallel_execute_major_iteration_dd(
+    rdl_handle* h, uint64_t grid_width, uint64_t grid_height, const rdl_cube_desc* cube,
+    float* const* residual, float* const* model, const float* const* psfs, uint64_t n_dd,
+    uint64_t psf_width, uint64_t psf_height, const int64_t* psf_offset_x,
+    const int64_t* psf_offset_y, void* stream, rdl_result* out);
 /* SubImage of the last facet run (parallel_deconvolution.h:22-35) */
 typedef struct {
   uint64_t x, y, width, height;

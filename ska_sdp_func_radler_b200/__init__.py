@@ -96,7 +96,8 @@ EXPORTED_SYMBOLS = [
     "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs",
-    "rdl_parallel_execute_major_iteration", "rdl_parallel_facet_count", "rdl_parallel_facet_get",
+    "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
+    "rdl_parallel_facet_count", "rdl_parallel_facet_get",
     "rdl_parallel_timing",
     "rdl_facet_dividing_path", "rdl_facet_flood_area", "rdl_facet_bounding_mask", "rdl_facet_grid",
     "rdl_dist_unique_id", "rdl_dist_init", "rdl_dist_set_row_band", "rdl_dist_set_row_blocks",
@@ -385,7 +386,6 @@ class DeconvolutionAlgorithm:
     def minor_iteration_count(self) -> int: return lib().rdl_minor_iteration_count(self._h)
     @property
     def kernel_launch_count(self) -> int: return lib().rdl_kernel_launch_count(self._h)
-    @property
     def reference_convolutions(self) -> dict:
         """{(width, height): count} of the Convolve calls the reference makes for the last call."""
         f = lib().rdl_reference_convolutions
@@ -395,6 +395,7 @@ class DeconvolutionAlgorithm:
         n = f(self._h, buf.ctypes.data, 64)
         return {(int(buf[3 * i]), int(buf[3 * i + 1])): int(buf[3 * i + 2]) for i in range(min(n, 64))}
 
+    @property
     def scale_count(self) -> int: return lib().rdl_scale_count(self._h)
 
     def scale_infos(self):
@@ -459,15 +460,36 @@ class DeconvolutionAlgorithm:
 
     # -- facets: ParallelDeconvolution (parallel_deconvolution.cc:494-654) ----------------
     def parallel_execute_major_iteration(self, grid_width: int, grid_height: int, cube: Cube,
-                                         residual, model, psfs, stream=None) -> Result:
+                                         residual, model, psfs, stream=None,
+                                         psf_offsets=None) -> Result:
+        """psf_offsets [(x, y)]: direction-dependent PSFs, psfs = [n_dd, n_channels, ph, pw]."""
         n = cube.width * cube.height
         rt, s0 = _plane_pointers(residual, cube.n_images, n)
         mt, s1 = _plane_pointers(model, cube.n_images, n)
+        out = _Result()
+        if psf_offsets is not None:
+            n_dd, n_c, ph, pw = psfs.shape
+            assert n_c == cube.n_channels and n_dd == len(psf_offsets)
+            flat = psfs.reshape(n_dd * n_c, ph, pw)
+            pt, s2 = _plane_pointers(flat, n_dd * n_c, ph * pw)
+            if not (s0 == s1 == s2):
+                raise ValueError("residual, model and psfs must live in the same memory space")
+            ox = np.ascontiguousarray([o[0] for o in psf_offsets], np.int64)
+            oy = np.ascontiguousarray([o[1] for o in psf_offsets], np.int64)
+            d = cube.desc(s0)
+            f = lib().rdl_parallel_execute_major_iteration_dd
+            f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(_CubeDesc), C.c_void_p,
+                          C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
+                          C.c_void_p, C.c_void_p, C.POINTER(_Result)]
+            self._check(f(self._h, grid_width, grid_height, C.byref(d), rt, mt, pt, n_dd, pw, ph,
+                          ox.ctypes.data, oy.ctypes.data, stream, C.byref(out)))
+            return Result(out.starting_peak_value if out.has_starting_peak else None,
+                          out.final_peak_value, bool(out.another_iteration_required),
+                          bool(out.is_diverging), out.iteration_number)
         pt, s2 = _plane_pointers(psfs, cube.n_channels, n)
         if not (s0 == s1 == s2):
             raise ValueError("residual, model and psfs must live in the same memory space")
         d = cube.desc(s0)
-        out = _Result()
         self._check(lib().rdl_parallel_execute_major_iteration(
             self._h, grid_width, grid_height, C.byref(d), rt, mt, pt, stream, C.byref(out)))
         return Result(out.starting_peak_value if out.has_starting_peak else None,

@@ -434,13 +434,23 @@ rdl_status rdl_scale_mask_get(const rdl_handle* h, uint64_t i, uint8_t* out) {
 }
 
 namespace {
+struct DdPsfArgs {
+  uint64_t n_dd = 0, width = 0, height = 0;
+  const int64_t* offset_x = nullptr;
+  const int64_t* offset_y = nullptr;
+};
+
 // grid_width = 0: the algorithm itself; otherwise ParallelDeconvolution over a facet grid
 rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* residual,
                        float* const* model, const float* const* psfs, void* stream_v,
-                       rdl_result* out, uint64_t grid_width, uint64_t grid_height) {
+                       rdl_result* out, uint64_t grid_width, uint64_t grid_height,
+                       const DdPsfArgs& dd = DdPsfArgs()) {
   if (!h || !out) return RDL_ERR_INVALID_ARGUMENT;
   return Guard(h, [&] {
     CheckCube(c);
+    if (dd.n_dd != 0 && (dd.width == 0 || dd.height == 0 || dd.width > c->width ||
+                         dd.height > c->height || !dd.offset_x || !dd.offset_y))
+      throw std::invalid_argument("direction-dependent PSFs need a size within the image and offsets");
     if (!residual || !model || !psfs) throw std::invalid_argument("null image table");
     const bool sharded = h->dist.band_set;
     const uint64_t frame_height = sharded ? h->dist.global_height : c->height;
@@ -469,8 +479,10 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
     if (host) {
       h->stage_residual.Reserve(cube.n_images * n);
       h->stage_model.Reserve(cube.n_images * n);
-      const size_t psf_n = cube.width * frame_height, psf_bytes = psf_n * sizeof(float);
-      h->stage_psf.Reserve(cube.n_channels * psf_n);
+      const size_t n_psf_planes = dd.n_dd ? dd.n_dd * cube.n_channels : cube.n_channels;
+      const size_t psf_n = dd.n_dd ? dd.width * dd.height : cube.width * frame_height;
+      const size_t psf_bytes = psf_n * sizeof(float);
+      h->stage_psf.Reserve(n_psf_planes * psf_n);
       for (size_t i = 0; i != cube.n_images; ++i) {
         cube.residual.p[i] = h->stage_residual.get() + i * n;
         cube.model.p[i] = h->stage_model.get() + i * n;
@@ -482,24 +494,37 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
       // the PSFs do not change between the major iterations of a run (radler.cc:175-268 passes the
       // same psf_images every time): with rdl_set_psfs_constant they cross PCIe once
       bool staged = h->psfs_constant && h->staged_psf_pixels == psf_n &&
-                    h->staged_psf_ptrs.size() == cube.n_channels;
-      for (size_t i = 0; staged && i != cube.n_channels; ++i) staged = h->staged_psf_ptrs[i] == psfs[i];
-      for (size_t i = 0; i != cube.n_channels; ++i) {
+                    h->staged_psf_ptrs.size() == n_psf_planes;
+      for (size_t i = 0; staged && i != n_psf_planes; ++i) staged = h->staged_psf_ptrs[i] == psfs[i];
+      for (size_t i = 0; i != n_psf_planes; ++i) {
         float* dst = h->stage_psf.get() + i * psf_n;
         if (!staged) {
           PinPlane(h, psfs[i], psf_bytes);
           RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], psf_bytes, cudaMemcpyHostToDevice, stream));
         }
-        cube.psf.p[i] = dst;
+        if (dd.n_dd)
+          cube.dd_psfs.push_back(dst);
+        else
+          cube.psf.p[i] = dst;
       }
-      h->staged_psf_ptrs.assign(psfs, psfs + cube.n_channels);
+      h->staged_psf_ptrs.assign(psfs, psfs + n_psf_planes);
       h->staged_psf_pixels = psf_n;
     } else {
       for (size_t i = 0; i != cube.n_images; ++i) {
         cube.residual.p[i] = residual[i];
         cube.model.p[i] = model[i];
       }
-      for (size_t i = 0; i != cube.n_channels; ++i) cube.psf.p[i] = psfs[i];
+      if (dd.n_dd)
+        cube.dd_psfs.assign(psfs, psfs + dd.n_dd * cube.n_channels);
+      else
+        for (size_t i = 0; i != cube.n_channels; ++i) cube.psf.p[i] = psfs[i];
+    }
+    if (dd.n_dd) {
+      cube.n_dd = dd.n_dd;
+      cube.psf_width = dd.width;
+      cube.psf_height = dd.height;
+      cube.psf_offset_x.assign(dd.offset_x, dd.offset_x + dd.n_dd);
+      cube.psf_offset_y.assign(dd.offset_y, dd.offset_y + dd.n_dd);
     }
     SetVec(cube);
     rdl_result r{};
@@ -538,6 +563,21 @@ rdl_status rdl_parallel_execute_major_iteration(rdl_handle* h, uint64_t grid_wid
                                                 rdl_result* out) {
   if (grid_width == 0 || grid_height == 0) return RDL_ERR_INVALID_ARGUMENT;
   return ExecuteImpl(h, c, residual, model, psfs, stream_v, out, grid_width, grid_height);
+}
+
+rdl_status rdl_parallel_execute_major_iteration_dd(
+    rdl_handle* h, uint64_t grid_width, uint64_t grid_height, const rdl_cube_desc* c,
+    float* const* residual, float* const* model, const float* const* psfs, uint64_t n_dd,
+    uint64_t psf_width, uint64_t psf_height, const int64_t* psf_offset_x,
+    const int64_t* psf_offset_y, void* stream_v, rdl_result* out) {
+  if (grid_width == 0 || grid_height == 0 || n_dd == 0) return RDL_ERR_INVALID_ARGUMENT;
+  DdPsfArgs dd;
+  dd.n_dd = n_dd;
+  dd.width = psf_width;
+  dd.height = psf_height;
+  dd.offset_x = psf_offset_x;
+  dd.offset_y = psf_offset_y;
+  return ExecuteImpl(h, c, residual, model, psfs, stream_v, out, grid_width, grid_height, dd);
 }
 
 // ---- facet geometry (host only; math/dijkstra_splitter.h) -----------------------------------

@@ -21,6 +21,7 @@ struct Facet {  // parallel_deconvolution.h:22-35 (SubImage)
   std::vector<uint8_t> boundary_mask;  // pixels this facet owns
   double peak = 0.0;
   bool reached_major_threshold = false;
+  size_t psf_index = 0;  // NearestPsfIndex of the facet centre (direction-dependent PSFs)
 };
 
 // Marks with 1.0 the cheapest top-to-bottom (vertical) / left-to-right (horizontal) path of

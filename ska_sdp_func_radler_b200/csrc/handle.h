@@ -78,6 +78,11 @@ struct DeviceCube {
   bool squared_joins = false;
   PtrTable residual{}, model{};
   ConstPtrTable psf{};  // per channel
+  // direction-dependent PSFs of a facet run (parallel_deconvolution.cc:34-55): n_dd sets of
+  // n_channels planes ([dd][channel]) of psf_width x psf_height, with their positions
+  std::vector<const float*> dd_psfs;
+  size_t n_dd = 0, psf_width = 0, psf_height = 0;
+  std::vector<int64_t> psf_offset_x, psf_offset_y;
   int vec = 1;          // 4 when width % 4 == 0 and all pointers are 16-byte aligned
   size_t PsfIndex(size_t image) const { return image / n_pol; }
   size_t Pixels() const { return width * height; }

@@ -142,6 +142,35 @@ rdl_result RunAlgorithm(rdl_handle& a, DeviceCube& cube, cudaStream_t stream) {
   }
 }
 
+// aocommon::Image::Resize: dst (w x h) from src (sw x sh), per dimension centred Trim or Untrim
+// with start = (outer - inner) / 2
+__global__ void ResizeKernel(float* dst, size_t w, size_t h, const float* src, size_t sw, size_t sh) {
+  const size_t mw = min(w, sw), mh = min(h, sh);
+  const size_t dx0 = (w - mw) / 2, dy0 = (h - mh) / 2, sx0 = (sw - mw) / 2, sy0 = (sh - mh) / 2;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < w * h;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const size_t y = i / w, x = i - y * w;
+    const bool in = x >= dx0 && x < dx0 + mw && y >= dy0 && y < dy0 + mh;
+    dst[i] = in ? src[(y - dy0 + sy0) * sw + (x - dx0 + sx0)] : 0.0f;
+  }
+}
+
+// NearestPsfIndex (parallel_deconvolution.cc:34-55): the first PSF set with the smallest squared
+// distance to (x, y); 0 without direction-dependent PSFs
+size_t NearestPsfIndex(const DeviceCube& cube, size_t x, size_t y) {
+  size_t best = 0;
+  uint64_t best_distance = 0;
+  for (size_t i = 0; i != cube.n_dd; ++i) {
+    const int64_t dx = cube.psf_offset_x[i] - int64_t(x), dy = cube.psf_offset_y[i] - int64_t(y);
+    const uint64_t d = uint64_t(dx * dx) + uint64_t(dy * dy);
+    if (i == 0 || d < best_distance) {
+      best = i;
+      best_distance = d;
+    }
+  }
+  return best;
+}
+
 // RunSubImage (parallel_deconvolution.cc:294-492) for one facet.
 void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
               double major_iteration_threshold, bool find_peak_only, cudaStream_t stream) {
@@ -172,13 +201,14 @@ void RunFacet(rdl_handle& h, ParallelState& st, Facet& f, DeviceCube& cube,
   // the model as it was, to undo a diverging facet
   RDL_CUDA(cudaMemcpyAsync(st.sub_model_start.get(), st.sub_model.get(),
                            cube.n_images * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-  // psf_image.Resize(sub width, sub height): centred crop (a facet is never larger than the frame)
-  const size_t px = (W - w) / 2, py = (cube.height - fh) / 2;
+  // psf_image.Resize(sub width, sub height) of the PSF set of this facet (:329): per dimension a
+  // centred crop when the PSF is larger than the facet, centred zero padding when it is smaller
   for (size_t c = 0; c != cube.n_channels; ++c) {
     float* dst = st.sub_psf.get() + c * n;
-    RDL_CUDA(cudaMemcpy2DAsync(dst, w * sizeof(float), cube.psf.p[c] + py * W + px,
-                               W * sizeof(float), w * sizeof(float), fh, cudaMemcpyDeviceToDevice,
-                               stream));
+    const float* src = cube.n_dd ? cube.dd_psfs[f.psf_index * cube.n_channels + c] : cube.psf.p[c];
+    const size_t pw = cube.n_dd ? cube.psf_width : W, ph = cube.n_dd ? cube.psf_height : cube.height;
+    ResizeKernel<<<GridFor(n), kThreads, 0, stream>>>(dst, w, fh, src, pw, ph);
+    ++h.launches;
     sub.psf.p[c] = dst;
   }
   sub.vec = (w % 4 == 0) ? 4 : 1;  // the sub buffers are cudaMalloc-aligned, planes are n floats
@@ -410,6 +440,20 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
         throw std::runtime_error(a.error);
       a.synced_rms = h.rms_generation;
     }
+    if (cube.n_dd) {
+      // the PSF set nearest to the image centre, padded to the image size (:518-546)
+      const size_t index = NearestPsfIndex(cube, cube.width / 2, cube.height / 2);
+      const size_t A = cube.Pixels();
+      st.sub_psf.Reserve(cube.n_channels * A);
+      for (size_t c = 0; c != cube.n_channels; ++c) {
+        float* dst = st.sub_psf.get() + c * A;
+        ResizeKernel<<<GridFor(A), kThreads, 0, stream>>>(dst, cube.width, cube.height,
+                                                          cube.dd_psfs[index * cube.n_channels + c],
+                                                          cube.psf_width, cube.psf_height);
+        ++h.launches;
+        cube.psf.p[c] = dst;
+      }
+    }
     const rdl_result r = RunAlgorithm(a, cube, stream);
     h.launches += a.launches;
     a.launches = 0;
@@ -458,6 +502,8 @@ rdl_result RunParallel(rdl_handle& h, DeviceCube& cube, size_t grid_width, size_
   st.facets = MakeFacets(integrated.data(), W, H,
                          h.mask_host.empty() ? nullptr : h.mask_host.data(), grid_width,
                          grid_height, &sharing);
+  for (Facet& f : st.facets)  // :163
+    f.psf_index = NearestPsfIndex(cube, f.x + f.width / 2, f.y + f.height / 2);
   st.geometry_ms = MsSince(geometry_start);
   std::vector<float>().swap(integrated);
 

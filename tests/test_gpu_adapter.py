@@ -77,7 +77,8 @@ def test_generic_clean_facets_through_the_reference_parallel_deconvolution(adapt
     pair = run_pair(adapter, "generic", res, psfs, calls=2, mask=mask, weights=weights,
                     frequencies=freqs, use_sub_minor_optimization=False, grid=grid, threads=1,
                     max_iterations=200, major_loop_gain=0.7, fit_terms=2)
-    assert pair[0][3] > 20
+    # (the iteration counter read back is the first facet's; that facet may have nothing to clean)
+    assert np.count_nonzero(pair[0][2]) > 20
     compare(pair, exact=True, peak=np.abs(res).max())
 
 

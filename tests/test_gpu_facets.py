@@ -167,3 +167,114 @@ def test_rms_image_and_mask_changed_between_parallel_calls(rdl, oracle, torch_cu
         assert np.float32(g.final_peak_value) == np.float32(w.final_peak_value), k
         assert np.array_equal(d_res.cpu().numpy(), r_res), k
         assert np.array_equal(d_model.cpu().numpy(), r_model), k
+
+
+# ---- direction-dependent PSFs (parallel_deconvolution.cc:34-55, :163, :329, :518-546) -----------
+def _psf_rectangular(size, w, h):
+    psf = np.zeros((size, size), np.float32)
+    c = size // 2
+    psf[c - w:c + w + 1, c - h:c + h + 1] = 1.0
+    return psf
+
+
+def _psf_cross(size, w, h):
+    psf = np.zeros((size, size), np.float32)
+    c = size // 2
+    psf[c - w:c + w + 1, c] = 1.0
+    psf[c, c - h:c + h + 1] = 1.0
+    return psf
+
+
+def _dd_fixture():
+    """python/test/test_psf.py:74-189: a 90 x 90 image, 9 differently shaped 30 x 30 PSFs on a
+    3 x 3 grid, one unit point source near the centre of every cell."""
+    image_size, psf_size = 90, 30
+    centres = [(i * 30 + 15, k * 30 + 15) for i in range(3) for k in range(3)]
+    w1, w2, w3 = 2, 4, 8
+    psfs = [_psf_rectangular(psf_size, w2, w2), _psf_cross(psf_size, w2, w2),
+            _psf_cross(psf_size, w1, w3), _psf_rectangular(psf_size, w2, 0),
+            _psf_cross(psf_size, w3, w1), _psf_rectangular(psf_size, w2, w1),
+            _psf_rectangular(psf_size, 0, w2), _psf_rectangular(psf_size, 0, 0),
+            _psf_rectangular(psf_size, w1, w2)]
+    rng = np.random.RandomState(10)
+    residual = np.zeros((1, image_size, image_size), np.float32)
+    sources = []
+    for (cx, cy) in centres:
+        off = rng.randint(-4, 4)
+        sources.append((cx + off, cy + off))
+        residual[0, cx + off, cy + off] = 1.0
+    return residual, np.stack(psfs)[:, None], centres, sources
+
+
+def test_direction_dependent_psfs_nearest_selection(rdl, oracle, torch_cuda):
+    """The reference's own DD-PSF test (python/test/test_psf.py:74-225) through the C ABI: one
+    iteration per facet with gain 1 removes every point source with the PSF of ITS cell; checked
+    against the shapes (the reference's check_values) and against the reference's own
+    ParallelDeconvolution sources, bit for bit."""
+    residual, psfs, centres, sources = _dd_fixture()
+    n = residual.shape[-1]
+    # the work table lists the centres as (x, y) = (first, second) coordinate of the numpy test
+    offsets = [(c[0], c[1]) for c in centres]
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    alg.apply(max_iterations=1, minor_loop_gain=1.0, major_loop_gain=1.0, clean_border_ratio=0.0)
+    g_res, g_model = residual.copy(), np.zeros_like(residual)
+    alg.parallel_execute_major_iteration(3, 3, rdl.Cube(n, n), g_res, g_model,
+                                         np.ascontiguousarray(psfs), psf_offsets=offsets)
+    if oracle.ref_lib() is not None:
+        ref = oracle.Reference("generic", n, n, 1, use_sub_minor_optimization=False, grid=(3, 3),
+                               threads=1, max_iterations=1, minor_loop_gain=1.0, major_loop_gain=1.0)
+        r_res, r_model = residual.copy(), np.zeros_like(residual)
+        ref.execute(r_res, r_model, psfs, psf_offsets=offsets)
+        assert np.array_equal(g_res, r_res) and np.array_equal(g_model, r_model)
+    # which PSF each source must have been cleaned with: offsets are (x, y), images are [y, x]
+    for k, (sx, sy) in enumerate(sources):
+        # the set whose offset (x, y) is nearest to the facet holding pixel [row sx, column sy]
+        d = [(ox - sy) ** 2 + (oy - sx) ** 2 for (ox, oy) in offsets]
+        psf = psfs[int(np.argmin(d)), 0]
+        c = psf.shape[0] // 2
+        sub = g_res[0, sx - 5:sx + 5, sy - 5:sy + 5] + psf[c - 5:c + 5, c - 5:c + 5]
+        assert sub[5, 5] == pytest.approx(1.0, rel=1e-5)
+        sub[5, 5] = 0
+        assert np.abs(sub).max() < 1e-6, k
+    assert np.abs(g_model).sum() == pytest.approx(9.0)
+
+
+@pytest.mark.parametrize("grid", [(1, 1), (2, 2), (5, 5)])
+def test_direction_dependent_psfs_match_reference_sources(rdl, oracle, torch_cuda, grid):
+    """25 direction-dependent PSFs smaller than the image (cpp/test/test_divergence.cc:26-142 uses
+    a 5 x 5 PSF grid over 5 x 5 facets): per-facet NearestPsfIndex + Resize, and the padded PSF of
+    the single-algorithm run, against the reference's own sources over two major iterations."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, psf_n, c = 200, 64, 2
+    res, full_psfs, weights, _ = hogbom_case(n, c)
+    rng = np.random.default_rng(9)
+    offsets, psfs = [], []
+    lo = (n - psf_n) // 2
+    for i in range(5):
+        for k in range(5):
+            offsets.append((k * 40 + 20, i * 40 + 20))
+            scale = np.float32(1.0 + 0.1 * rng.standard_normal())
+            p = full_psfs[:, lo:lo + psf_n, lo:lo + psf_n] * scale
+            p[:, psf_n // 2, psf_n // 2] = 1.0
+            psfs.append(p)
+    psfs = np.ascontiguousarray(np.stack(psfs))  # [25, c, 64, 64]
+    kw = dict(max_iterations=300, minor_loop_gain=0.1, major_loop_gain=0.7, clean_border_ratio=0.0)
+    ref = oracle.Reference("generic", n, n, c, weights=weights, use_sub_minor_optimization=False,
+                           grid=grid, threads=1, **kw)
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    alg.apply(**kw)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, n, n), device="cuda")
+    d_psf = torch.from_numpy(psfs).cuda()
+    cube = rdl.Cube(n, n, c, 1, weights)
+    for call in range(2):
+        w = ref.execute(r_res, r_model, psfs, psf_offsets=offsets)
+        g = alg.parallel_execute_major_iteration(grid[0], grid[1], cube, d_res, d_model, d_psf,
+                                                 psf_offsets=offsets)
+        assert g.another_iteration_required == w.another_iteration_required, call
+        assert np.float32(g.final_peak_value) == np.float32(w.final_peak_value), call
+        assert np.array_equal(d_res.cpu().numpy(), r_res), call
+        assert np.array_equal(d_model.cpu().numpy(), r_model), call
+    assert ref.iteration_number > 10
