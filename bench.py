@@ -593,6 +593,21 @@ def run_ours(args):
             del un_alg
             # end to end through host buffers (pinned; PSFs uploaded on every call)
             ms["e2e"] = multiscale_e2e(ms_alg, ms_cube, ms_res0, ms_psfs, barrier, 1)
+            # major iterations 2..n of a run: the PSFs are the ones of the first (radler.cc:175-268),
+            # so with rdl_set_psfs_constant(1) what the call derives from them alone is kept
+            ms_alg.set_psfs_constant(True)
+            k_total, k_r, _, _ = run_multiscale_device(rdl, ms_alg, ms_cube, ms_res0, ms_psfs, 2, 1,
+                                                       barrier, stream)
+            k_e2e = multiscale_e2e(ms_alg, ms_cube, ms_res0, ms_psfs, barrier, 1)
+            ms_alg.set_psfs_constant(False)
+            ms["psfs_constant"] = {
+                "ms_per_major_iteration": k_total / 2, "e2e_ms_per_step": k_e2e["ms_per_step"],
+                "components_cleaned": int(k_r.iteration_number),
+                "e2e_h2d_bytes_per_step": 2 * c * n * n * 4,
+                "note": "the same major iteration from the second call of a run on, with "
+                        "rdl_set_psfs_constant(1): scale-convolved / twice-convolved PSFs, kernel "
+                        "spectra and PSF peaks kept from the previous call, PSF planes not uploaded "
+                        "again; results bit-identical (tests/test_gpu_multiscale.py)"}
             if not args.no_cpu:
                 cores = os.cpu_count() or 1
                 own, mkl, best, per_size = price_reference_convolutions(conv_counts, cores)

@@ -143,11 +143,19 @@ rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t 
 rdl_status rdl_set_spectral_fitter(rdl_handle* h, int32_t mode, uint64_t n_terms,
                                    const double* frequencies, const float* weights,
                                    uint64_t n_channels, uint64_t n_polarizations);
+/* NOT SUPPORTED (no entry point): SetSpectrallyForcedImages (deconvolution_algorithm.h:155-158,
+ * the forced-terms fit: RDL_FIT modes other than polynomial are rejected with
+ * RDL_ERR_UNSUPPORTED) and SetLogReceiver (:113-115; the library does not log -- status codes
+ * and rdl_last_error carry what the reference would report). */
 
-/* RDL_MEM_HOST calls only. Radler passes the same psf_images to every major iteration of a run
- * (radler.cc:175-268): with rdl_set_psfs_constant(h, 1) the caller promises that PSF planes
- * passed again under the same pointers are unchanged, and they are copied to the device once
- * instead of on every call. Any other pointer, plane size or plane count uploads again. */
+/* Radler passes the same psf_images to every major iteration of a run (radler.cc:175-268): with
+ * rdl_set_psfs_constant(h, 1) the caller promises that PSF planes passed again under the same
+ * pointers are unchanged. RDL_MEM_HOST calls then copy them to the device once instead of on
+ * every call (any other pointer, plane size or plane count uploads again), and a multiscale
+ * handle (either memory space) keeps what it derives from the PSFs alone -- scale-convolved and
+ * twice-convolved PSFs, kernel spectra, PSF peaks -- from one call to the next, which holds HBM
+ * between calls (K4: up to ~60 GB) until the option is cleared or the handle destroyed. Results
+ * are the same bits with and without the option. */
 rdl_status rdl_set_psfs_constant(rdl_handle* h, int32_t constant);
 /* RDL_MEM_HOST calls only. With rdl_set_pin_host_buffers(h, 1) the caller's residual / model /
  * PSF planes are registered (cudaHostRegister) the first time they are seen, so that pageable

@@ -270,7 +270,8 @@ RDL_SETTER(rdl_set_divergence_limit(rdl_handle* h, float v), h->settings.diverge
 RDL_SETTER(rdl_set_iteration_number(rdl_handle* h, uint64_t n), h->iteration_number = n)
 RDL_SETTER(rdl_set_trace_capacity(rdl_handle* h, uint64_t n), h->trace_capacity = n)
 RDL_SETTER(rdl_set_psfs_constant(rdl_handle* h, int32_t v),
-           (h->psfs_constant = v != 0, h->staged_psf_ptrs.clear()))
+           (h->psfs_constant = v != 0, h->staged_psf_ptrs.clear(),
+            h->ms ? MultiScaleInvalidatePsfCache(*h->ms) : void()))
 RDL_SETTER(rdl_set_pin_host_buffers(rdl_handle* h, int32_t v),
            (h->pin_host_buffers = v != 0, (v == 0 ? UnpinAll(h) : void())))
 RDL_SETTER(rdl_set_auto_mask_mode(rdl_handle* h, int32_t track, int32_t use),
@@ -496,6 +497,8 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
       bool staged = h->psfs_constant && h->staged_psf_pixels == psf_n &&
                     h->staged_psf_ptrs.size() == n_psf_planes;
       for (size_t i = 0; staged && i != n_psf_planes; ++i) staged = h->staged_psf_ptrs[i] == psfs[i];
+      // new pixels under the same staging addresses: what multiscale kept of the old ones goes
+      if (!staged && h->ms) MultiScaleInvalidatePsfCache(*h->ms);
       for (size_t i = 0; i != n_psf_planes; ++i) {
         float* dst = h->stage_psf.get() + i * psf_n;
         if (!staged) {

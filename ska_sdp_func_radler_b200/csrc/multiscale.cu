@@ -162,12 +162,43 @@ __global__ void SumSquaresKernel(const float* image, size_t n, double* out) {
 
 }  // namespace
 
+// Everything a call derives from the PSFs alone: kept from one ExecuteMajorIteration to the next
+// when the caller has promised that the PSFs do not change (rdl_set_psfs_constant; radler.cc:175-268
+// passes the same psf_images in every major iteration, and the reference recomputes all of this
+// each time). The key is what the contents depend on besides the PSF pixels.
+struct MultiScalePsfCache {
+  bool valid = false;
+  std::vector<const float*> psf_ptrs;
+  std::vector<float> weights, scale_sizes;
+  size_t width = 0, height = 0, n_pol = 0;
+  int shape = 0;
+  double padding = 0.0;
+  bool sharded = false;
+  std::vector<float> psf_peak;  // of the integrated PSF per scale
+  DeviceBuffer<float> integrated_psf;
+  std::vector<DeviceBuffer<float>> convolved_psfs;  // [psf][scale], empty for scale 0
+  std::vector<DeviceBuffer<float2>> scale_spectra;
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float2>> psf_spectra;
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float>> twice;  // [psf, scale]
+  void Clear() {
+    valid = false;
+    psf_peak.clear();
+    convolved_psfs.clear();
+    scale_spectra.clear();
+    psf_spectra.clear();
+    twice.clear();
+  }
+};
+
 class MultiScaleState {
  public:
   std::vector<rdl_scale_info> scales;
   std::vector<DeviceBuffer<uint8_t>> scale_masks;
   size_t mask_pixels = 0;
+  MultiScalePsfCache psf_cache;  // not cloned: a clone fills its own
 };
+
+void MultiScaleInvalidatePsfCache(MultiScaleState& s) { s.psf_cache.Clear(); }
 
 std::shared_ptr<MultiScaleState> CloneMultiScaleState(const MultiScaleState& src, cudaStream_t stream) {
   auto dst = std::make_shared<MultiScaleState>();
@@ -272,7 +303,10 @@ class MultiScaleRun {
  public:
   MultiScaleRun(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
       : h_(h), cube_(cube), stream_(stream), st_(*h.ms), width_(cube.width), height_(cube.height),
-        n_(cube.Pixels()), conv_(GetConvolver(h, cube.width, cube.height)) {
+        n_(cube.Pixels()), conv_(GetConvolver(h, cube.width, cube.height)), cache_(h.ms->psf_cache),
+        integrated_psf_(cache_.integrated_psf), convolved_psfs_(cache_.convolved_psfs),
+        scale_spectra_(cache_.scale_spectra), psf_spectra_(cache_.psf_spectra),
+        twice_cache_(cache_.twice) {
     if (h.dist.comm && h.dist.world > 1 && !h.dist.band_set && cube.n_channels > 1) {
       sharded_ = true;
       world_ = h.dist.world;
@@ -328,17 +362,54 @@ class MultiScaleRun {
   MultiScaleState& st_;
   size_t width_, height_, n_;
   FftConvolver& conv_;
-  DeviceBuffer<float> integrated_, scratch_, integrated_psf_;
-  std::vector<DeviceBuffer<float>> convolved_psfs_;  // [psf][scale], empty for scale 0
+  // PSF-derived planes and spectra live in the state's cache (see MultiScalePsfCache)
+  MultiScalePsfCache& cache_;
+  bool cache_hit_ = false;
+  bool CacheMatches() const;
+  void StampCache();
+  DeviceBuffer<float> integrated_, scratch_;
+  DeviceBuffer<float>& integrated_psf_;
+  std::vector<DeviceBuffer<float>>& convolved_psfs_;
   std::vector<const float*> base_psf_;               // scale-0 "convolved" PSF of each slot
   std::vector<DeviceBuffer<float>> twice_convolved_, individual_convolved_;
-  std::vector<DeviceBuffer<float2>> scale_spectra_;
-  std::map<std::pair<size_t, size_t>, DeviceBuffer<float2>> psf_spectra_;
-  std::map<std::pair<size_t, size_t>, DeviceBuffer<float>> twice_cache_;  // [psf, scale]
+  std::vector<DeviceBuffer<float2>>& scale_spectra_;
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float2>>& psf_spectra_;
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float>>& twice_cache_;
   DeviceBuffer<float2> psf_spectrum_tmp_;
   DeviceBuffer<float> shape_dev_, values_dev_;  // loop without the sub-minor optimisation
   DeviceBuffer<double> sumsq_;
 };
+
+bool MultiScaleRun::CacheMatches() const {
+  const MultiScalePsfCache& c = cache_;
+  if (!c.valid || !h_.psfs_constant) return false;
+  if (c.width != width_ || c.height != height_ || c.n_pol != cube_.n_pol ||
+      c.shape != h_.config.ms_shape || c.padding != double(h_.config.ms_convolution_padding) ||
+      c.sharded != sharded_ || c.weights != cube_.weights)
+    return false;
+  if (c.psf_ptrs.size() != cube_.n_channels || c.scale_sizes.size() != st_.scales.size() ||
+      c.psf_peak.size() != st_.scales.size())
+    return false;
+  for (size_t p = 0; p != cube_.n_channels; ++p)
+    if (c.psf_ptrs[p] != cube_.psf.p[p]) return false;
+  for (size_t si = 0; si != st_.scales.size(); ++si)
+    if (c.scale_sizes[si] != st_.scales[si].scale) return false;
+  return true;
+}
+
+void MultiScaleRun::StampCache() {
+  MultiScalePsfCache& c = cache_;
+  c.width = width_;
+  c.height = height_;
+  c.n_pol = cube_.n_pol;
+  c.shape = h_.config.ms_shape;
+  c.padding = double(h_.config.ms_convolution_padding);
+  c.sharded = sharded_;
+  c.weights = cube_.weights;
+  c.psf_ptrs.assign(cube_.psf.p, cube_.psf.p + cube_.n_channels);
+  c.scale_sizes.clear();
+  for (const rdl_scale_info& e : st_.scales) c.scale_sizes.push_back(e.scale);
+}
 
 float MultiScaleRun::ReadPixel(const float* image, size_t index) {
   float v = 0.0f;
@@ -405,12 +476,15 @@ void MultiScaleRun::ConvolvePsfs(size_t slot, const float* psf, bool is_integrat
       // per-channel PSFs: only the owner of the channel ever uses its convolved PSFs
       if (!is_integrated && !MineChannel(slot)) continue;
       DeviceBuffer<float>& dst = convolved_psfs_[slot * n_scales + si];
-      dst.Reserve(n_);
-      conv_.ConvolveWith(psf, width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0, stream_);
+      if (!cache_hit_) {
+        dst.Reserve(n_);
+        conv_.ConvolveWith(psf, width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0, stream_);
+      }
       convolved = dst.get();
     }
     if (is_integrated) {
-      e.psf_peak = ReadPixel(convolved, width_ / 2 + (height_ / 2) * width_);
+      if (!cache_hit_) cache_.psf_peak[si] = ReadPixel(convolved, width_ / 2 + (height_ / 2) * width_);
+      e.psf_peak = cache_.psf_peak[si];
       double exp_term;
       if (e.scale == 0.0f || n_scales < 2)
         exp_term = 0.0;
@@ -700,13 +774,19 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
   size_t threshold_countdown = std::max<size_t>(8, n_scales * 3 / 2);
   integrated_.Resize(n_);
   scratch_.Resize(n_);
-  integrated_psf_.Resize(n_);
   const size_t n_psfs = cube_.n_channels;
-  convolved_psfs_.resize(n_psfs * n_scales);
+  cache_hit_ = CacheMatches();
+  if (!cache_hit_) {
+    cache_.Clear();
+    integrated_psf_.Resize(n_);
+    convolved_psfs_.resize(n_psfs * n_scales);
+    cache_.psf_peak.assign(n_scales, 0.0f);
+    StampCache();
+  }
   base_psf_.assign(n_psfs, nullptr);
 
   // GetIntegratedPsf (image_set.cc:499-530) + ConvolvePsfs
-  {
+  if (!cache_hit_) {
     ConstPtrTable t{};
     for (size_t p = 0; p != n_psfs; ++p) t.p[p] = cube_.psf.p[p];
     const bool aligned = cube_.vec == 4;
@@ -717,6 +797,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
   if (n_psfs > 1)
     for (size_t p = 0; p != n_psfs; ++p) ConvolvePsfs(p, cube_.psf.p[p], false);
   h.launches += conv_.TakeLaunchCount();
+  cache_.valid = h.psfs_constant;  // the lazily filled maps (spectra, twice-convolved) only grow
 
   FindActiveScaleConvolvedMaxima(true);
   rdl_result result{};
@@ -901,8 +982,18 @@ rdl_result RunMultiScale(rdl_handle& h, DeviceCube& cube, cudaStream_t stream) {
   h.trace_host.clear();
   h.minor_iterations = 0;
   h.reference_convolutions.clear();
-  MultiScaleRun run(h, cube, stream);
-  return run.Execute();
+  try {
+    MultiScaleRun run(h, cube, stream);
+    const rdl_result r = run.Execute();
+    if (!h.psfs_constant) {  // nothing is kept between calls: give the HBM back
+      h.ms->psf_cache.Clear();
+      h.ms->psf_cache.integrated_psf = DeviceBuffer<float>();
+    }
+    return r;
+  } catch (...) {
+    h.ms->psf_cache.Clear();
+    throw;
+  }
 }
 
 }  // namespace rdl

@@ -9,6 +9,8 @@
 namespace rdl {
 std::shared_ptr<MultiScaleState> CloneMultiScaleState(const MultiScaleState& src,
                                                       cudaStream_t stream);
+// drops what the state keeps of the PSFs (rdl_set_psfs_constant runs): call when PSF pixels change
+void MultiScaleInvalidatePsfCache(MultiScaleState& s);
 uint64_t MultiScaleScaleCount(const MultiScaleState& s);
 rdl_scale_info MultiScaleScaleInfo(const MultiScaleState& s, uint64_t i);
 void MultiScaleCopyScaleMask(const MultiScaleState& s, uint64_t i, uint8_t* out_host);

