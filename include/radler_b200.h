@@ -360,6 +360,20 @@ rdl_status rdl_iuwt_smooth(rdl_handle* h, const float* device_in, float* device_
 rdl_status rdl_iuwt_decompose(rdl_handle* h, const float* device_input, uint64_t width,
                               uint64_t height, int32_t n_scales, int32_t include_largest,
                               float* device_coefficients, void* stream);
+/* The same decomposition for callers that may not allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the
+ * reference. The two ping-pong planes that
+ * rdl_iuwt_decompose keeps in cudaMalloc'ed buffers of the handle are a file-scope device array
+ * of the library instead (8 MiB, held by every GPU that loads the library until exit); the call
+ * runs no cudaMalloc, cudaFree or allocating library routine. Limit: width * height <=
+ * RDL_STATIC_SCRATCH_MAX_PIXELS, larger images fail with RDL_ERR_INVALID_ARGUMENT and a message.
+ * All calls on a device share the array, which keeps the last call's contents (nothing here
+ * needs it cleared): calls that overlap on the GPU race, so serialise them. Results are the bits
+ * of rdl_iuwt_decompose. Asynchronous on `stream` like rdl_iuwt_decompose. */
+#define RDL_STATIC_SCRATCH_MAX_PIXELS (1u << 20)
+rdl_status rdl_iuwt_decompose_static(rdl_handle* h, const float* device_input, uint64_t width,
+                                     uint64_t height, int32_t n_scales, int32_t include_largest,
+                                     float* device_coefficients, void* stream);
 /* IuwtDecomposition::Decompose(x, x, false): the input aliased to the scratch image, which is
  * how IuwtDeconvolutionAlgorithm calls it (iuwt_deconvolution_algorithm.cc:344,385,685,780) and
  * which changes scale 0 (iuwt_decomposition.cc:19-26,58-61: a recursive row pass, and the

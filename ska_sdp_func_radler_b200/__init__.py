@@ -93,7 +93,7 @@ EXPORTED_SYMBOLS = [
     "rdl_scale_mask_get", "rdl_trace_size", "rdl_trace_get", "rdl_last_selected_count",
     "rdl_minor_iteration_count", "rdl_kernel_launch_count", "rdl_reference_convolutions", "rdl_execute_major_iteration",
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
-    "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
+    "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_static", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
@@ -192,6 +192,7 @@ def lib():
     L.rdl_dist_finalize.argtypes = [vp]
     L.rdl_iuwt_smooth.argtypes = [vp, vp, vp, u64, u64, C.c_int32, C.c_int32, vp]
     L.rdl_iuwt_decompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
+    L.rdl_iuwt_decompose_static.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp]
     L.rdl_iuwt_recompose.argtypes = [vp, vp, u64, u64, C.c_int32, C.c_int32, vp, vp, vp]
     i32, f32, pu64 = C.c_int32, C.c_float, C.POINTER(u64)
     L.rdl_iuwt_select_structures.argtypes = [vp, vp, vp, u64, u64, i32, C.POINTER(f32), i32, i32,
@@ -600,6 +601,16 @@ class DeconvolutionAlgorithm:
         assert coefficients.shape[0] >= n_scales + (1 if include_largest else 0)
         self._check(lib().rdl_iuwt_decompose(self._h, image.data_ptr(), w, h, n_scales,
                                              int(include_largest), coefficients.data_ptr(), stream))
+
+    def iuwt_decompose_static(self, image, coefficients, n_scales, include_largest=True,
+                              stream=None):
+        """iuwt_decompose without device allocations: the scratch planes are a static device
+        array of the library (width * height <= 2**20; calls must not overlap on the GPU)."""
+        h, w = image.shape
+        assert coefficients.shape[0] >= n_scales + (1 if include_largest else 0)
+        self._check(lib().rdl_iuwt_decompose_static(self._h, image.data_ptr(), w, h, n_scales,
+                                                    int(include_largest), coefficients.data_ptr(),
+                                                    stream))
 
     def iuwt_decompose_aliased(self, x, coefficients, n_scales, stream=None):
         """IuwtDecomposition::Decompose(x, x, false) (input aliased to the scratch image)."""
