@@ -97,6 +97,13 @@ struct HogbomParams {
 void LaunchHogbomStep(const HogbomParams& p, CleanState* state, bool first, int vec,
                       cudaStream_t stream);
 
+// The whole single-GPU loop in one cooperative launch, for cubes that stay in L2 (K1, facets).
+// scratch: HogbomPersistentScratchBytes() of device memory (barrier words + candidate slots).
+// Returns false when a cooperative launch is not possible on this device.
+size_t HogbomPersistentScratchBytes();
+bool LaunchHogbomPersistent(const HogbomParams& p, CleanState* state, void* scratch, int vec,
+                            cudaStream_t stream);
+
 // Joined control step of the row-sharded loop: picks the best of the gathered candidates and
 // runs the same loop control as the single-GPU path (every rank redundantly, bit-identically).
 // frame row of local row yl / local row of frame row y (false when another rank owns it)

@@ -34,6 +34,7 @@
 // (including its wrap-around), evaluated at FFT round-off like every other convolution here.
 #include "fft.cuh"
 #include "fft_fast_plan.h"
+#include "fft_spec.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -886,10 +887,15 @@ struct FftConvolver::Impl {
   size_t row_smem = 0, smem1 = 0, smem2 = 0;
   // register-radix engine (2-3-5-7-smooth frames)
   bool use_fast = false;
+  bool use_spec = true;  // radix-specialised instances (fft_spec.cu) where one exists; RDL_FFT_SPEC=0: off
   fast::HostFastPlan fp;
   fast::RowPlan frp{};
   fast::ColPlan fcp{};
-  DeviceBuffer<float2> f_tw_row, f_tw_row2, f_split, f_tw_h1, f_tw_h;
+  DeviceBuffer<float2> f_tw_row, f_tw_row2, f_split, f_tw_h1, f_tw_h, f_tw_wa, f_tw_wb;
+  // whole columns in shared memory (one kernel instead of strided + block + strided) where the
+  // plan allows and fft_spec.cu has an instance; RDL_FFT_WHOLE=0: off
+  bool use_whole = false;
+  fast::WholePlan fwp{};
   DeviceBuffer<uint4> f_pairs;
   int band_tiles = 0;  // column tiles per band of the column passes (L2-resident bands)
 
@@ -1029,6 +1035,20 @@ FftConvolver::FftConvolver(size_t width, size_t height, size_t content_width, si
       if (band_mb > 0.0 && d.fcp.H2 > 1 && tile_mb * tiles > 1.5 * band_mb)
         d.band_tiles = std::max(1, int(band_mb / tile_mb));
       d.use_fast = true;
+      if (const char* e = std::getenv("RDL_FFT_SPEC")) d.use_spec = std::atoi(e) != 0;
+      // off unless asked for: measured SLOWER than strided + block + strided on B200 (8192^2 1.00 vs
+      // 0.79 ms, 9216^2 1.31 vs 0.90, 4096^2 0.224 vs 0.182; profiles/r02_fft_bench_whole_column.jsonl):
+      // one CTA per SM with load, five shared-memory passes and store in series loses more than
+      // the 16 B/px it saves
+      bool want_whole = false;
+      if (const char* e = std::getenv("RDL_FFT_WHOLE")) want_whole = d.use_spec && std::atoi(e) != 0;
+      if (want_whole && d.fp.whole_ok &&
+          fast::HasWholeColumnSpec(d.fp.whole.ra, d.fp.whole.rb, d.fp.whole.rc)) {
+        upload(d.f_tw_wa, d.fp.tw_whole_a);
+        upload(d.f_tw_wb, d.fp.tw_whole_b);
+        d.fwp = d.fp.MakeWholePlan(d.f_tw_wa.get(), d.f_tw_wb.get());
+        d.use_whole = true;
+      }
       d.work.Resize(size_t(d.H) * d.pitch);
       RDL_CUDA(cudaMemset(d.work.get(), 0, size_t(d.H) * d.pitch * sizeof(float2)));
       return;
@@ -1153,7 +1173,9 @@ void FftConvolver::ForwardRows(const float* src, size_t sw, size_t sh, size_t ox
     io.spec = d.work.get();
     io.pitch = d.pitch;
     const int grid = (int(sh) + d.fp.rows_per_cta - 1) / d.fp.rows_per_cta;
-    FastRowForwardKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, io);
+    if (!d.use_spec ||
+        !fast::LaunchRowForwardSpec(d.frp, io, grid, d.fp.row_threads, d.fp.row_smem, stream))
+      FastRowForwardKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, io);
     ++launches_;
     return;
   }
@@ -1197,17 +1219,28 @@ void FftConvolver::MakeKernelSpectrum(const float* kernel_image, float2* spectru
     fast::ColIo io = d.MakeFastColIo();
     io.kspec_out = spectrum_out;
     io.scale = float(1.0 / (4.0 * double(d.W) * double(d.H)));
+    if (d.use_whole) {
+      fast::LaunchWholeColumnSpec(false, d.fwp, io, d.pitch / d.fwp.tw, d.fp.whole_threads,
+                                  d.fp.whole_smem, stream);
+      ++launches_;
+      return;
+    }
     const int tiles = d.pitch / kTileCols;
     const int groups = (d.fcp.H1 + fast::kStridedRows - 1) / fast::kStridedRows;
     for (int t0 = 0; t0 < tiles; t0 += d.band_tiles) {
       const int nt = std::min(d.band_tiles, tiles - t0);
       if (d.fcp.H2 > 1) {
-        FastColumnStridedKernel<false><<<dim3(nt, groups), fast::kTile * fast::kStridedRows, 0, stream>>>(
-            d.fcp, io, t0);
+        if (!d.use_spec ||
+            !fast::LaunchColumnStridedSpec(false, d.fcp, io, t0, dim3(nt, groups),
+                                           fast::kTile * fast::kStridedRows, stream))
+          FastColumnStridedKernel<false><<<dim3(nt, groups), fast::kTile * fast::kStridedRows, 0, stream>>>(
+              d.fcp, io, t0);
         ++launches_;
       }
-      FastColumnBlockKernel<false><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
-          d.fcp, io, t0);
+      if (!d.use_spec || !fast::LaunchColumnBlockSpec(false, d.fcp, io, t0, dim3(nt, d.fcp.H2),
+                                                      d.fp.block_threads, d.fp.block_smem, stream))
+        FastColumnBlockKernel<false><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
+            d.fcp, io, t0);
       ++launches_;
     }
     return;
@@ -1293,19 +1326,30 @@ void FftConvolver::ConvolveAt(const float* src, size_t sw, size_t sh, size_t sox
     const int tiles = d.pitch / kTileCols;
     const int groups = (d.fcp.H1 + fast::kStridedRows - 1) / fast::kStridedRows;
     const int strided_threads = fast::kTile * fast::kStridedRows;
-    for (int t0 = 0; t0 < tiles; t0 += d.band_tiles) {
+    for (int t0 = 0; t0 < tiles && !d.use_whole; t0 += d.band_tiles) {
       const int nt = std::min(d.band_tiles, tiles - t0);
       if (d.fcp.H2 > 1) {
-        FastColumnStridedKernel<false><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
+        if (!d.use_spec || !fast::LaunchColumnStridedSpec(false, d.fcp, io, t0, dim3(nt, groups),
+                                                          strided_threads, stream))
+          FastColumnStridedKernel<false><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
         ++launches_;
       }
-      FastColumnBlockKernel<true><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
-          d.fcp, io, t0);
+      if (!d.use_spec || !fast::LaunchColumnBlockSpec(true, d.fcp, io, t0, dim3(nt, d.fcp.H2),
+                                                      d.fp.block_threads, d.fp.block_smem, stream))
+        FastColumnBlockKernel<true><<<dim3(nt, d.fcp.H2), d.fp.block_threads, d.fp.block_smem, stream>>>(
+            d.fcp, io, t0);
       ++launches_;
       if (d.fcp.H2 > 1) {
-        FastColumnStridedKernel<true><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
+        if (!d.use_spec || !fast::LaunchColumnStridedSpec(true, d.fcp, io, t0, dim3(nt, groups),
+                                                          strided_threads, stream))
+          FastColumnStridedKernel<true><<<dim3(nt, groups), strided_threads, 0, stream>>>(d.fcp, io, t0);
         ++launches_;
       }
+    }
+    if (d.use_whole) {
+      fast::LaunchWholeColumnSpec(true, d.fwp, io, d.pitch / d.fwp.tw, d.fp.whole_threads,
+                                  d.fp.whole_smem, stream);
+      ++launches_;
     }
     fast::RowIo rio{};
     rio.dst = dst;
@@ -1317,7 +1361,9 @@ void FftConvolver::ConvolveAt(const float* src, size_t sw, size_t sh, size_t sox
     rio.pitch = d.pitch;
     rio.mode = mode;
     const int grid = (int(dh) + d.fp.rows_per_cta - 1) / d.fp.rows_per_cta;
-    FastRowInverseKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, rio);
+    if (!d.use_spec ||
+        !fast::LaunchRowInverseSpec(d.frp, rio, grid, d.fp.row_threads, d.fp.row_smem, stream))
+      FastRowInverseKernel<<<grid, d.fp.row_threads, d.fp.row_smem, stream>>>(d.frp, rio);
     ++launches_;
     return;
   }

@@ -611,6 +611,142 @@ RDL_HD void ColumnBlockPassC(const ColPlan& p, const ColIo& io, const float2* sm
   }
 }
 
+// ---- whole columns in shared memory -----------------------------------------------------------
+// The four-step scheme above moves the spectrum through HBM three times (strided, block,
+// strided). Where a column tile of the WHOLE height fits in shared memory -- tw = 4 columns up to
+// H ~ 6000, 2 columns up to H ~ 12000 -- one kernel does everything: H = ra * rb * rc forward
+// (decimation in frequency, three passes), product with the kernel spectrum, three inverse
+// passes. A 2-column tile touches 16 bytes per spectrum row, so neighbouring tiles share
+// sectors and DRAM bursts: they run on different SMs at about the same time and meet in L2.
+// Frequency k = ka + ra * kb + ra * rb * kc sits at position pos = (ka * rb + kb) * rc + kc, in
+// shared memory as well as in the kernel spectrum (which the forward-only flavour writes in that
+// order). One padding row per rc positions keeps the last pass (one thread per rc-run) off a
+// single bank.
+struct WholePlan {
+  int H, ra, rb, rc, l2;  // l2 = rb * rc
+  int tw;                 // tile width in columns (2 or 4)
+  // twa[(q - 1) * l2 + j] = exp(-2 pi i j q / H), twb[(q - 1) * rc + j] = exp(-2 pi i j q / l2)
+  const float2* twa;
+  const float2* twb;
+};
+
+RDL_HD int WholeSlot(const WholePlan& p, int pos) { return pos + pos / p.rc; }
+RDL_HD size_t WholeSmemElements(const WholePlan& p) { return size_t(p.H + p.H / p.rc) * p.tw; }
+
+template <int RA>
+RDL_HD void WholePassA(const WholePlan& p, const ColIo& io, float2* smem, int c0, int tid, int n_threads) {
+  const int tasks = p.l2 * p.tw;
+  for (int idx = tid; idx < tasks; idx += n_threads) {
+    const int j = idx / p.tw, c = idx - j * p.tw;
+    const float2* g = io.spec + size_t(j) * io.pitch + c0 + c;
+    float2 v[RA];
+    StaticFor<RA>([&](auto q) {
+      const int y = j + p.l2 * q;
+      v[q] = (y >= io.y0 && y < io.y1) ? g[size_t(p.l2) * q * io.pitch] : make_float2(0.0f, 0.0f);
+    });
+    Dft<RA, false>::Run(v);
+    smem[WholeSlot(p, j) * p.tw + c] = v[0];
+    StaticFor<RA - 1>([&](auto qq) {
+      constexpr int q = decltype(qq)::value + 1;
+      smem[WholeSlot(p, j + p.l2 * q) * p.tw + c] = CMulF(v[q], RDL_LDG(p.twa + (q - 1) * p.l2 + j));
+    });
+  }
+}
+
+template <int RB, bool INV>
+RDL_HD void WholePassB(const WholePlan& p, float2* smem, int tid, int n_threads) {
+  const int per_block = p.rc * p.tw;
+  const int tasks = p.ra * per_block;
+  for (int idx = tid; idx < tasks; idx += n_threads) {
+    const int ka = idx / per_block, t = idx - ka * per_block;
+    const int j = t / p.tw, c = t - j * p.tw;
+    const int base = ka * p.l2 + j;
+    float2 v[RB];
+    if (!INV) {
+      StaticFor<RB>([&](auto q) { v[q] = smem[WholeSlot(p, base + p.rc * q) * p.tw + c]; });
+      Dft<RB, false>::Run(v);
+      smem[WholeSlot(p, base) * p.tw + c] = v[0];
+      StaticFor<RB - 1>([&](auto qq) {
+        constexpr int q = decltype(qq)::value + 1;
+        smem[WholeSlot(p, base + p.rc * q) * p.tw + c] = CMulF(v[q], RDL_LDG(p.twb + (q - 1) * p.rc + j));
+      });
+    } else {
+      v[0] = smem[WholeSlot(p, base) * p.tw + c];
+      StaticFor<RB - 1>([&](auto qq) {
+        constexpr int q = decltype(qq)::value + 1;
+        v[q] = CMulConj(smem[WholeSlot(p, base + p.rc * q) * p.tw + c], RDL_LDG(p.twb + (q - 1) * p.rc + j));
+      });
+      Dft<RB, true>::Run(v);
+      StaticFor<RB>([&](auto q) { smem[WholeSlot(p, base + p.rc * q) * p.tw + c] = v[q]; });
+    }
+  }
+}
+
+// last forward pass, product (or the scaled kernel spectrum out), first inverse pass
+template <int RC, bool CONVOLVE>
+RDL_HD void WholePassC(const WholePlan& p, const ColIo& io, float2* smem, int c0, int tid, int n_threads) {
+  const int tasks = p.ra * p.rb * p.tw;
+  for (int idx = tid; idx < tasks; idx += n_threads) {
+    const int b = idx / p.tw, c = idx - b * p.tw;  // b = ka * rb + kb
+    const int pos0 = b * p.rc;
+    float2* s = smem + WholeSlot(p, pos0) * p.tw + c;  // the rc positions of a run share one pad offset
+    const size_t g0 = size_t(pos0) * io.pitch + c0 + c;
+    float2 v[RC], k[RC];
+    if (CONVOLVE) StaticFor<RC>([&](auto q) { k[q] = RDL_LDG(io.kspec + g0 + size_t(q) * io.pitch); });
+    StaticFor<RC>([&](auto q) { v[q] = s[q * p.tw]; });
+    Dft<RC, false>::Run(v);
+    if (!CONVOLVE) {
+      StaticFor<RC>([&](auto q) {
+        io.kspec_out[g0 + size_t(q) * io.pitch] = make_float2(io.scale * v[q].x, io.scale * v[q].y);
+      });
+      continue;
+    }
+    StaticFor<RC>([&](auto q) { v[q] = CMulF(v[q], k[q]); });
+    Dft<RC, true>::Run(v);
+    StaticFor<RC>([&](auto q) { s[q * p.tw] = v[q]; });
+  }
+}
+
+template <int RA>
+RDL_HD void WholePassD(const WholePlan& p, const ColIo& io, const float2* smem, int c0, int tid,
+                       int n_threads) {
+  const int tasks = p.l2 * p.tw;
+  for (int idx = tid; idx < tasks; idx += n_threads) {
+    const int j = idx / p.tw, c = idx - j * p.tw;
+    float2 v[RA];
+    v[0] = smem[WholeSlot(p, j) * p.tw + c];
+    StaticFor<RA - 1>([&](auto qq) {
+      constexpr int q = decltype(qq)::value + 1;
+      v[q] = CMulConj(smem[WholeSlot(p, j + p.l2 * q) * p.tw + c], RDL_LDG(p.twa + (q - 1) * p.l2 + j));
+    });
+    Dft<RA, true>::Run(v);
+    float2* g = io.spec + size_t(j) * io.pitch + c0 + c;
+    StaticFor<RA>([&](auto q) {
+      const int y = j + p.l2 * q;
+      if (y >= io.out_y0 && y < io.out_y1) g[size_t(p.l2) * q * io.pitch] = v[q];
+    });
+  }
+}
+
+// all phases of one tile, thread by thread (the kernels in fft_spec.cu put a __syncthreads()
+// between the phases; the CPU emulation runs phase after phase over all threads)
+template <int PHASE, int RA, int RB, int RC, bool CONVOLVE>
+RDL_HD void WholeColumnPhase(const WholePlan& p, const ColIo& io, float2* smem, int tile, int tid,
+                             int n_threads) {
+  const int c0 = tile * p.tw;
+  if (PHASE == 0) {
+    WholePassA<RA>(p, io, smem, c0, tid, n_threads);
+  } else if (PHASE == 1) {
+    WholePassB<RB, false>(p, smem, tid, n_threads);
+  } else if (PHASE == 2) {
+    WholePassC<RC, CONVOLVE>(p, io, smem, c0, tid, n_threads);
+  } else if (PHASE == 3) {
+    WholePassB<RB, true>(p, smem, tid, n_threads);
+  } else {
+    WholePassD<RA>(p, io, smem, c0, tid, n_threads);
+  }
+}
+
 // ---- kernel bodies by phase (a __syncthreads() separates the phases of one CTA) -----------------
 RDL_HD int MinInt(int a, int b) { return a < b ? a : b; }
 

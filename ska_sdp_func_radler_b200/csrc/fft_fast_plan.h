@@ -122,6 +122,12 @@ struct HostFastPlan {
   size_t block_smem = 0;
   std::vector<float2> tw_row1, tw_row2, tw_split, tw_h1, tw_h;
   std::vector<uint4> pairs;
+  // whole columns in shared memory (WholePlan): radices of H, tile width, tables
+  bool whole_ok = false;
+  RowChoice whole;
+  int whole_tw = 0, whole_threads = 512;
+  size_t whole_smem = 0;
+  std::vector<float2> tw_whole_a, tw_whole_b;
 
   void Build(int width, int height) {
     ok = false;
@@ -166,6 +172,38 @@ struct HostFastPlan {
     block_smem = size_t(h1) * kTile * sizeof(float2);
     block_threads = std::clamp(RoundUp32(std::max(col.ra, col.rb) * kTile), 64, 256);
     ok = true;
+    // one kernel for the whole column transform where a 4- or 2-column tile of the full height
+    // fits in shared memory (three passes worth it from H = 2048 on)
+    whole = ChooseRowRadices(H);
+    whole_ok = false;
+    if (whole.ok && whole.ra > 1 && whole.rb > 1 && whole.rc > 1 && H >= 2048) {
+      for (int tw : {4, 2}) {
+        const size_t bytes = size_t(H + H / whole.rc) * tw * sizeof(float2);
+        if (bytes <= size_t(200) * 1024 && pitch % tw == 0) {
+          whole_tw = tw;
+          whole_smem = bytes;
+          whole_ok = true;
+          break;
+        }
+      }
+    }
+    if (whole_ok) {
+      tw_whole_a = stage_table(whole.ra, whole.rb * whole.rc, H);
+      tw_whole_b = stage_table(whole.rb, whole.rc, whole.rb * whole.rc);
+    }
+  }
+
+  WholePlan MakeWholePlan(const float2* d_twa, const float2* d_twb) const {
+    WholePlan p{};
+    p.H = H;
+    p.ra = whole.ra;
+    p.rb = whole.rb;
+    p.rc = whole.rc;
+    p.l2 = whole.rb * whole.rc;
+    p.tw = whole_tw;
+    p.twa = d_twa;
+    p.twb = d_twb;
+    return p;
   }
 
   RowPlan MakeRowPlan(const float2* d_tw1, const float2* d_tw2, const float2* d_split,

@@ -5,6 +5,7 @@
 // Path A (sub-minor optimisation) lives in subminor.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "handle.h"
 #include "subminor.cuh"
@@ -133,6 +134,30 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   host.p->iteration = h.iteration_number;
   RDL_CUDA(cudaMemcpyAsync(h.state.get(), host.p, sizeof(CleanState), cudaMemcpyHostToDevice,
                            stream));
+
+  // Cubes that stay in L2 together with their PSFs (K1, facets): the whole loop in one
+  // cooperative launch, no launch + last-CTA control per iteration (clean_kernels.cu).
+  // RDL_HOGBOM_PERSISTENT_MB moves the limit (0 switches the path off).
+  const char* env_mb = getenv("RDL_HOGBOM_PERSISTENT_MB");
+  const double limit_mb = env_mb ? atof(env_mb) : 40.0;
+  const double cube_mb = double(cube.n_images) * double(cube.Pixels()) * sizeof(float) / 1048576.0;
+  if (!sharded && cube_mb <= limit_mb) {
+    h.persist_scratch.Reserve(HogbomPersistentScratchBytes());
+    if (LaunchHogbomPersistent(p, h.state.get(), h.persist_scratch.get(), cube.vec, stream)) {
+      ++h.launches;
+      RDL_CUDA(cudaMemcpyAsync(host.p, h.state.get(), sizeof(CleanState), cudaMemcpyDeviceToHost,
+                               stream));
+      RDL_CUDA(cudaStreamSynchronize(stream));
+      const CleanState s = *host.p;
+      h.iteration_number = s.iteration;
+      h.trace_host.resize(s.n_trace);
+      if (s.n_trace)
+        RDL_CUDA(cudaMemcpyAsync(h.trace_host.data(), h.trace_dev.get(),
+                                 s.n_trace * sizeof(TraceEntry), cudaMemcpyDeviceToHost, stream));
+      RDL_CUDA(cudaStreamSynchronize(stream));
+      return FinishResult(h, s, iteration_at_start);
+    }
+  }
   step(true);
 
   // Batch size: about a millisecond of device work between polls.

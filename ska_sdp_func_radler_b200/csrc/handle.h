@@ -200,6 +200,7 @@ struct rdl_handle {
   // row-sharded multi-GPU loop (not cloned)
   rdl::DistContext dist;
   rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;
+  rdl::DeviceBuffer<unsigned char> persist_scratch;  // HogbomPersistentKernel: barrier + candidates
   rdl::ComponentList components;     // MultiScaleAlgorithm::component_list_ (track_components)
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone

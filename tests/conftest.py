@@ -33,3 +33,15 @@ def torch_cuda():
     import torch
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
     return torch
+
+
+@pytest.fixture(params=["persistent", "stepwise"])
+def hogbom_loop_flavour(request, monkeypatch):
+    """GenericClean path B has two drivers with the same arithmetic: one cooperative kernel for
+    cubes that stay in L2 (the default up to 40 MB) and one fused kernel launch per iteration.
+    Tests at small sizes run under both."""
+    if request.param == "stepwise":
+        monkeypatch.setenv("RDL_HOGBOM_PERSISTENT_MB", "0")
+    else:
+        monkeypatch.delenv("RDL_HOGBOM_PERSISTENT_MB", raising=False)
+    return request.param

@@ -15,10 +15,14 @@ using namespace rdl::fast;
 
 namespace {
 
+bool g_whole = false;  // column transforms through the whole-column kernel bodies where planned
+
 struct Engine {
   HostFastPlan hp;
   RowPlan rp;
   ColPlan cp;
+  WholePlan wp;
+  bool whole = false;
   std::vector<float2> work;
 
   bool Build(int W, int H) {
@@ -26,6 +30,9 @@ struct Engine {
     if (!hp.ok) return false;
     rp = hp.MakeRowPlan(hp.tw_row1.data(), hp.tw_row2.data(), hp.tw_split.data(), hp.pairs.data());
     cp = hp.MakeColPlan(hp.tw_h1.data(), hp.tw_h.data());
+    whole = g_whole && hp.whole_ok;
+    if (g_whole && !hp.whole_ok) return false;
+    if (whole) wp = hp.MakeWholePlan(hp.tw_whole_a.data(), hp.tw_whole_b.data());
     work.assign(size_t(H) * hp.pitch, make_float2(0.0f, 0.0f));
     return true;
   }
@@ -90,6 +97,27 @@ struct Engine {
       }
   }
 
+  // one tile after the other, phase by phase, every thread of the 512
+  template <bool CONVOLVE>
+  void Whole(const ColIo& io) {
+    const int tiles = hp.pitch / wp.tw, threads = hp.whole_threads;
+    std::vector<float2> smem(WholeSmemElements(wp));
+    for (int tile = 0; tile < tiles; ++tile) {
+      const int c0 = tile * wp.tw;
+      for (int t = 0; t < threads; ++t)
+        RDL_DISPATCH_RADIX(wp.ra, (WholePassA<kR>(wp, io, smem.data(), c0, t, threads)))
+      for (int t = 0; t < threads; ++t)
+        RDL_DISPATCH_RADIX(wp.rb, (WholePassB<kR, false>(wp, smem.data(), t, threads)))
+      for (int t = 0; t < threads; ++t)
+        RDL_DISPATCH_LAST_RADIX(wp.rc, (WholePassC<kR, CONVOLVE>(wp, io, smem.data(), c0, t, threads)))
+      if (!CONVOLVE) continue;
+      for (int t = 0; t < threads; ++t)
+        RDL_DISPATCH_RADIX(wp.rb, (WholePassB<kR, true>(wp, smem.data(), t, threads)))
+      for (int t = 0; t < threads; ++t)
+        RDL_DISPATCH_RADIX(wp.ra, (WholePassD<kR>(wp, io, smem.data(), c0, t, threads)))
+    }
+  }
+
   ColIo MakeIo() {
     ColIo io{};
     io.spec = work.data();
@@ -108,6 +136,10 @@ struct Engine {
     ColIo io = MakeIo();
     io.kspec_out = out.data();
     io.scale = float(1.0 / (4.0 * double(hp.W) * double(hp.H)));
+    if (whole) {
+      Whole<false>(io);
+      return;
+    }
     if (cp.H2 > 1) Strided<false>(io);
     Block<false>(io);
   }
@@ -121,9 +153,13 @@ struct Engine {
     io.y1 = soy + sh;
     io.out_y0 = doy;
     io.out_y1 = doy + dh;
-    if (cp.H2 > 1) Strided<false>(io);
-    Block<true>(io);
-    if (cp.H2 > 1) Strided<true>(io);
+    if (whole) {
+      Whole<true>(io);
+    } else {
+      if (cp.H2 > 1) Strided<false>(io);
+      Block<true>(io);
+      if (cp.H2 > 1) Strided<true>(io);
+    }
     RowInverse(dst, dw, dh, dox, doy, mode);
   }
 };
@@ -254,6 +290,11 @@ int Dump(int W, int H, int sw, int sh, int dw, int dh, int mode, unsigned seed, 
 
 int main(int argc, char** argv) {
   int failures = 0;
+  if (argc >= 2 && std::string(argv[1]) == "whole") {  // "whole dump ..." / "whole W H ..."
+    g_whole = true;
+    --argc;
+    ++argv;
+  }
   if (argc == 11 && std::string(argv[1]) == "dump")
     return Dump(std::atoi(argv[2]), std::atoi(argv[3]), std::atoi(argv[4]), std::atoi(argv[5]),
                 std::atoi(argv[6]), std::atoi(argv[7]), std::atoi(argv[8]), unsigned(std::atoi(argv[9])),

@@ -44,13 +44,34 @@ CASES = [
 ]
 
 
+# the whole-column kernel (H = ra * rb * rc in shared memory, 2 or 4 columns per tile): every
+# column height of the BASELINE frames and their paddings, partial source / destination rows
+WHOLE_CASES = [
+    (32, 2048, None, None, 0), (32, 2304, (32, 2048), (32, 2048), 1), (32, 4096, None, None, 0),
+    (32, 4536, None, None, 0), (32, 4608, (30, 4096), (30, 4096), 2), (32, 4704, None, None, 0),
+    (32, 4860, (32, 4096), (32, 4000), 1), (32, 8192, None, None, 0), (32, 9072, None, None, 0),
+    (32, 9216, (32, 8192), (32, 8192), 1), (32, 9408, (32, 8192), (32, 8192), 2),
+    (32, 9720, None, None, 0),
+]
+
+
 @pytest.mark.parametrize("w,h,src,dst,mode", CASES)
 def test_emulated_kernels_match_float64_fft(emulator, w, h, src, dst, mode):
+    _run_case(emulator, w, h, src, dst, mode, False)
+
+
+@pytest.mark.parametrize("w,h,src,dst,mode", WHOLE_CASES)
+def test_emulated_whole_column_kernel_matches_float64_fft(emulator, w, h, src, dst, mode):
+    _run_case(emulator, w, h, src, dst, mode, True)
+
+
+def _run_case(emulator, w, h, src, dst, mode, whole):
     sw, sh = src or (w, h)
     dw, dh = dst or (w, h)
     with tempfile.TemporaryDirectory() as tmp:
         path = os.path.join(tmp, "dump.bin")
-        r = subprocess.run([emulator, "dump", str(w), str(h), str(sw), str(sh), str(dw), str(dh),
+        r = subprocess.run([emulator] + (["whole"] if whole else []) +
+                           ["dump", str(w), str(h), str(sw), str(sh), str(dw), str(dh),
                             str(mode), str(w * 7 + h), path], capture_output=True, text=True)
         assert r.returncode == 0, r.stdout + r.stderr
         data = np.fromfile(path, np.float32)

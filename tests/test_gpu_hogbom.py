@@ -155,7 +155,7 @@ def _assert_same(o, o_imgs, g, g_imgs, alg):
 
 
 @pytest.mark.parametrize("shift", [(0, 0), (7, -11), (-9, 15), (-9, 23)])
-def test_path_b_point_source_fixture(rdl, oracle, torch_cuda, shift):
+def test_path_b_point_source_fixture(rdl, oracle, torch_cuda, hogbom_loop_flavour, shift):
     # cpp/test/test_radler.cc:98-172 through the CUDA path
     psf, res, src = plus_psf_fixture(*shift)
     st = dict(threshold=1e-8, max_iterations=1000, clean_border_ratio=0.0)
@@ -167,7 +167,7 @@ def test_path_b_point_source_fixture(rdl, oracle, torch_cuda, shift):
 
 @pytest.mark.parametrize("n,c,iters,device_resident", [(256, 1, 500, False), (250, 1, 300, True),
                                                        (512, 4, 400, True), (1024, 1, 2000, True)])
-def test_path_b_matches_oracle(rdl, oracle, torch_cuda, n, c, iters, device_resident):
+def test_path_b_matches_oracle(rdl, oracle, torch_cuda, hogbom_loop_flavour, n, c, iters, device_resident):
     res, psfs, weights, freqs = hogbom_case(n, c)
     st = dict(threshold=0.0, max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1)
     o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, weights, st,
@@ -176,7 +176,7 @@ def test_path_b_matches_oracle(rdl, oracle, torch_cuda, n, c, iters, device_resi
     _assert_same(o, oi, g, gi, alg)
 
 
-def test_path_b_variants(rdl, oracle, torch_cuda):
+def test_path_b_variants(rdl, oracle, torch_cuda, hogbom_loop_flavour):
     res, psfs, weights, freqs = hogbom_case(256, 3)
     rng = np.random.default_rng(2)
     mask = (rng.uniform(size=(256, 256)) < 0.5).astype(np.uint8)
@@ -195,7 +195,7 @@ def test_path_b_variants(rdl, oracle, torch_cuda):
     _assert_same(o, oi, g, gi, alg)
 
 
-def test_path_b_divergence(rdl, oracle, torch_cuda):
+def test_path_b_divergence(rdl, oracle, torch_cuda, hogbom_loop_flavour):
     # a PSF with peak -1.5 makes every subtraction grow the peak (test_divergence.cc idea)
     res, psfs, weights, _ = hogbom_case(128, 1)
     psfs = psfs * np.float32(-1.5)

@@ -73,7 +73,7 @@ def rel(a, b):
 # ---- RMS factor image ------------------------------------------------------------------------
 @pytest.mark.parametrize("sub_minor", [False, True])
 @pytest.mark.parametrize("n,c", [(256, 1), (200, 3)])
-def test_generic_clean_with_rms_factor(rdl, oracle, torch_cuda, sub_minor, n, c):
+def test_generic_clean_with_rms_factor(rdl, oracle, torch_cuda, hogbom_loop_flavour, sub_minor, n, c):
     res, psfs, weights, freqs = hogbom_case(n, c)
     rms = rms_image(n)
     rng = np.random.default_rng(4)
@@ -123,7 +123,8 @@ def test_multiscale_with_rms_factor(rdl, oracle, torch_cuda, fast):
 # ---- several polarisations in a loop -------------------------------------------------------------
 @pytest.mark.parametrize("sub_minor", [False, True])
 @pytest.mark.parametrize("pols,pol_norm", POLS)
-def test_generic_clean_multi_polarisation_loop(rdl, oracle, torch_cuda, sub_minor, pols, pol_norm):
+def test_generic_clean_multi_polarisation_loop(rdl, oracle, torch_cuda, hogbom_loop_flavour, sub_minor,
+                                               pols, pol_norm):
     n, c = 160, 3
     res, psfs, weights, freqs = pol_case(n, c, pols)
     n_pol = len(pols)
