@@ -252,7 +252,20 @@ def _is_torch(a) -> bool:
 
 
 def _plane_pointers(a, n: int, plane_elems: int):
-    """Pointer table (void*[n]) of the n image planes of `a` + its memory space."""
+    """Pointer table (void*[n]) of the n image planes of `a` + its memory space. `a` is one
+    contiguous [n, H, W] array / tensor, or a list of n separately allocated planes (what an
+    ImageSet of aocommon::Images is)."""
+    if isinstance(a, (list, tuple)):
+        if len(a) != n:
+            raise ValueError(f"expected {n} planes")
+        ptrs, spaces = [], set()
+        for plane in a:
+            t, space = _plane_pointers(plane, 1, plane_elems)
+            ptrs.append(t[0])
+            spaces.add(space)
+        if len(spaces) != 1:
+            raise ValueError("planes of one cube must live in one memory space")
+        return (C.c_void_p * n)(*ptrs), spaces.pop()
     if _is_torch(a):
         if not a.is_cuda:
             raise ValueError("torch tensors passed to radler_b200 must live on a CUDA device")

@@ -20,6 +20,17 @@ struct PinnedState {
   ~PinnedState() { cudaFreeHost(p); }
 };
 
+struct Events {
+  cudaEvent_t e[2] = {nullptr, nullptr};
+  Events() {
+    for (auto& v : e) RDL_CUDA(cudaEventCreateWithFlags(&v, cudaEventDisableTiming));
+  }
+  ~Events() {
+    for (auto& v : e)
+      if (v) cudaEventDestroy(v);
+  }
+};
+
 rdl_result FinishResult(const rdl_handle& h, const CleanState& s, uint64_t iteration_at_start) {
   // generic_clean.cc:75-88, 208-252
   rdl_result r{};
@@ -160,21 +171,56 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   }
   step(true);
 
-  // Batch size: about a millisecond of device work between polls.
-  // (identical on every rank of a sharded run: the ranks must issue the same number of exchanges)
+  // The host runs AHEAD of the device: a launch whose loop has ended returns at once (st->done),
+  // so batches are queued before it is known that they are needed -- two in flight, doubling from
+  // about a millisecond of work up to about 50 ms (64 launches when every step carries a collective) --
+  // and the control block of batch k is looked at while batch k + 1 runs. A host thread that is
+  // descheduled for tens of milliseconds (measured on shared hosts: whole steps 2-3x slower with
+  // a synchronisation every 8 launches) no longer idles the GPU; the price is at most one batch
+  // of empty launches after the loop ends. Batch sizes are a fixed schedule, identical on every
+  // rank of a sharded run (the ranks must issue the same number of exchanges).
   const double pixels = sharded ? double(width) * double(h.dist.global_height) / h.dist.world
                                 : double(cube.Pixels());
   const double bytes_per_iteration = 12.0 * double(cube.n_images) * pixels;
   const double t_iteration = std::max(bytes_per_iteration / 6.0e12, 3.0e-6);
-  const int batch = int(std::clamp(1.0e-3 / t_iteration, 8.0, 256.0));
-  for (;;) {
-    RDL_CUDA(cudaMemcpyAsync(host.p, h.state.get(), sizeof(CleanState), cudaMemcpyDeviceToHost,
-                             stream));
-    RDL_CUDA(cudaStreamSynchronize(stream));
-    if (host.p->done) break;
-    for (int b = 0; b != batch; ++b) step(false);
+  uint64_t batch = uint64_t(std::clamp(1.0e-3 / t_iteration, 8.0, 256.0));
+  // about 50 ms of queued work per batch (a queue of a thousand short launches measured slower
+  // per launch than one of a few hundred)
+  const uint64_t batch_cap =
+      sharded ? 64 : uint64_t(std::clamp(50.0e-3 / t_iteration, double(batch), 256.0));
+  // no more launches than iterations that can still happen
+  uint64_t budget = h.settings.max_iterations > h.iteration_number
+                        ? h.settings.max_iterations - h.iteration_number
+                        : 0;
+  PinnedState slots[2];
+  Events events;
+  auto issue = [&](int slot, uint64_t count) {
+    for (uint64_t b = 0; b != count; ++b) step(false);
     RDL_CUDA(cudaGetLastError());
+    RDL_CUDA(cudaMemcpyAsync(slots[slot].p, h.state.get(), sizeof(CleanState),
+                             cudaMemcpyDeviceToHost, stream));
+    RDL_CUDA(cudaEventRecord(events.e[slot], stream));
+  };
+  auto take = [&](uint64_t want) {
+    const uint64_t n = std::min(want, budget);
+    budget -= n;
+    return n;
+  };
+  int cur = 0;
+  issue(cur, take(batch));
+  for (;;) {
+    batch = std::min(batch * 2, batch_cap);
+    issue(cur ^ 1, take(batch));
+    RDL_CUDA(cudaEventSynchronize(events.e[cur]));
+    if (slots[cur].p->done) break;
+    cur ^= 1;
+    if (budget == 0) {  // everything that can happen is queued: the last copy tells
+      RDL_CUDA(cudaEventSynchronize(events.e[cur]));
+      break;
+    }
   }
+  RDL_CUDA(cudaStreamSynchronize(stream));  // drains what was queued ahead
+  *host.p = *slots[cur].p;
   const CleanState s = *host.p;
   h.iteration_number = s.iteration;
   h.trace_host.resize(s.n_trace);

@@ -123,15 +123,21 @@ def test_k5_facets_8x8_reduced_frame(rdl, oracle, torch_cuda, sub_minor):
     if not sub_minor:
         assert np.array_equal(g_res, r_res) and np.array_equal(g_model, r_model)
         return
-    # Path A: CorrectResidualDirty goes through FFTs, so the residual of a facet carries round-off
-    # that differs between the two FFT implementations; the next sub-minor pass selects the pixels
-    # above a threshold, and a pixel within that round-off of the threshold enters one run and
-    # not the other (the analogue of the multiscale near-tie). Over 64 facets x 2 calls this can
-    # happen: allow a handful of displaced components, everything else within 1e-5.
+    # Path A: CorrectResidualDirty goes through FFTs, so after the first call the two residuals
+    # differ by FFT round-off (3e-7 of the peak). The dividers of the next call are minimum-cost
+    # paths through THAT image: where two routes tie to within the round-off, a divider passes one
+    # pixel further left or right, and that pixel belongs to the neighbouring facet, whose version
+    # of it (its own components' sidelobes subtracted) differs. Seen here: ONE pixel of 2^20,
+    # 1.7e-3 of the peak, same models; each facet alone agrees three ways (oracle, reference
+    # sources, device) within 2e-7 (tools/k5_debug2.py). Allow a few such pixels, everything else
+    # within 1e-5.
+    diff = np.abs(g_res - r_res)
+    flipped = int(np.count_nonzero(diff > 1e-5 * peak))
     moved = int(np.count_nonzero(np.abs(g_model - r_model) > 1e-5 * peak))
-    _record("k5_path_a_8x8.json", {"model_pixels_differing": moved,
-                                   "residual_max_rel": float(np.abs(g_res - r_res).max() / peak),
+    _record("k5_path_a_8x8.json", {"residual_pixels_beyond_1e-5": flipped,
+                                   "model_pixels_differing": moved,
+                                   "residual_max_rel": float(diff.max() / peak),
                                    "components": int(np.count_nonzero(r_model))})
-    assert moved <= 4
-    tol = (1e-5 if moved == 0 else 5e-3) * peak
-    assert np.abs(g_res - r_res).max() <= tol
+    assert moved == 0
+    assert flipped <= 8
+    assert diff.max() <= 5e-3 * peak

@@ -24,6 +24,19 @@ alg = rdl.GenericClean(use_sub_minor_optimization=False)
 alg.apply(max_iterations=iters, clean_border_ratio=0.0, minor_loop_gain=0.1, threshold=0.0,
           trace_capacity=iters)
 res, model = res0.clone(), torch.zeros_like(res0)
+# PROBE_PAD_KB: planes at a stride of n * n * 4 + pad bytes instead of back to back (power-of-two
+# plane strides put pixel (x, y) of every image at the same offset modulo any power of two)
+pad = int(os.environ.get("PROBE_PAD_KB", "0")) * 256  # floats
+if pad:
+    def spread(t):
+        big = torch.empty((c, n * n + pad), device=dev)
+        planes = [big[i, :n * n].view(n, n) for i in range(c)]
+        for i in range(c):
+            planes[i].copy_(t[i])
+        return planes, big
+    res, _keep1 = spread(res)
+    model, _keep2 = spread(model)
+    psfs, _keep3 = spread(psfs)
 stream = torch.cuda.current_stream().cuda_stream
 
 
@@ -70,4 +83,4 @@ print(json.dumps({"size": n, "channels": c, "batch": os.environ.get("RDL_HOGBOM_
                   "achieved_gbs": alg_bytes / (ms * 1e-3) / 1e9,
                   "frac": alg_bytes / (ms * 1e-3) / 1e9 / peak, "ms_per_step": per_step,
                   "persistent_mb": os.environ.get("RDL_HOGBOM_PERSISTENT_MB", "default"),
-                  "resident": os.environ.get("RDL_HOGBOM_RESIDENT", "default"), "clocks": clk}))
+                  "resident": os.environ.get("RDL_HOGBOM_RESIDENT", "default"), "plane_pad_kb": os.environ.get("PROBE_PAD_KB", "0"), "clocks": clk}))
