@@ -468,12 +468,18 @@ def run_ours(args):
         e2e_s = float(tmax[0])
     plane = n * n * 4
     band = n * rows * 4
+    # one GPU: the model planes stay on the host (the call returns a component log and applies it
+    # there); row-sharded runs still move them
+    model_planes = 0 if world == 1 else 1
+    log_bytes = (c + 1) * 4 * iters if world == 1 else 0
     e2e = {"value": e2e_iters / e2e_s, "unit": "iterations/s",
-           "h2d_bytes_per_step": (2 * c * band + c * plane) * world,
-           "d2h_bytes_per_step": 2 * c * band * world,
+           "h2d_bytes_per_step": ((1 + model_planes) * c * band + c * plane) * world,
+           "d2h_bytes_per_step": (1 + model_planes) * c * band * world + log_bytes,
            "ms_per_step": e2e_s / e2e_steps * 1e3,
-           "note": "rdl_execute_major_iteration with RDL_MEM_HOST pinned buffers: residual, model "
-                   "and PSFs copied to HBM, residual and model copied back, every step"}
+           "note": "rdl_execute_major_iteration with RDL_MEM_HOST pinned buffers, every step: "
+                   "residual and PSFs copied to HBM, residual copied back; the model planes stay on "
+                   "the host (one GPU: the call logs its components on the device and applies them "
+                   "to the caller's planes, same fp32 adds; row-sharded: model planes copied both ways)"}
 
     def time_e2e(r_, m_, p_, steps):
         alg.set_iteration_number(0)
@@ -495,7 +501,7 @@ def run_ours(args):
     alg.set_psfs_constant(True)
     v_cached, ms_cached = time_e2e(np_res, np_model, np_psf, e2e_steps)
     e2e["psfs_cached"] = {"value": v_cached, "ms_per_step": ms_cached,
-                          "h2d_bytes_per_step": 2 * c * band * world,
+                          "h2d_bytes_per_step": (1 + model_planes) * c * band * world,
                           "note": "same call with rdl_set_psfs_constant(1): the PSF planes cross "
                                   "PCIe on the first call only"}
     # what the C++ adapter really passes: pageable aocommon::Image buffers

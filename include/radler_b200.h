@@ -209,7 +209,12 @@ uint64_t rdl_reference_convolutions(const rdl_handle* h, uint64_t* triples, uint
  * are updated in place; psfs[c] (c < n_channels) are read-only, same size as the
  * images. With RDL_MEM_HOST the images are staged to HBM and copied back inside
  * the call; with RDL_MEM_DEVICE they are used where they are. `stream` is a
- * cudaStream_t (NULL = the handle's own stream). */
+ * cudaStream_t (NULL = the handle's own stream).
+ * RDL_MEM_HOST + GenericClean without the sub-minor loop (one GPU, no facets): the model planes
+ * are neither uploaded nor downloaded -- the call records its components (pixel, one value per
+ * image) on the device and adds them to the caller's planes before it returns, in order and with
+ * the same fp32 additions, so the result is the same bits (used while the component log stays
+ * below 256 MB, i.e. max_iterations - iteration_number below ~4 M for 16 images). */
 rdl_status rdl_execute_major_iteration(rdl_handle* h, const rdl_cube_desc* cube,
                                        float* const* residual, float* const* model,
                                        const float* const* psfs, void* stream, rdl_result* out);

@@ -260,14 +260,18 @@ __device__ void HogbomControl(const HogbomParams& p, CleanState* st, float* s_va
       for (int i = lane; i < p.n_images; i += 32, ++slot_i) s_values[i] = fitted[slot_i];
       __syncwarp();
     }
+    const unsigned long long k_log = iteration - p.log_first_iteration;
     for (int i = lane; i < p.n_images; i += 32) {
       const float v = __fmul_rn(s_values[i], p.gain);
-      if (owner) {
+      if (p.log_values) {
+        p.log_values[k_log * p.n_images + i] = v;
+      } else if (owner) {
         float* m = p.model.p[i] + local_index;
         *m = __fadd_rn(*m, v);
       }
       st->factors[i] = v;
     }
+    if (p.log_values && lane == 0) p.log_index[k_log] = index;
     if (lane == 0 && st->n_trace < p.trace_capacity) {
       p.trace[st->n_trace] = TraceEntry{uint32_t(iteration), 0u, uint32_t(x), uint32_t(y), val};
       st->n_trace = st->n_trace + 1;
@@ -646,10 +650,16 @@ __global__ void __launch_bounds__(kPersistThreads, 1)
         const float f = __fmul_rn(s_values[i], p.gain);
         s_values[i] = f;
         if (blockIdx.x == 0) {
-          float* m = p.model.p[i] + index;
-          *m = __fadd_rn(*m, f);
+          if (p.log_values) {
+            p.log_values[(iteration - p.log_first_iteration) * p.n_images + i] = f;
+          } else {
+            float* m = p.model.p[i] + index;
+            *m = __fadd_rn(*m, f);
+          }
         }
       }
+      if (blockIdx.x == 0 && lane == 0 && p.log_values)
+        p.log_index[iteration - p.log_first_iteration] = index;
       if (blockIdx.x == 0 && lane == 0) {
         if (n_trace < p.trace_capacity) {
           p.trace[n_trace] = TraceEntry{uint32_t(iteration), 0u, uint32_t(px), uint32_t(py), val};
@@ -929,13 +939,20 @@ __global__ void __launch_bounds__(kPersistThreads, 1)
       // model += factor, software-pipelined: the load is issued here, the add and the store wait
       // until this thread has done its share of the next iteration (every CTA is waiting for this
       // one's next candidate, so the L2 round trip must not sit in front of it)
+      if (p.log_values) {
+        const unsigned long long k_log = iteration - p.log_first_iteration;
 #pragma unroll
-      for (int k = 0; k < C; ++k) {
-        model_ptr[k] = p.model.p[k] + index;
-        model_old[k] = __ldcg(model_ptr[k]);
-        model_add[k] = factors[k];
+        for (int k = 0; k < C; ++k) p.log_values[k_log * C + k] = factors[k];
+        p.log_index[k_log] = index;
+      } else {
+#pragma unroll
+        for (int k = 0; k < C; ++k) {
+          model_ptr[k] = p.model.p[k] + index;
+          model_old[k] = __ldcg(model_ptr[k]);
+          model_add[k] = factors[k];
+        }
+        model_pending = true;
       }
-      model_pending = true;
       if (n_trace < p.trace_capacity) {
         p.trace[n_trace] = TraceEntry{uint32_t(iteration), 0u, uint32_t(px), uint32_t(py), val};
         ++n_trace;

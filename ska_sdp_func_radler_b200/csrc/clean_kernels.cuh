@@ -83,6 +83,13 @@ struct HogbomParams {
   int n_fit, n_pol;
   TraceEntry* trace;
   unsigned long long trace_capacity;
+  // Component log (host-memory calls): instead of model[i][peak] += value, component k of the
+  // call (k = iteration - log_first_iteration) is recorded as its frame index and its n_images
+  // values; the host applies them to its model planes in order (the same fp32 adds), so the model
+  // never crosses PCIe. Null: the model planes are updated on the device.
+  uint32_t* log_index;
+  float* log_values;
+  unsigned long long log_first_iteration;
   // rows of a sharded cube: local row yl is frame row
   //   y = y_offset + ((yl / block_rows) * block_world + block_rank) * block_rows + yl % block_rows
   // of a width x global_height frame. Contiguous band: block_rows = height, block_world = 1;

@@ -105,6 +105,32 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
   p.block_world = 1;
   p.block_rank = 0;
   const bool sharded = h.dist.band_set;
+  const bool logging = h.model_log && !sharded;
+  h.model_log_count = 0;
+  if (logging) {
+    const uint64_t capacity = h.settings.max_iterations > h.iteration_number
+                                  ? h.settings.max_iterations - h.iteration_number
+                                  : 0;
+    h.log_index.Reserve(std::max<uint64_t>(capacity, 1));
+    h.log_values.Reserve(std::max<uint64_t>(capacity, 1) * cube.n_images);
+    p.log_index = h.log_index.get();
+    p.log_values = h.log_values.get();
+    p.log_first_iteration = h.iteration_number;
+  }
+  // the component log of the call, for the host to apply to its model planes
+  auto collect_log = [&](const CleanState& s) {
+    if (!logging) return;
+    const uint64_t count = s.iteration - iteration_at_start;
+    h.model_log_count = count;
+    h.log_index_host.resize(count);
+    h.log_values_host.resize(count * cube.n_images);
+    if (count == 0) return;
+    RDL_CUDA(cudaMemcpyAsync(h.log_index_host.data(), h.log_index.get(), count * sizeof(uint32_t),
+                             cudaMemcpyDeviceToHost, stream));
+    RDL_CUDA(cudaMemcpyAsync(h.log_values_host.data(), h.log_values.get(),
+                             count * cube.n_images * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    RDL_CUDA(cudaStreamSynchronize(stream));
+  };
   if (sharded) {
     // Row band of a width x global_height frame (rdl_dist_set_row_band): borders, window and
     // peak indices are the frame's; mask / RMS image are full-frame, offset to this band.
@@ -166,6 +192,7 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
         RDL_CUDA(cudaMemcpyAsync(h.trace_host.data(), h.trace_dev.get(),
                                  s.n_trace * sizeof(TraceEntry), cudaMemcpyDeviceToHost, stream));
       RDL_CUDA(cudaStreamSynchronize(stream));
+      collect_log(s);
       return FinishResult(h, s, iteration_at_start);
     }
   }
@@ -228,6 +255,7 @@ rdl_result RunGenericClean(rdl_handle& h, DeviceCube& cube, cudaStream_t stream)
     RDL_CUDA(cudaMemcpyAsync(h.trace_host.data(), h.trace_dev.get(),
                              s.n_trace * sizeof(TraceEntry), cudaMemcpyDeviceToHost, stream));
   RDL_CUDA(cudaStreamSynchronize(stream));
+  collect_log(s);
   return FinishResult(h, s, iteration_at_start);
 }
 

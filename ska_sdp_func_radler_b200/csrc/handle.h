@@ -136,6 +136,12 @@ struct rdl_handle {
   uint64_t iteration_number = 0;
   int device = 0;
   cudaStream_t own_stream = nullptr;
+  // host-memory multiscale calls: the model planes are uploaded on a second stream behind the
+  // residual and PSF planes, while the call already works; model_ready is set (non-null) for the
+  // duration of such a call and the algorithm waits on it before it first touches the model
+  cudaStream_t upload_stream = nullptr;
+  cudaEvent_t upload_event = nullptr, model_ready = nullptr;
+  bool model_pending = false;
   std::string error;
   uint64_t launches = 0;
 
@@ -201,6 +207,13 @@ struct rdl_handle {
   rdl::DistContext dist;
   rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;
   rdl::DeviceBuffer<unsigned char> persist_scratch;  // HogbomPersistentKernel: barrier + candidates
+  // component log of a host-memory GenericClean call (clean_kernels.cuh, HogbomParams::log_*)
+  bool model_log = false;        // set by the caller of RunGenericClean for this call
+  uint64_t model_log_count = 0;  // components recorded by the call
+  rdl::DeviceBuffer<uint32_t> log_index;
+  rdl::DeviceBuffer<float> log_values;
+  std::vector<uint32_t> log_index_host;
+  std::vector<float> log_values_host;
   rdl::ComponentList components;     // MultiScaleAlgorithm::component_list_ (track_components)
   double beam_size_in_pixels = 1.0;  // multiscale_algorithm.cc:153-163
   std::shared_ptr<rdl::MultiScaleState> ms;  // deep-copied by rdl_clone

@@ -315,6 +315,13 @@ class MultiScaleRun {
   }
 
   rdl_result Execute();
+  ~MultiScaleRun() {
+    if (comm_stream_) {
+      cudaStreamSynchronize(comm_stream_);
+      cudaStreamDestroy(comm_stream_);
+    }
+    for (cudaEvent_t e : events_) cudaEventDestroy(e);
+  }
 
  private:
   std::vector<rdl_scale_info>& Scales() { return st_.scales; }
@@ -340,6 +347,13 @@ class MultiScaleRun {
   const float2* PsfSpectrum(size_t p, size_t si, FftConvolver& padded);
   const float* TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum);
   void Sync() { RDL_CUDA(cudaStreamSynchronize(stream_)); }
+  // host-memory calls upload the model planes on a second stream (abi.cu): wait for them before
+  // the first kernel that touches the model
+  void WaitForModel() {
+    if (!h_.model_pending) return;
+    RDL_CUDA(cudaStreamWaitEvent(stream_, h_.model_ready, 0));
+    h_.model_pending = false;
+  }
   // channel sharding over the ranks
   int OwnerOfChannel(size_t channel) const {
     return sharded_ ? int(channel * size_t(world_) / cube_.n_channels) : 0;
@@ -353,6 +367,40 @@ class MultiScaleRun {
     for (size_t i = 0; i != cube_.n_images; ++i) roots[i] = OwnerOfChannel(cube_.PsfIndex(i));
     NcclBroadcastPlanes(h_.dist, planes, roots.data(), cube_.n_images, n_, stream_);
   }
+
+  // Pipelined exchange: planes travel on a second stream while the next channel's convolution
+  // runs on the main one. BeginShare: the exchange stream waits for everything queued so far
+  // (receive buffers are free); SharePlane: the owner's exchange waits for the producing kernels
+  // of that plane only; EndShare: the main stream waits for the exchange. Every rank calls
+  // SharePlane in the same order (one communicator, one issue order).
+  void BeginShare() {
+    if (!sharded_) return;
+    if (!comm_stream_) RDL_CUDA(cudaStreamCreateWithFlags(&comm_stream_, cudaStreamNonBlocking));
+    WaitOn(comm_stream_, stream_);
+  }
+  void SharePlane(float* plane, int root) {
+    if (!sharded_) return;
+    if (root == rank_) WaitOn(comm_stream_, stream_);
+    NcclBroadcastPlanes(h_.dist, &plane, &root, 1, n_, comm_stream_);
+  }
+  void EndShare() {
+    if (!sharded_) return;
+    WaitOn(stream_, comm_stream_);
+  }
+  void WaitOn(cudaStream_t waiter, cudaStream_t producer) {
+    // a stream wait binds to the record that precedes it, so events can be recycled
+    if (events_.size() < 32) {
+      cudaEvent_t fresh = nullptr;
+      RDL_CUDA(cudaEventCreateWithFlags(&fresh, cudaEventDisableTiming));
+      events_.push_back(fresh);
+    }
+    cudaEvent_t e = events_[next_event_++ % events_.size()];
+    RDL_CUDA(cudaEventRecord(e, producer));
+    RDL_CUDA(cudaStreamWaitEvent(waiter, e, 0));
+  }
+  cudaStream_t comm_stream_ = nullptr;
+  std::vector<cudaEvent_t> events_;
+  size_t next_event_ = 0;
 
   bool sharded_ = false;
   int world_ = 1, rank_ = 0;
@@ -836,18 +884,18 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       const float2* spectrum = ScaleSpectrum(swp);
       std::vector<const float*> twice(n_psfs);
       for (size_t p = 0; p != n_psfs; ++p) twice[p] = TwiceConvolvedPsf(p, swp, spectrum);
-      std::vector<float*> shared_planes(cube_.n_images);
+      for (size_t i = 0; i != cube_.n_images; ++i) individual_convolved_[i].Reserve(n_);
+      BeginShare();
       for (size_t i = 0; i != cube_.n_images; ++i) {
-        individual_convolved_[i].Reserve(n_);
         ++h.reference_convolutions[{width_, height_}];
         if (MineImage(i))
           conv_.ConvolveWith(cube_.residual.p[i], width_, height_, spectrum,
                              individual_convolved_[i].get(), width_, height_, 0, stream_);
+        SharePlane(individual_convolved_[i].get(), OwnerOfChannel(cube_.PsfIndex(i)));
         conv_residual.p[i] = individual_convolved_[i].get();
-        shared_planes[i] = individual_convolved_[i].get();
         psf_per_image.p[i] = twice[cube_.PsfIndex(i)];
       }
-      ShareImagePlanes(shared_planes.data());
+      EndShare();
       h.launches += conv_.TakeLaunchCount();
     } else {
       // scale 0: the "convolved" images are the images themselves; the sub-minor loop only
@@ -880,6 +928,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
         throw std::domain_error("channel-sharded multiscale needs the fast sub-minor loop");
       PtrTable convolved{};
       for (size_t i = 0; i != cube_.n_images; ++i) convolved.p[i] = individual_convolved_[i].get();
+      WaitForModel();
       diverging = RunWithoutSubMinorLoop(swp, first_sub_iteration_threshold, initial_peak_value,
                                          convolved, psf_per_image);
       ActivateScales(swp);
@@ -931,15 +980,23 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       SubMinorUpdateAutoMask(h, int(cube_.n_images), st_.scale_masks[swp].get(), stream_);
     if (h.config.track_components)
       SubMinorUpdateComponentList(h, int(cube_.n_images), swp, stream_);
+    WaitForModel();
+    BeginShare();
     for (size_t i = 0; i != cube_.n_images; ++i) {
       ++h.reference_convolutions[{conv_w, conv_h}];
       if (S[swp].scale != 0.0f) ++h.reference_convolutions[{width_, height_}];
-      if (!MineImage(i)) continue;
+      if (!MineImage(i)) {
+        SharePlane(cube_.residual.p[i], OwnerOfChannel(cube_.PsfIndex(i)));
+        continue;
+      }
       const float2* psf_spectrum = PsfSpectrum(cube_.PsfIndex(i), swp, padded);
       SubMinorScatterModel(h, int(i), scratch_.get(), n_, stream_);
       // CorrectResidualDirty (subminor_loop.cc:195-218): residual -= Trim(Convolve(Untrim(model)))
       padded.ConvolveWith(scratch_.get(), width_, height_, psf_spectrum, cube_.residual.p[i], width_,
                           height_, 1, stream_);
+      // the corrected residual of this channel, for the joined peak search of all ranks: on its
+      // way while the model transform below runs
+      SharePlane(cube_.residual.p[i], rank_);
       // model += Transform(full model, scale)  (multiscale_algorithm.cc:442-460)
       if (S[swp].scale != 0.0f)
         conv_.ConvolveWith(scratch_.get(), width_, height_, ScaleSpectrum(swp), cube_.model.p[i], width_,
@@ -947,13 +1004,13 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       else
         SubMinorAddModelTo(h, int(i), cube_.model.p[i], stream_);
     }
+    EndShare();
     h.launches += padded.TakeLaunchCount() + conv_.TakeLaunchCount();
-    // the corrected residuals of every channel, for the joined peak search of all ranks
-    ShareImagePlanes(cube_.residual.p);
 
     ActivateScales(swp);
     FindActiveScaleConvolvedMaxima(false);
     if (!SelectMaximumScale(swp)) {
+      WaitForModel();
       ShareImagePlanes(cube_.model.p);
       Sync();
       result.iteration_number = h.iteration_number;
@@ -961,6 +1018,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       return result;
     }
   }
+  WaitForModel();
   ShareImagePlanes(cube_.model.p);
 
   const bool max_iter_reached = h.iteration_number >= set.max_iterations;

@@ -203,3 +203,42 @@ def test_path_b_divergence(rdl, oracle, torch_cuda, hogbom_loop_flavour):
     o, oi, g, gi, alg = _run_both(rdl, oracle, res, psfs, None, st)
     assert o.is_diverging
     _assert_same(o, oi, g, gi, alg)
+
+
+@pytest.mark.parametrize("c", [1, 3])
+def test_path_b_host_buffers_keep_the_model_on_the_host(rdl, oracle, torch_cuda, hogbom_loop_flavour, c):
+    # RDL_MEM_HOST, GenericClean without the sub-minor loop: the model planes are not uploaded; the
+    # call logs its components on the device and applies them to the caller's planes in order.
+    # Same bits as the device-resident call, from a non-zero model, over two major iterations
+    # (components falling on the same pixel several times).
+    torch = torch_cuda
+    n = 192
+    res, psfs, weights, _ = hogbom_case(n, c, seed=17)
+    rng = np.random.default_rng(3)
+    model0 = rng.normal(0, 0.1, res.shape).astype(np.float32)
+    cube = rdl.Cube(n, n, c, 1, weights)
+
+    def run(host):
+        alg = rdl.GenericClean(use_sub_minor_optimization=False)
+        if host:
+            r, m = res.copy(), model0.copy()
+            p = psfs
+        else:
+            r, m = torch.from_numpy(res.copy()).cuda(), torch.from_numpy(model0.copy()).cuda()
+            p = torch.from_numpy(psfs).cuda()
+        out = []
+        for call in range(2):
+            alg.apply(max_iterations=150 * (call + 1), clean_border_ratio=0.0, major_loop_gain=0.9,
+                      trace_capacity=1000)
+            g = alg.execute_major_iteration(cube, r, m, p)
+            out.append(g.iteration_number)
+        if not host:
+            r, m = r.cpu().numpy(), m.cpu().numpy()
+        return out, r, m
+
+    it_h, r_h, m_h = run(True)
+    it_d, r_d, m_d = run(False)
+    assert it_h == it_d and it_h[1] > it_h[0] > 5
+    assert np.array_equal(r_h, r_d)
+    assert np.array_equal(m_h, m_d)
+    assert np.count_nonzero(m_h != model0) < it_h[1] * c  # some pixels were hit more than once
