@@ -16,8 +16,11 @@
 // tolerance; the stopping rules compare those sums against constants (SNR > 100, SNR < previous,
 // rmsAfter > rmsBefore), so a run can only branch differently at a knife edge.
 //
-// Not built: cubes with more than one image (PerformSubImageFitAll's per-component refit,
-// :628-801); the call fails with RDL_ERR_UNSUPPORTED for those.
+// Cubes with several images (:628-801, PerformSubImageFitAll / FitSingle / ComponentFit[Boxed]): the
+// structure model of the integrated image is split into its connected components (row-major
+// seed scan + FloodFill2D), every component is refitted per image inside its own box, and the
+// images get component * factor(image) / factor(integrated). The component sums are float32
+// sequential sums in flood-fill order in the reference, fixed-order double sums here.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -208,6 +211,65 @@ __global__ void UntrimKernel(float* dst, int width, int height, const float* box
 
 int GridFor(size_t n) { return int(std::clamp<size_t>((n + 255) / 256, 1, size_t(kSmCount) * 16)); }
 
+// ---- PerformSubImageFitSingle (:672-742): components of the structure model -------------------
+// first row-major pixel with !mask && |model| > threshold (the seed scan of :688-693)
+__global__ void FindSeedKernel(const float* model, const uint8_t* mask, size_t n, float threshold,
+                               unsigned* first) {
+  unsigned best = 0xffffffffu;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    if (!mask[i] && fabsf(model[i]) > threshold) best = min(best, unsigned(i));
+  for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if ((threadIdx.x & 31) == 0 && best != 0xffffffffu) atomicMin(first, best);
+}
+// area = pixels the flood fill has just set; sub_dirty = model inside the area, 0 elsewhere;
+// box[0..3] = min x, max x, min y, max y of the area
+__global__ void AreaKernel(const float* model, const uint8_t* mask_after, const uint8_t* mask_before,
+                           int width, size_t n, uint8_t* area, float* sub_dirty, unsigned* box) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const bool in = mask_after[i] && !mask_before[i];
+    area[i] = in ? 1 : 0;
+    sub_dirty[i] = in ? model[i] : 0.0f;
+    if (in) {
+      const unsigned y = unsigned(i / width), x = unsigned(i - size_t(y) * width);
+      atomicMin(box + 0, x);
+      atomicMax(box + 1, x);
+      atomicMin(box + 2, y);
+      atomicMax(box + 3, y);
+    }
+  }
+}
+// partial sums over the area of model and masked_dirty, both bw x bh boxes at (x1, y1) of the
+// frame the area mask lives in (PerformSubImageComponentFit, :790-794)
+__global__ void __launch_bounds__(kRedThreads) AreaSumsKernel(const float* model, const float* masked_dirty,
+                                                              const uint8_t* area, int area_width, int x1,
+                                                              int y1, int bw, int bh, double* partial) {
+  __shared__ double red[32];
+  double m_sum = 0.0, d_sum = 0.0;
+  const size_t n = size_t(bw) * bh;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const int y = int(i / bw), x = int(i - size_t(y) * bw);
+    if (!area[size_t(y + y1) * area_width + x + x1]) continue;
+    m_sum += double(model[i]);
+    d_sum += double(masked_dirty[i]);
+  }
+  m_sum = BlockSum(m_sum, red);
+  d_sum = BlockSum(d_sum, red);
+  if (threadIdx.x == 0) {
+    partial[2 * blockIdx.x] = m_sum;
+    partial[2 * blockIdx.x + 1] = d_sum;
+  }
+}
+// fitted[i] += model[i] * factor / integrated_factor inside the area (:729-733)
+__global__ void FittedAddKernel(float* fitted, const float* model, const uint8_t* area, float factor,
+                                float integrated, size_t n) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    if (area[i]) fitted[i] = __fadd_rn(fitted[i], __fdiv_rn(__fmul_rn(model[i], factor), integrated));
+}
+
 int EndScale(size_t max_image_dimension) {  // iuwt_decomposition.h:182-184
   return std::max(int(std::log2(double(max_image_dimension))) - 3, 2);
 }
@@ -325,6 +387,22 @@ class IuwtRun {
                                   size_t height, const std::vector<float>& thresholds,
                                   const ValComponent& max_comp, bool allow_trimming,
                                   const uint8_t* prior_mask);
+  // cubes with several images: the structure found in the integrated image is refitted per image
+  void PerformSubImageFitAll(Decomposition& iuwt, const uint8_t* masks, const float* structure_model,
+                             float* scratch_a, float* scratch_b, const ValComponent& max_comp,
+                             float* fitted_model, const float* psf, const float* dirty, size_t width,
+                             size_t height);
+  void PerformSubImageFitSingle(Decomposition& iuwt, const uint8_t* masks, const float* structure_model,
+                                float* scratch_b, const ValComponent& max_comp, const float* psf,
+                                float* sub_dirty, float* fitted_sub_model,
+                                std::vector<float>& correction_factor, size_t width, size_t height);
+  float PerformSubImageComponentFitBoxed(Decomposition& iuwt, const uint8_t* masks, float* model,
+                                         const float* masked_dirty, const float* psf,
+                                         const float2* psf_kernel, size_t x1, size_t y1, size_t x2,
+                                         size_t y2, size_t width, size_t height);
+  float PerformSubImageComponentFit(Decomposition& iuwt, const uint8_t* masks, float* model,
+                                    const float* masked_dirty, const float2* psf_kernel, size_t x_offset,
+                                    size_t y_offset, size_t width, size_t height, size_t area_width);
 
   rdl_handle& h_;
   DeviceCube& cube_;
@@ -346,6 +424,13 @@ class IuwtRun {
       cg_model_, gradient_;
   DeviceBuffer<float2> small_spectrum_;
   DeviceBuffer<uint8_t> masks_full_, masks_small_, small_prior_;
+  // PerformSubImageFit*: current bounding box in the full frame (cur_box_*), work planes
+  size_t cur_box_x1_ = 0, cur_box_y1_ = 0, cur_box_x2_ = 0, cur_box_y2_ = 0;
+  DeviceBuffer<uint8_t> mask2d_, mask2d_before_, area_, fit_masks_;
+  DeviceBuffer<unsigned> fit_scalars_;
+  DeviceBuffer<float> fit_sub_dirty_, fit_psf_, fit_model_, fit_masked_dirty_, fit_small_psf_;
+  DeviceBuffer<float2> fit_spectrum_, fit_small_spectrum_;
+  Decomposition fit_iuwt_;
 };
 
 // MeasureRMSPerScale (:42-102). The Gaussian fits and the flood fills at its end only produce
@@ -617,11 +702,18 @@ bool IuwtRun::FillAndDeconvolveStructure(Decomposition& iuwt, float* dirty, floa
                                                         int(new_height), masks + s * n);
       ++h_.launches;
     }
-    // structure_model_full.Trim(...)
-    small_model_.Reserve(small_n);
-    TrimKernel<<<GridFor(small_n), 256, 0, stream_>>>(small_model_.get(), structure_model_full, int(width),
-                                                      int(x1), int(y1), int(new_width), int(new_height),
-                                                      nullptr);
+    // structure_model_full.Trim(...): every image of the set
+    cur_box_x1_ = x1;
+    cur_box_x2_ = x2;
+    cur_box_y1_ = y1;
+    cur_box_y2_ = y2;
+    const size_t n_img = cube_.n_images;
+    small_model_.Reserve(n_img * small_n);
+    for (size_t i = 0; i != n_img; ++i)
+      TrimKernel<<<GridFor(small_n), 256, 0, stream_>>>(small_model_.get() + i * small_n,
+                                                        structure_model_full + i * n, int(width), int(x1),
+                                                        int(y1), int(new_width), int(new_height), nullptr);
+    h_.launches += n_img - 1;
     const uint8_t* small_prior = nullptr;
     if (prior_mask) {
       small_prior_.Reserve(small_n);
@@ -638,10 +730,15 @@ bool IuwtRun::FillAndDeconvolveStructure(Decomposition& iuwt, float* dirty, floa
         trimmed_iuwt_, small_dirty_.get(), small_model_.get(), small_scratch_.get(), small_psf_.get(),
         small_kernel, cur_end_scale, cur_min_scale, new_width, new_height, thresholds, new_max, false,
         small_prior);
-    UntrimKernel<<<GridFor(n), 256, 0, stream_>>>(structure_model_full, int(width), int(height),
-                                                  small_model_.get(), int(x1), int(y1), int(new_width),
-                                                  int(new_height));
-    ++h_.launches;
+    for (size_t i = 0; i != n_img; ++i)
+      UntrimKernel<<<GridFor(n), 256, 0, stream_>>>(structure_model_full + i * n, int(width), int(height),
+                                                    small_model_.get() + i * small_n, int(x1), int(y1),
+                                                    int(new_width), int(new_height));
+    h_.launches += n_img;
+    cur_box_x1_ = 0;
+    cur_box_x2_ = width;
+    cur_box_y1_ = 0;
+    cur_box_y2_ = height;
     RDL_CUDA(cudaGetLastError());
     return result;
   }
@@ -669,10 +766,176 @@ bool IuwtRun::FillAndDeconvolveStructure(Decomposition& iuwt, float* dirty, floa
   const float rms_after = Rms(masked_dirty_.get(), n);
   if (rms_after > rms_before) return false;  // "RMS got worse"
 
-  // PerformSubImageFitAll with a single image: fitted_model.SetImage(0, structure_model)
-  Copy(structure_model_full, cg_model_.get(), n);
+  if (cube_.n_images == 1) {
+    // PerformSubImageFitAll with a single image: fitted_model.SetImage(0, structure_model)
+    Copy(structure_model_full, cg_model_.get(), n);
+  } else {
+    PerformSubImageFitAll(iuwt, masks, cg_model_.get(), scratch, masked_dirty_.get(), max_comp,
+                          structure_model_full, psf, dirty, width, height);
+  }
   RDL_CUDA(cudaGetLastError());
   return true;
+}
+
+// PerformSubImageFitAll (:628-670): with several images the structure model found in the
+// integrated image is refitted image by image. First the per-component correction factors of the
+// integrated image itself, then every image of the set (trimmed to the current box, with its own
+// PSF): fitted[img] += component * factor(img) / factor(integrated).
+void IuwtRun::PerformSubImageFitAll(Decomposition& iuwt, const uint8_t* masks,
+                                    const float* structure_model, float* scratch_a, float* scratch_b,
+                                    const ValComponent& max_comp, float* fitted_model, const float* psf,
+                                    const float* dirty, size_t width, size_t height) {
+  const size_t n = width * height;
+  std::vector<float> correction_factors;
+  Copy(scratch_a, dirty, n);
+  PerformSubImageFitSingle(iuwt, masks, structure_model, scratch_b, max_comp, psf, scratch_a, nullptr,
+                           correction_factors, width, height);
+  Zero(fitted_model, cube_.n_images * n);
+  const size_t bw = cur_box_x2_ - cur_box_x1_, bh = cur_box_y2_ - cur_box_y1_;
+  if (bw != width || bh != height) throw std::logic_error("IUWT box does not match the sub-image");
+  for (size_t img = 0; img != cube_.n_images; ++img) {
+    TrimKernel<<<GridFor(n), 256, 0, stream_>>>(scratch_a, cube_.residual.p[img], int(width_),
+                                                int(cur_box_x1_), int(cur_box_y1_), int(bw), int(bh),
+                                                nullptr);
+    ++h_.launches;
+    const float* sub_psf = cube_.psf.p[cube_.PsfIndex(img)];
+    if (width_ != width || height_ != height) {
+      fit_psf_.Reserve(n);
+      TrimKernel<<<GridFor(n), 256, 0, stream_>>>(fit_psf_.get(), sub_psf, int(width_),
+                                                  int((width_ - width) / 2), int((height_ - height) / 2),
+                                                  int(width), int(height), nullptr);
+      ++h_.launches;
+      sub_psf = fit_psf_.get();
+    }
+    PerformSubImageFitSingle(iuwt, masks, structure_model, scratch_b, max_comp, sub_psf, scratch_a,
+                             fitted_model + img * n, correction_factors, width, height);
+  }
+}
+
+// PerformSubImageFitSingle (:672-742)
+void IuwtRun::PerformSubImageFitSingle(Decomposition& iuwt, const uint8_t* masks,
+                                       const float* structure_model, float* scratch_b,
+                                       const ValComponent& max_comp, const float* psf, float* sub_dirty,
+                                       float* fitted_sub_model, std::vector<float>& correction_factor,
+                                       size_t width, size_t height) {
+  const size_t n = width * height;
+  const float2* psf_kernel = KernelSpectrum(psf, width, height, fit_spectrum_);
+  float* masked_dirty = scratch_b;
+  DecomposeAliased(iuwt, sub_dirty);  // iuwt.Decompose(sub_dirty, sub_dirty, false)
+  RecomposeMasked(iuwt, masks, masked_dirty);
+  mask2d_.Reserve(n);
+  mask2d_before_.Reserve(n);
+  area_.Reserve(n);
+  fit_scalars_.Reserve(8);
+  RDL_CUDA(cudaMemsetAsync(mask2d_.get(), 0, n, stream_));
+  const float peak_level = std::fabs(ReadPixel(structure_model, size_t(max_comp.y) * width + max_comp.x));
+  const float threshold = peak_level * 1e-4f;
+  size_t component_index = 0;
+  for (;;) {
+    // next seed in row-major order
+    const unsigned none = 0xffffffffu;
+    RDL_CUDA(cudaMemcpyAsync(fit_scalars_.get(), &none, sizeof(none), cudaMemcpyHostToDevice, stream_));
+    FindSeedKernel<<<GridFor(n), 256, 0, stream_>>>(structure_model, mask2d_.get(), n, threshold,
+                                                    fit_scalars_.get());
+    ++h_.launches;
+    unsigned seed = none;
+    RDL_CUDA(cudaMemcpyAsync(&seed, fit_scalars_.get(), sizeof(seed), cudaMemcpyDeviceToHost, stream_));
+    Sync();
+    if (seed == none) break;
+    RDL_CUDA(cudaMemcpyAsync(mask2d_before_.get(), mask2d_.get(), n, cudaMemcpyDeviceToDevice, stream_));
+    IuwtFloodfill2D(h_, structure_model, mask2d_.get(), width, height, threshold, true, seed % width,
+                    seed / width, stream_);
+    // the area, the model inside it, its bounding box
+    const unsigned box_init[4] = {0xffffffffu, 0u, 0xffffffffu, 0u};
+    RDL_CUDA(cudaMemcpyAsync(fit_scalars_.get() + 4, box_init, sizeof(box_init), cudaMemcpyHostToDevice,
+                             stream_));
+    AreaKernel<<<GridFor(n), 256, 0, stream_>>>(structure_model, mask2d_.get(), mask2d_before_.get(),
+                                                int(width), n, area_.get(), sub_dirty,
+                                                fit_scalars_.get() + 4);
+    ++h_.launches;
+    unsigned box[4];
+    RDL_CUDA(cudaMemcpyAsync(box, fit_scalars_.get() + 4, sizeof(box), cudaMemcpyDeviceToHost, stream_));
+    Sync();
+    size_t box_x1 = box[0], box_x2 = box[1], box_y1 = box[2], box_y2 = box[3];  // maxima inclusive (sic)
+    AdjustBox(box_x1, box_y1, box_x2, box_y2, width, height, iuwt.n_scales);
+    const float factor = PerformSubImageComponentFitBoxed(iuwt, masks, sub_dirty, masked_dirty, psf,
+                                                          psf_kernel, box_x1, box_y1, box_x2, box_y2,
+                                                          width, height);
+    if (fitted_sub_model != nullptr) {
+      const float integrated = correction_factor.at(component_index);
+      if (std::isfinite(factor) && std::isfinite(integrated) && integrated != 0.0f) {
+        FittedAddKernel<<<GridFor(n), 256, 0, stream_>>>(fitted_sub_model, structure_model, area_.get(),
+                                                         factor, integrated, n);
+        ++h_.launches;
+      }
+      ++component_index;
+    } else {
+      correction_factor.push_back(factor);
+    }
+  }
+  RDL_CUDA(cudaGetLastError());
+}
+
+// PerformSubImageComponentFitBoxed (:744-777)
+float IuwtRun::PerformSubImageComponentFitBoxed(Decomposition& iuwt, const uint8_t* masks, float* model,
+                                                const float* masked_dirty, const float* psf,
+                                                const float2* psf_kernel, size_t x1, size_t y1,
+                                                size_t x2, size_t y2, size_t width, size_t height) {
+  if (x1 > 0 || y1 > 0 || x2 < width || y2 < height) {
+    const size_t new_width = x2 - x1, new_height = y2 - y1, small_n = new_width * new_height;
+    const size_t n = width * height;
+    fit_iuwt_.Shape(iuwt.n_scales, new_width, new_height);
+    fit_masks_.Reserve(size_t(iuwt.n_scales) * small_n);
+    for (int s = 0; s != iuwt.n_scales; ++s)
+      TrimBytesKernel<<<GridFor(small_n), 256, 0, stream_>>>(fit_masks_.get() + size_t(s) * small_n,
+                                                             masks + size_t(s) * n, int(width), int(x1),
+                                                             int(y1), int(new_width), int(new_height));
+    fit_model_.Reserve(small_n);
+    TrimKernel<<<GridFor(small_n), 256, 0, stream_>>>(fit_model_.get(), model, int(width), int(x1), int(y1),
+                                                      int(new_width), int(new_height), nullptr);
+    fit_small_psf_.Reserve(small_n);
+    TrimKernel<<<GridFor(small_n), 256, 0, stream_>>>(fit_small_psf_.get(), psf, int(width),
+                                                      int((width - new_width) / 2),
+                                                      int((height - new_height) / 2), int(new_width),
+                                                      int(new_height), nullptr);
+    const float2* small_kernel = KernelSpectrum(fit_small_psf_.get(), new_width, new_height,
+                                                fit_small_spectrum_);
+    fit_masked_dirty_.Reserve(small_n);
+    TrimKernel<<<GridFor(small_n), 256, 0, stream_>>>(fit_masked_dirty_.get(), masked_dirty, int(width),
+                                                      int(x1), int(y1), int(new_width), int(new_height),
+                                                      nullptr);
+    h_.launches += 3 + iuwt.n_scales;
+    return PerformSubImageComponentFit(fit_iuwt_, fit_masks_.get(), fit_model_.get(),
+                                       fit_masked_dirty_.get(), small_kernel, x1, y1, new_width,
+                                       new_height, width);
+  }
+  return PerformSubImageComponentFit(iuwt, masks, model, masked_dirty, psf_kernel, 0, 0, width, height,
+                                     width);
+}
+
+// PerformSubImageComponentFit (:779-801): IUWT^-1 mask IUWT (model (x) PSF), then the ratio of the
+// sums of masked dirty and model over the component's area. (float32 sequential sums over the
+// area in flood-fill order in the reference; fixed-order double sums here.)
+float IuwtRun::PerformSubImageComponentFit(Decomposition& iuwt, const uint8_t* masks, float* model,
+                                           const float* masked_dirty, const float2* psf_kernel,
+                                           size_t x_offset, size_t y_offset, size_t width,
+                                           size_t height, size_t area_width) {
+  Convolve(model, psf_kernel, width, height);
+  DecomposeAliased(iuwt, model);
+  RecomposeMasked(iuwt, masks, model);
+  partial_.Reserve(2 * kRedBlocks + 8);
+  AreaSumsKernel<<<kRedBlocks, kRedThreads, 0, stream_>>>(model, masked_dirty, area_.get(), int(area_width),
+                                                          int(x_offset), int(y_offset), int(width),
+                                                          int(height), partial_.get());
+  FinishSumKernel<<<1, 64, 0, stream_>>>(partial_.get(), kRedBlocks, 2, partial_.get() + 2 * kRedBlocks);
+  h_.launches += 2;
+  double sums[2];
+  RDL_CUDA(cudaMemcpyAsync(sums, partial_.get() + 2 * kRedBlocks, sizeof(sums), cudaMemcpyDeviceToHost,
+                           stream_));
+  Sync();
+  const float model_sum = float(sums[0]), dirty_sum = float(sums[1]);
+  if (model_sum == 0.0f || !std::isfinite(dirty_sum) || !std::isfinite(model_sum)) return 0.0f;
+  return dirty_sum / model_sum;
 }
 
 // PerformMajorIteration (:803-918)
@@ -697,8 +960,13 @@ float IuwtRun::PerformMajorIteration(uint64_t& iter_counter, uint64_t n_iter,
   // "Measuring PSF..."; the PSF convolved with itself only feeds the dead outputs
   MeasureRMSPerScale(psf.get(), max_scale);
 
-  structure_model_.Reserve(n);
-  Zero(structure_model_.get(), n);
+  const size_t n_img = cube_.n_images;
+  structure_model_.Reserve(n_img * n);
+  Zero(structure_model_.get(), n_img * n);
+  cur_box_x1_ = 0;
+  cur_box_x2_ = width_;
+  cur_box_y1_ = 0;
+  cur_box_y2_ = height_;
   Decomposition iuwt;
   iuwt.Shape(max_scale, width_, height_);  // room for every scale count this call can reach
   iuwt.n_scales = cur_end_scale;
@@ -715,16 +983,25 @@ float IuwtRun::PerformMajorIteration(uint64_t& iter_counter, uint64_t n_iter,
                                                       scratch.get(), size_t(cur_end_scale),
                                                       cur_min_scale, max_components);
     if (succeeded) {
-      ScaleKernel<<<GridFor(n), 256, 0, stream_>>>(structure_model_.get(), minor_loop_gain_, n);
-      AddSubKernel<<<GridFor(n), 256, 0, stream_>>>(cube_.model.p[0], structure_model_.get(), true, n);
-      // dirty = dirty - structureModel (x) psf, per image with its own PSF
-      Copy(scratch.get(), structure_model_.get(), n);
-      const float2* kernel =
-          KernelSpectrum(cube_.psf.p[cube_.PsfIndex(0)], width_, height_, image_psf_spectrum);
-      Convolve(scratch.get(), kernel, width_, height_);
-      AddSubKernel<<<GridFor(n), 256, 0, stream_>>>(cube_.residual.p[0], scratch.get(), false, n);
+      ScaleKernel<<<GridFor(n_img * n), 256, 0, stream_>>>(structure_model_.get(), minor_loop_gain_,
+                                                           n_img * n);
+      size_t spectrum_of = size_t(-1);
+      const float2* kernel = nullptr;
+      for (size_t i = 0; i != n_img; ++i) {
+        float* part = structure_model_.get() + i * n;
+        AddSubKernel<<<GridFor(n), 256, 0, stream_>>>(cube_.model.p[i], part, true, n);
+        // dirty = dirty - structureModel (x) psf, per image with its own PSF
+        Copy(scratch.get(), part, n);
+        if (cube_.PsfIndex(i) != spectrum_of) {
+          spectrum_of = cube_.PsfIndex(i);
+          kernel = KernelSpectrum(cube_.psf.p[spectrum_of], width_, height_, image_psf_spectrum);
+        }
+        Convolve(scratch.get(), kernel, width_, height_);
+        AddSubKernel<<<GridFor(n), 256, 0, stream_>>>(cube_.residual.p[i], scratch.get(), false, n);
+        h_.launches += 2;
+      }
       LaunchIntegrate(linear, residual, n, dirty.get(), cube_.vec, stream_);
-      h_.launches += 4;
+      h_.launches += 2;
 
       while (max_components.size() > initial_components.size())
         initial_components.push_back(max_components[initial_components.size()]);
@@ -759,10 +1036,6 @@ float IuwtRun::PerformMajorIteration(uint64_t& iter_counter, uint64_t n_iter,
 
 // IuwtDeconvolution::ExecuteMajorIteration (iuwt_deconvolution.h:21-38)
 rdl_result RunIuwt(rdl_handle& h, DeviceCube& cube, cudaStream_t stream) {
-  if (cube.n_images != 1)
-    throw std::domain_error(
-        "IuwtDeconvolution on the device supports single-image cubes; the per-component refit of "
-        "joined images (PerformSubImageFitAll) is not built");
   h.trace_host.clear();
   IuwtRun run(h, cube, stream);
   uint64_t iteration_number = h.iteration_number;
