@@ -340,13 +340,45 @@ class MultiScaleRun {
   bool RunWithoutSubMinorLoop(size_t swp, float first_sub_iteration_threshold,
                               float initial_peak_value, PtrTable& conv_residual,
                               const ConstPtrTable& psf_per_image);
-  const float* ConvolvedPsf(size_t p, size_t si) const {
-    return Scales2()[si].scale == 0.0f ? base_psf_[p] : convolved_psfs_[p * st_.scales.size() + si].get();
+  // PSF of slot p convolved with the kernel of scale si. The per-channel ones are made when a
+  // scale is first selected (the reference convolves every PSF with every scale up front,
+  // multiscale_algorithm.cc:29-88; scales that are never selected never need theirs).
+  const float* ConvolvedPsf(size_t p, size_t si) {
+    if (Scales2()[si].scale == 0.0f) return base_psf_[p];
+    DeviceBuffer<float>& dst = convolved_psfs_[p * st_.scales.size() + si];
+    if (dst.empty()) {
+      dst.Reserve(n_);
+      conv_.ConvolveWith(base_psf_[p], width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0,
+                         stream_);
+    }
+    return dst.get();
   }
   const std::vector<rdl_scale_info>& Scales2() const { return st_.scales; }
   const float2* PsfSpectrum(size_t p, size_t si, FftConvolver& padded);
   const float* TwiceConvolvedPsf(size_t p, size_t si, const float2* scale_spectrum);
   void Sync() { RDL_CUDA(cudaStreamSynchronize(stream_)); }
+  // components of image i at scale si that still have to be transformed into the model; null
+  // when HBM is short (then the caller transforms at once, like the reference)
+  float* PendingModel(size_t image, size_t si) {
+    const auto key = std::make_pair(image, si);
+    auto it = pending_model_.find(key);
+    if (it != pending_model_.end()) return it->second.get();
+    if (DeviceAvailableBytes() < n_ * sizeof(float) * 4 + (size_t(16) << 30)) return nullptr;
+    DeviceBuffer<float> buf(n_);
+    RDL_CUDA(cudaMemsetAsync(buf.get(), 0, n_ * sizeof(float), stream_));
+    float* p = buf.get();
+    pending_model_.emplace(key, std::move(buf));
+    return p;
+  }
+  void FlushModelTransforms() {
+    for (auto& [key, buf] : pending_model_)
+      conv_.ConvolveWith(buf.get(), width_, height_, ScaleSpectrum(key.second), cube_.model.p[key.first],
+                         width_, height_, 2, stream_);
+    h_.launches += conv_.TakeLaunchCount();
+    if (!pending_model_.empty()) Sync();  // the buffers go back to the pool below
+    pending_model_.clear();
+  }
+  std::map<std::pair<size_t, size_t>, DeviceBuffer<float>> pending_model_;
   // host-memory calls upload the model planes on a second stream (abi.cu): wait for them before
   // the first kernel that touches the model
   void WaitForModel() {
@@ -524,6 +556,11 @@ void MultiScaleRun::ConvolvePsfs(size_t slot, const float* psf, bool is_integrat
       // per-channel PSFs: only the owner of the channel ever uses its convolved PSFs
       if (!is_integrated && !MineChannel(slot)) continue;
       DeviceBuffer<float>& dst = convolved_psfs_[slot * n_scales + si];
+      if (!is_integrated) {
+        // per-channel PSFs: on demand (ConvolvedPsf); slot 0 held the integrated PSF's until now
+        if (!cache_hit_) dst = DeviceBuffer<float>();
+        continue;
+      }
       if (!cache_hit_) {
         dst.Reserve(n_);
         conv_.ConvolveWith(psf, width_, height_, ScaleSpectrum(si), dst.get(), width_, height_, 0, stream_);
@@ -997,12 +1034,20 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
       // the corrected residual of this channel, for the joined peak search of all ranks: on its
       // way while the model transform below runs
       SharePlane(cube_.residual.p[i], rank_);
-      // model += Transform(full model, scale)  (multiscale_algorithm.cc:442-460)
-      if (S[swp].scale != 0.0f)
+      // model += Transform(full model, scale)  (multiscale_algorithm.cc:442-460). The transform
+      // is linear: the components of every minor iteration that picked this scale are collected
+      // per (image, scale) and transformed ONCE when the call ends (FlushModelTransforms),
+      // memory permitting -- one convolution per image and scale used instead of one per image and
+      // minor iteration. The model differs from the iteration-by-iteration sum by fp32 round-off
+      // only and feeds back into nothing (peaks come from the residual).
+      if (S[swp].scale == 0.0f) {
+        SubMinorAddModelTo(h, int(i), cube_.model.p[i], stream_);
+      } else if (float* pending = PendingModel(i, swp)) {
+        SubMinorAddModelTo(h, int(i), pending, stream_);
+      } else {
         conv_.ConvolveWith(scratch_.get(), width_, height_, ScaleSpectrum(swp), cube_.model.p[i], width_,
                            height_, 2, stream_);
-      else
-        SubMinorAddModelTo(h, int(i), cube_.model.p[i], stream_);
+      }
     }
     EndShare();
     h.launches += padded.TakeLaunchCount() + conv_.TakeLaunchCount();
@@ -1011,6 +1056,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     FindActiveScaleConvolvedMaxima(false);
     if (!SelectMaximumScale(swp)) {
       WaitForModel();
+      FlushModelTransforms();
       ShareImagePlanes(cube_.model.p);
       Sync();
       result.iteration_number = h.iteration_number;
@@ -1019,6 +1065,7 @@ rdl_result MultiScaleRun::Execute() {  // multiscale_algorithm.cc:183-576
     }
   }
   WaitForModel();
+  FlushModelTransforms();
   ShareImagePlanes(cube_.model.p);
 
   const bool max_iter_reached = h.iteration_number >= set.max_iterations;
