@@ -440,6 +440,27 @@ rdl_status rdl_iuwt_max_abs(rdl_handle* h, const float* device_image, uint64_t w
                             void* stream);
 
 /* utils::CalculateGoodFFTSize / GetConvolutionSize (cpp/utils/fft_size_calculations.h:15-50) */
+/* ---- local-RMS maps (cpp/math/rms_image.cc), the producer of the image that
+ * rdl_set_rms_factor_image consumes; device pointers ------------------------------------------
+ * SlidingMinimum / SlidingMaximum (rms_image.cc:39-84): separable minimum over the half-open
+ * windows [x - w/2, x + w/2) clipped to the image, exactly the reference's bounds. Out of place. */
+rdl_status rdl_rms_sliding_minimum(rdl_handle* h, const float* device_in, float* device_out,
+                                   uint64_t width, uint64_t height, uint64_t window_size,
+                                   int32_t maximum, void* stream);
+/* MakeRmsFactorImage (rms_image.cc:97-123), in place: value = (min / value)^strength for non-zero
+ * pixels (strength 0: all ones); *stddev = the minimum. Negative pixels: RDL_ERR_INVALID_ARGUMENT. */
+rdl_status rdl_rms_make_factor_image(rdl_handle* h, float* device_image, uint64_t n_pixels,
+                                     double local_rms_strength, double* stddev, void* stream);
+/* Make / MakeWithNegativityLimit (rms_image.cc:16-37, 86-95): sqrt(norm * (image^2 convolved with
+ * the Gaussian window)), optionally max'ed with |sliding minimum| * 0.3. The window is
+ * schaapcommon::math::RestoreImage in the reference (not in its tree): here a circular FFT
+ * convolution with a unit-peak elliptical Gaussian of FWHM beam * window_size, position angle
+ * (radians) from +y towards +x; that part is restated, not pinned. */
+rdl_status rdl_rms_make(rdl_handle* h, const float* device_in, float* device_out, uint64_t width,
+                        uint64_t height, double window_size, double beam_major, double beam_minor,
+                        double beam_pa, double pixel_scale_l, double pixel_scale_m,
+                        int32_t with_negativity_limit, void* stream);
+
 uint64_t rdl_good_fft_size(uint64_t minimum_size);
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);
 

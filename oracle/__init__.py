@@ -634,6 +634,26 @@ def iuwt_analysis():
     return _iuwt_analysis("orc_")
 
 
+def ref_rms_sliding_minimum(image, window, maximum=False):
+    """math::rms_image::SlidingMinimum / SlidingMaximum of the reference's own rms_image.cc."""
+    a = _f32(image)
+    out = np.empty_like(a)
+    f = ref_lib().ref_rms_sliding_minimum
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int]
+    f(_ptr(a), _ptr(out), a.shape[1], a.shape[0], int(window), int(maximum))
+    return out
+
+
+def ref_rms_make_factor_image(image, strength):
+    """math::rms_image::MakeRmsFactorImage -> (factor image, stddev)."""
+    a = _f32(image).copy()
+    f = ref_lib().ref_rms_make_factor_image
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_double]
+    f.restype = C.c_double
+    stddev = f(_ptr(a), a.shape[1], a.shape[0], float(strength))
+    return a, stddev
+
+
 def ref_iuwt_analysis():
     """The same five functions from the reference's own image_analysis.cc /
     iuwt_deconvolution_algorithm.cc compiled in oracle/_ref."""

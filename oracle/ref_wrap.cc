@@ -11,6 +11,7 @@
 #include "algorithms/iuwt/image_analysis.h"
 #include "algorithms/iuwt/iuwt_decomposition.h"
 #include "algorithms/iuwt/iuwt_mask.h"
+#include "math/rms_image.h"
 // Mad and GetMaxAbs are private members of the reference's class; the wrapper below needs them
 #define private public
 #include "algorithms/iuwt_deconvolution_algorithm.h"
@@ -269,5 +270,23 @@ float ref_iuwt_max_abs(const float* image, uint64_t w, uint64_t h, float clean_b
   *x = px;
   *y = py;
   return v;
+}
+// cpp/math/rms_image.cc: the sliding minimum / maximum and the RMS -> factor conversion
+void ref_rms_sliding_minimum(const float* in, float* out, uint64_t w, uint64_t h, uint64_t window,
+                             int maximum) {
+  aocommon::Image input(w, h), output;
+  std::copy_n(in, w * h, input.Data());
+  if (maximum)
+    math::rms_image::SlidingMaximum(output, input, window);
+  else
+    math::rms_image::SlidingMinimum(output, input, window);
+  std::copy_n(output.Data(), w * h, out);
+}
+double ref_rms_make_factor_image(float* image, uint64_t w, uint64_t h, double strength) {
+  aocommon::Image img(w, h);
+  std::copy_n(image, w * h, img.Data());
+  const double stddev = math::rms_image::MakeRmsFactorImage(img, strength);
+  std::copy_n(img.Data(), w * h, image);
+  return stddev;
 }
 }

@@ -95,7 +95,7 @@ EXPORTED_SYMBOLS = [
     "rdl_find_peak", "rdl_subtract_image", "rdl_integrate", "rdl_convolve",
     "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_static", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
-    "rdl_iuwt_max_abs",
+    "rdl_iuwt_max_abs", "rdl_rms_sliding_minimum", "rdl_rms_make_factor_image", "rdl_rms_make",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
     "rdl_parallel_facet_count", "rdl_parallel_facet_get",
     "rdl_parallel_timing",
@@ -677,6 +677,35 @@ class DeconvolutionAlgorithm:
                                                 threshold, int(use_abs), seed[0], seed[1],
                                                 C.byref(area), stream))
         return area.value
+
+    # -- local-RMS maps (cpp/math/rms_image.cc) -----------------------------------------
+    def rms_sliding_minimum(self, image, out, window_size, maximum=False, stream=None):
+        h, w = image.shape
+        f = lib().rdl_rms_sliding_minimum
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64,
+                      C.c_int32, C.c_void_p]
+        self._check(f(self._h, image.data_ptr(), out.data_ptr(), w, h, int(window_size),
+                      int(maximum), stream))
+
+    def rms_make_factor_image(self, image, local_rms_strength=1.0, stream=None) -> float:
+        """In place; returns the lowest RMS (MakeRmsFactorImage's return value)."""
+        f = lib().rdl_rms_make_factor_image
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.POINTER(C.c_double),
+                      C.c_void_p]
+        s = C.c_double()
+        self._check(f(self._h, image.data_ptr(), image.numel(), float(local_rms_strength),
+                      C.byref(s), stream))
+        return s.value
+
+    def rms_make(self, image, out, window_size, beam_major, beam_minor, beam_pa, pixel_scale_l,
+                 pixel_scale_m, with_negativity_limit=False, stream=None):
+        h, w = image.shape
+        f = lib().rdl_rms_make
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64] + \
+            [C.c_double] * 6 + [C.c_int32, C.c_void_p]
+        self._check(f(self._h, image.data_ptr(), out.data_ptr(), w, h, float(window_size),
+                      float(beam_major), float(beam_minor), float(beam_pa), float(pixel_scale_l),
+                      float(pixel_scale_m), int(with_negativity_limit), stream))
 
     def iuwt_mad(self, image, stream=None):
         """IuwtDeconvolutionAlgorithm::Mad (iuwt_deconvolution_algorithm.cc:104-110)."""

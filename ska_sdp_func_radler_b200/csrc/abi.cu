@@ -12,6 +12,7 @@
 #include "parallel.cuh"
 #include "handle.h"
 #include "multiscale.cuh"
+#include "rms_image.cuh"
 
 using namespace rdl;
 
@@ -932,6 +933,40 @@ rdl_status rdl_iuwt_decompose_aliased(rdl_handle* h, float* device_x, uint64_t w
     RDL_CUDA(cudaSetDevice(h->device));
     IuwtDecomposeAliased(*h, device_x, width, height, n_scales, device_coefficients,
                          StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_rms_sliding_minimum(rdl_handle* h, const float* device_in, float* device_out,
+                                   uint64_t width, uint64_t height, uint64_t window_size,
+                                   int32_t maximum, void* stream_v) {
+  if (!h || !device_in || !device_out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    RmsSlidingMinimum(*h, device_in, device_out, width, height, window_size, maximum != 0,
+                      StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_rms_make_factor_image(rdl_handle* h, float* device_image, uint64_t n_pixels,
+                                     double local_rms_strength, double* stddev, void* stream_v) {
+  if (!h || !device_image) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    const double s = RmsMakeFactorImage(*h, device_image, n_pixels, local_rms_strength,
+                                        StreamOf(h, stream_v));
+    if (stddev) *stddev = s;
+  });
+}
+
+rdl_status rdl_rms_make(rdl_handle* h, const float* device_in, float* device_out, uint64_t width,
+                        uint64_t height, double window_size, double beam_major, double beam_minor,
+                        double beam_pa, double pixel_scale_l, double pixel_scale_m,
+                        int32_t with_negativity_limit, void* stream_v) {
+  if (!h || !device_in || !device_out) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    RmsMake(*h, device_in, device_out, width, height, window_size, beam_major, beam_minor, beam_pa,
+            pixel_scale_l, pixel_scale_m, with_negativity_limit != 0, StreamOf(h, stream_v));
   });
 }
 

@@ -207,6 +207,9 @@ struct rdl_handle {
   rdl::DistContext dist;
   rdl::DeviceBuffer<rdl::DistCandidate> cand_local, cand_all;
   rdl::DeviceBuffer<unsigned char> persist_scratch;  // HogbomPersistentKernel: barrier + candidates
+  // local-RMS maps (rms_image.cu)
+  rdl::DeviceBuffer<float> rms_temp, rms_kernel, rms_min;
+  rdl::DeviceBuffer<unsigned> rms_scalar;
   // component log of a host-memory GenericClean call (clean_kernels.cuh, HogbomParams::log_*)
   bool model_log = false;        // set by the caller of RunGenericClean for this call
   uint64_t model_log_count = 0;  // components recorded by the call
