@@ -532,17 +532,31 @@ rdl_status ExecuteImpl(rdl_handle* h, const rdl_cube_desc* c, float* const* resi
       for (size_t i = 0; staged && i != n_psf_planes; ++i) staged = h->staged_psf_ptrs[i] == psfs[i];
       // new pixels under the same staging addresses: what multiscale kept of the old ones goes
       if (!staged && h->ms) MultiScaleInvalidatePsfCache(*h->ms);
+      // Row-sharded runs: every rank is handed the same full-frame PSFs. Each plane crosses PCIe
+      // on ONE rank (plane i on rank i % world) and reaches the others over NVLink, so the PSF
+      // upload of the job is one copy of the PSFs instead of one per GPU.
+      const bool share_upload = sharded && h->dist.comm && h->dist.world > 1 && !dd.n_dd;
+      std::vector<float*> shared_planes;
+      std::vector<int> shared_roots;
       for (size_t i = 0; i != n_psf_planes; ++i) {
         float* dst = h->stage_psf.get() + i * psf_n;
-        if (!staged) {
+        const int root = share_upload ? int(i % size_t(h->dist.world)) : h->dist.rank;
+        if (!staged && root == h->dist.rank) {
           PinPlane(h, psfs[i], psf_bytes);
           RDL_CUDA(cudaMemcpyAsync(dst, psfs[i], psf_bytes, cudaMemcpyHostToDevice, stream));
+        }
+        if (!staged && share_upload) {
+          shared_planes.push_back(dst);
+          shared_roots.push_back(root);
         }
         if (dd.n_dd)
           cube.dd_psfs.push_back(dst);
         else
           cube.psf.p[i] = dst;
       }
+      if (!shared_planes.empty())
+        NcclBroadcastPlanes(h->dist, shared_planes.data(), shared_roots.data(), shared_planes.size(),
+                            psf_n, stream);
       h->staged_psf_ptrs.assign(psfs, psfs + n_psf_planes);
       h->staged_psf_pixels = psf_n;
       if (model_behind) {

@@ -10,8 +10,15 @@ namespace rdl {
 namespace fast {
 namespace {
 
-template <int RA, int RB, int RC, int MINB>
-__global__ void __launch_bounds__(128, MINB)
+// T threads: enough for the pair pass (ra * rb / 2 + 1 tasks per row) to finish in ONE round. With
+// the plan's 128 threads a 4096-point row has 129 pair tasks: one thread ran a second round
+// alone while the CTA waited at the barrier (ncu source page of RowInverseSpecKernel<16,16,16>:
+// 17 % of the samples on that barrier, profiles/r02_ncu_rowinverse_8192_source.txt). Worth 2-3 %
+// per convolution where 160 threads do it (129-145 pair tasks); 192 threads for the 163-169 pair
+// tasks of 9072 / 9408 cost more occupancy than the second round (measured +9 %), so those stay
+// at 128.
+template <int RA, int RB, int RC, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB)
     RowForwardSpecKernel(const __grid_constant__ RowPlan p, const __grid_constant__ RowIo io) {
   extern __shared__ __align__(16) float2 smem[];
   const int row0 = blockIdx.x * p.rows_per_cta;
@@ -23,8 +30,8 @@ __global__ void __launch_bounds__(128, MINB)
   RowForwardPass3<RC>(p, io, smem, row0, n_rows, threadIdx.x, blockDim.x);
 }
 
-template <int RA, int RB, int RC, int MINB>
-__global__ void __launch_bounds__(128, MINB)
+template <int RA, int RB, int RC, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB)
     RowInverseSpecKernel(const __grid_constant__ RowPlan p, const __grid_constant__ RowIo io) {
   extern __shared__ __align__(16) float2 smem[];
   const int row0 = blockIdx.x * p.rows_per_cta;
@@ -84,12 +91,12 @@ void AllowSharedMemory(K kernel, size_t smem) {
     RDL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
 }
 
-// (ra, rb, rc, CTAs per SM the register budget is cut for)
-#define RDL_ROW_SPECS(X)                                                                           \
-  X(16, 16, 16, 6) /* 8192 */ X(16, 16, 8, 6) /* 4096 */ X(18, 16, 16, 5) /* 9216 */               \
-  X(21, 16, 14, 4) /* 9408 */ X(14, 14, 12, 6) /* 4704 */ X(16, 16, 9, 6) /* 4608 */               \
-  X(18, 15, 9, 5) /* 4860 */ X(18, 18, 7, 5) /* 4536 */ X(18, 18, 14, 5) /* 9072 */                \
-  X(16, 16, 4, 6) /* 2048 */
+// (ra, rb, rc, threads, CTAs per SM the register budget is cut for)
+#define RDL_ROW_SPECS(X)                                                                            \
+  X(16, 16, 16, 160, 5) /* 8192 */ X(16, 16, 8, 160, 5) /* 4096 */ X(18, 16, 16, 160, 4) /* 9216 */ \
+  X(21, 16, 14, 128, 4) /* 9408 */ X(14, 14, 12, 128, 6) /* 4704 */ X(16, 16, 9, 160, 5) /* 4608 */ \
+  X(18, 15, 9, 160, 4) /* 4860 */ X(18, 18, 7, 128, 5) /* 4536 */ X(18, 18, 14, 128, 5) /* 9072 */  \
+  X(16, 16, 4, 128, 6) /* 2048 */
 // (H2, CTAs per SM)
 #define RDL_STRIDED_SPECS(X) X(16, 6) X(18, 6) X(21, 5) X(24, 4) X(28, 4) X(32, 4)
 // (ra, rb, CTAs per SM)
@@ -132,10 +139,11 @@ bool LaunchWholeColumnSpec(bool convolve, const WholePlan& p, const ColIo& io, i
 
 bool LaunchRowForwardSpec(const RowPlan& p, const RowIo& io, int grid, int threads, size_t smem,
                           cudaStream_t stream) {
-#define X(A, B, C, M)                                                             \
+#define X(A, B, C, T, M)                                                          \
   if (p.ra == A && p.rb == B && p.rc == C) {                                      \
-    AllowSharedMemory(RowForwardSpecKernel<A, B, C, M>, smem);                    \
-    RowForwardSpecKernel<A, B, C, M><<<grid, threads, smem, stream>>>(p, io);     \
+    AllowSharedMemory(RowForwardSpecKernel<A, B, C, T, M>, smem);                 \
+    RowForwardSpecKernel<A, B, C, T, M>                                           \
+        <<<grid, p.rows_per_cta == 1 ? T : threads, smem, stream>>>(p, io);       \
     return true;                                                                  \
   }
   RDL_ROW_SPECS(X)
@@ -145,10 +153,11 @@ bool LaunchRowForwardSpec(const RowPlan& p, const RowIo& io, int grid, int threa
 
 bool LaunchRowInverseSpec(const RowPlan& p, const RowIo& io, int grid, int threads, size_t smem,
                           cudaStream_t stream) {
-#define X(A, B, C, M)                                                             \
+#define X(A, B, C, T, M)                                                          \
   if (p.ra == A && p.rb == B && p.rc == C) {                                      \
-    AllowSharedMemory(RowInverseSpecKernel<A, B, C, M>, smem);                    \
-    RowInverseSpecKernel<A, B, C, M><<<grid, threads, smem, stream>>>(p, io);     \
+    AllowSharedMemory(RowInverseSpecKernel<A, B, C, T, M>, smem);                 \
+    RowInverseSpecKernel<A, B, C, T, M>                                           \
+        <<<grid, p.rows_per_cta == 1 ? T : threads, smem, stream>>>(p, io);       \
     return true;                                                                  \
   }
   RDL_ROW_SPECS(X)

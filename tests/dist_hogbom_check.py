@@ -64,6 +64,23 @@ for (n, c, iters, fit, block) in [(256, 1, 150, False, 0), (192, 3, 120, False, 
         print(f"rank {rank}: MISMATCH case n={n} c={c} fit={fit} block={block}: iterations "
               f"{g.iteration_number} vs {o.iteration_number}", flush=True)
     ok = ok and good
+    # the same run through HOST buffers: every rank passes its rows and the full PSFs; each PSF
+    # plane is uploaded by one rank and broadcast (abi.cu). Two calls, the second with the PSFs
+    # kept on the device.
+    h_res = np.ascontiguousarray(res[:, rows])
+    h_model = np.zeros_like(h_res)
+    alg.set_iteration_number(0)
+    alg.set_psfs_constant(True)
+    band_cube = rdl.Cube(n, len(rows), c, 1, weights)
+    alg.apply(max_iterations=iters // 2, clean_border_ratio=0.02, trace_capacity=iters)
+    alg.execute_major_iteration(band_cube, h_res, h_model, psfs)
+    alg.apply(max_iterations=iters, clean_border_ratio=0.02, trace_capacity=iters)
+    g2 = alg.execute_major_iteration(band_cube, h_res, h_model, psfs)
+    good = (g2.iteration_number == o.iteration_number and np.array_equal(h_res, o_res[:, rows]) and
+            np.array_equal(h_model, o_model[:, rows]))
+    if not good:
+        print(f"rank {rank}: HOST-BUFFER MISMATCH case n={n} c={c} fit={fit} block={block}", flush=True)
+    ok = ok and good
     alg.dist_finalize()
 flag = torch.tensor([1 if ok else 0], device=dev)
 if world > 1:
