@@ -55,3 +55,28 @@ def test_fails_loudly_without_gpu(rdl):
         rdl.GenericClean()
     assert e.value.status == rdl.RDL_ERR_NO_DEVICE
     assert "no CPU fallback" in str(e.value)
+
+
+def test_plane_pointer_tables():
+    """Cubes are passed as one contiguous [n, H, W] array or as a list of separately allocated
+    planes (what an ImageSet of aocommon::Images is); both give the same pointer table."""
+    import ctypes
+
+    import numpy as np
+
+    import ska_sdp_func_radler_b200 as rdl
+    cube = np.arange(3 * 4 * 5, dtype=np.float32).reshape(3, 4, 5)
+    table, space = rdl._plane_pointers(cube, 3, 20)
+    assert space == rdl.MEM_HOST
+    assert [table[i] for i in range(3)] == [cube.ctypes.data + i * 80 for i in range(3)]
+    planes = [np.ascontiguousarray(cube[i]) for i in range(3)]
+    table2, space2 = rdl._plane_pointers(planes, 3, 20)
+    assert space2 == rdl.MEM_HOST
+    assert [table2[i] for i in range(3)] == [p.ctypes.data for p in planes]
+    for i in range(3):  # the table really addresses the planes
+        first = ctypes.cast(table2[i], ctypes.POINTER(ctypes.c_float))[0]
+        assert first == planes[i][0, 0]
+    with pytest.raises(ValueError):
+        rdl._plane_pointers(planes[:2], 3, 20)
+    with pytest.raises(ValueError):
+        rdl._plane_pointers([p.astype(np.float64) for p in planes], 3, 20)
