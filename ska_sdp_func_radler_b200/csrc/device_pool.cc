@@ -20,8 +20,18 @@ struct Pool {
   std::mutex lock;
   std::map<std::pair<int, size_t>, std::vector<void*>> blocks;
   size_t cached_bytes = 0;
+  // Three quarters of the device's memory unless RDL_POOL_MAX_GB says otherwise (135 GB on a
+  // B200). A K4 multiscale call holds ~110 GB of planes and spectra; with the earlier fixed cap of
+  // 96 GB the surplus went back to the driver at the end of every call and was allocated again in
+  // the next, at 0.4 s for some calls and nothing for others (which blocks stayed was a matter
+  // of release order): major iterations of 390 and 800-900 ms alternated in one process.
   size_t max_cached_bytes = size_t(96) << 30;
   Pool() {
+    size_t free_bytes = 0, total_bytes = 0;
+    if (cudaMemGetInfo(&free_bytes, &total_bytes) == cudaSuccess && total_bytes > 0)
+      max_cached_bytes = total_bytes / 4 * 3;
+    else
+      cudaGetLastError();
     if (const char* gb = std::getenv("RDL_POOL_MAX_GB")) max_cached_bytes = size_t(std::atof(gb) * double(1 << 30));
   }
 };

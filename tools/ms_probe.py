@@ -21,7 +21,7 @@ if c > 1:
     alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, freqs, weights, 1)
 cube = rdl.Cube(n, n, c, 1, weights)
 stream = torch.cuda.current_stream().cuda_stream
-for rep in range(2):
+for rep in range(int(sys.argv[4]) if len(sys.argv) > 4 else 2):
     res = res0.clone()
     model = torch.zeros_like(res)
     alg.set_iteration_number(0)
