@@ -461,6 +461,29 @@ rdl_status rdl_rms_make(rdl_handle* h, const float* device_in, float* device_out
                         double beam_pa, double pixel_scale_l, double pixel_scale_m,
                         int32_t with_negativity_limit, void* stream);
 
+/* ---- the steps of Radler::Perform either side of ExecuteMajorIteration,
+ * for a caller that keeps the cube in device memory between major iterations. Device pointers
+ * only; `device_inputs` / `device_outputs` / `device_models` are host arrays of device pointers. */
+/* integrated.MedianAndStdDevFromMAD() (radler.cc:162-169; aocommon, restated): median of the
+ * finite pixels and 1.4826 x the median of |pixel - median|; n_finite = pixels that took part
+ * (0: both results 0). Any output pointer may be null. Synchronises the stream. */
+rdl_status rdl_median_and_stddev_from_mad(rdl_handle* h, const float* device_image,
+                                         uint64_t n_pixels, float* median, float* stddev,
+                                         uint64_t* n_finite, void* stream);
+/* ImageSet::LoadAndAverage (image_set.cc:105-140) after the loads: output[output_index[i]] +=
+ * input[i] * weights[i] in the order given (weight 0: input not read), then every output is
+ * scaled by 1 / (sum of its weights). The reference's order is: per deconvolution channel, its
+ * original channels in turn, polarisations innermost; output_index = channel * n_pol + pol. */
+rdl_status rdl_load_and_average(rdl_handle* h, const float* const* device_inputs,
+                                const double* weights, const uint32_t* output_index,
+                                uint64_t n_inputs, float* const* device_outputs,
+                                uint64_t n_outputs, uint64_t n_pixels, void* stream);
+/* The auto-mask derived from the model planes when the second auto-masking phase starts
+ * (radler.cc:254-266): mask = 1 where any model plane is finite and non-zero, else 0. */
+rdl_status rdl_auto_mask_from_model(rdl_handle* h, const float* const* device_models,
+                                    uint64_t n_models, uint8_t* device_mask, uint64_t n_pixels,
+                                    void* stream);
+
 uint64_t rdl_good_fft_size(uint64_t minimum_size);
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);
 

@@ -654,6 +654,37 @@ def ref_rms_make_factor_image(image, strength):
     return a, stddev
 
 
+def ref_load_and_average(inputs, weights, n_pol, n_deconvolution):
+    """ImageSet::LoadAndAverage(true) of the reference's own image_set.cc: `inputs` is
+    [original channel][pol] planes (shape (n_original * n_pol, h, w)), `weights` one per plane;
+    returns (n_deconvolution * n_pol, h, w)."""
+    a = _f32(inputs)
+    n_in, h, w = a.shape
+    n_original = n_in // n_pol
+    wts = np.ascontiguousarray(weights, np.float64)
+    out = np.zeros((min(n_deconvolution, n_original) * n_pol, h, w), np.float32)
+    in_ptrs = (C.c_void_p * n_in)(*[a[i].ctypes.data for i in range(n_in)])
+    out_ptrs = (C.c_void_p * len(out))(*[out[i].ctypes.data for i in range(len(out))])
+    f = ref_lib().refa_load_and_average
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
+                  C.c_uint64, C.c_void_p]
+    if f(in_ptrs, wts.ctypes.data, n_original, n_pol, n_deconvolution, w, h, out_ptrs) != 0:
+        raise RuntimeError("refa_load_and_average failed")
+    return out
+
+
+def ref_median_and_stddev_from_mad(image):
+    """aocommon::Image::MedianAndStdDevFromMAD, the stand-in of oracle/ref_shim (aocommon is not
+    in the reference tree: restated, unpinned) -> (median, stddev) as float32."""
+    a = _f32(image).ravel()
+    m, s = C.c_float(), C.c_float()
+    f = ref_lib().refa_median_and_stddev_from_mad
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(_ptr(a), a.size, C.byref(m), C.byref(s))
+    return np.float32(m.value), np.float32(s.value)
+
+
 def ref_iuwt_analysis():
     """The same five functions from the reference's own image_analysis.cc /
     iuwt_deconvolution_algorithm.cc compiled in oracle/_ref."""

@@ -422,3 +422,63 @@ int refa_component_get(void* handle, uint64_t scale, uint64_t i, uint64_t* x, ui
 }
 
 }  // extern "C"
+
+// ---- Radler::Perform's steps either side of ExecuteMajorIteration ----------------------------
+namespace {
+// residual accessor over a caller's plane
+class MemoryAccessor final : public aocommon::ImageAccessor {
+ public:
+  MemoryAccessor(const float* data, size_t w, size_t h) : data_(data), w_(w), h_(h) {}
+  size_t Width() const override { return w_; }
+  size_t Height() const override { return h_; }
+  void Load(float* data) const override { std::memcpy(data, data_, w_ * h_ * sizeof(float)); }
+  void Store(const float*) override { throw std::runtime_error("read-only accessor"); }
+
+ private:
+  const float* data_;
+  size_t w_, h_;
+};
+}  // namespace
+
+extern "C" {
+// ImageSet::LoadAndAverage(true) (image_set.cc:105-140) on a work table of n_original channels x
+// n_pol polarisations averaged to n_deconvolution channels; inputs[channel * n_pol + pol],
+// weights per entry in the same order; outputs[deconvolution channel * n_pol + pol].
+int refa_load_and_average(const float* const* inputs, const double* weights, uint64_t n_original,
+                          uint64_t n_pol, uint64_t n_deconvolution, uint64_t width,
+                          uint64_t height, float* const* outputs) {
+  return Guard(nullptr, [&] {
+    static const aocommon::PolarizationEnum kPols[4] = {
+        aocommon::PolarizationEnum::StokesI, aocommon::PolarizationEnum::StokesQ,
+        aocommon::PolarizationEnum::StokesU, aocommon::PolarizationEnum::StokesV};
+    WorkTable table(std::vector<PsfOffset>{}, n_original, n_deconvolution);
+    for (size_t ch = 0; ch != n_original; ++ch) {
+      for (size_t p = 0; p != n_pol; ++p) {
+        auto e = std::make_unique<WorkTableEntry>();
+        e->band_start_frequency = e->band_end_frequency = 1.0e8 + 1.0e6 * ch;
+        e->polarization = kPols[p % 4];
+        e->original_channel_index = ch;
+        e->image_weight = weights[ch * n_pol + p];
+        e->model_accessor = std::make_unique<UnusedAccessor>();
+        e->residual_accessor =
+            std::make_unique<MemoryAccessor>(inputs[ch * n_pol + p], width, height);
+        if (p == 0) e->psf_accessors.emplace_back(std::make_unique<UnusedAccessor>());
+        table.AddEntry(std::move(e));
+      }
+    }
+    ImageSet set(table, false, {}, width, height);
+    set.LoadAndAverage(true);
+    for (size_t i = 0; i != set.Size(); ++i)
+      std::memcpy(outputs[i], set[i].Data(), width * height * sizeof(float));
+  });
+}
+
+// integrated.MedianAndStdDevFromMAD() (radler.cc:165-166): the aocommon stand-in of ref_shim
+void refa_median_and_stddev_from_mad(const float* image, uint64_t n, float* median, float* stddev) {
+  aocommon::Image img(n, 1);
+  std::memcpy(img.Data(), image, n * sizeof(float));
+  const std::pair<float, float> r = img.MedianAndStdDevFromMAD();
+  *median = r.first;
+  *stddev = r.second;
+}
+}  // extern "C"

@@ -96,6 +96,7 @@ EXPORTED_SYMBOLS = [
     "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_static", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs", "rdl_rms_sliding_minimum", "rdl_rms_make_factor_image", "rdl_rms_make",
+    "rdl_median_and_stddev_from_mad", "rdl_load_and_average", "rdl_auto_mask_from_model",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
     "rdl_parallel_facet_count", "rdl_parallel_facet_get",
     "rdl_parallel_timing",
@@ -706,6 +707,40 @@ class DeconvolutionAlgorithm:
         self._check(f(self._h, image.data_ptr(), out.data_ptr(), w, h, float(window_size),
                       float(beam_major), float(beam_minor), float(beam_pa), float(pixel_scale_l),
                       float(pixel_scale_m), int(with_negativity_limit), stream))
+
+    def median_and_stddev_from_mad(self, image, stream=None):
+        """integrated.MedianAndStdDevFromMAD() of Radler::Perform (radler.cc:162-169) on a device
+        plane -> (median, stddev, n_finite)."""
+        f = lib().rdl_median_and_stddev_from_mad
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                      C.c_void_p]
+        m, s, n = C.c_float(), C.c_float(), C.c_uint64()
+        self._check(f(self._h, image.data_ptr() if image.numel() else None, image.numel(),
+                      C.byref(m), C.byref(s), C.byref(n), stream))
+        return m.value, s.value, n.value
+
+    def load_and_average(self, inputs, weights, output_index, outputs, stream=None):
+        """ImageSet::LoadAndAverage (image_set.cc:105-140) with the planes already on the device:
+        `inputs` / `outputs` are sequences of equally sized device planes."""
+        n_in, n_out = len(inputs), len(outputs)
+        in_ptrs = (C.c_void_p * max(n_in, 1))(*[t.data_ptr() for t in inputs])
+        out_ptrs = (C.c_void_p * max(n_out, 1))(*[t.data_ptr() for t in outputs])
+        w = (C.c_double * max(n_in, 1))(*[float(v) for v in weights])
+        idx = (C.c_uint32 * max(n_in, 1))(*[int(v) for v in output_index])
+        f = lib().rdl_load_and_average
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                      C.c_uint64, C.c_uint64, C.c_void_p]
+        n_pixels = outputs[0].numel() if n_out else 0
+        self._check(f(self._h, in_ptrs, w, idx, n_in, out_ptrs, n_out, n_pixels, stream))
+
+    def auto_mask_from_model(self, models, mask, stream=None):
+        """The auto-mask Radler::Perform derives from the model planes (radler.cc:254-266):
+        `mask` (uint8 device plane) = 1 where any of `models` is finite and non-zero."""
+        n = len(models)
+        ptrs = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in models])
+        f = lib().rdl_auto_mask_from_model
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
+        self._check(f(self._h, ptrs, n, mask.data_ptr(), mask.numel(), stream))
 
     def iuwt_mad(self, image, stream=None):
         """IuwtDeconvolutionAlgorithm::Mad (iuwt_deconvolution_algorithm.cc:104-110)."""

@@ -12,6 +12,7 @@
 #include "parallel.cuh"
 #include "handle.h"
 #include "multiscale.cuh"
+#include "image_statistics.cuh"
 #include "rms_image.cuh"
 
 using namespace rdl;
@@ -1037,6 +1038,43 @@ rdl_status rdl_iuwt_floodfill_2d(rdl_handle* h, const float* device_image, uint8
     RDL_CUDA(cudaSetDevice(h->device));
     *area_size = IuwtFloodfill2D(*h, device_image, device_mask, width, height, threshold,
                                  use_abs != 0, seed_x, seed_y, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_median_and_stddev_from_mad(rdl_handle* h, const float* device_image,
+                                         uint64_t n_pixels, float* median, float* stddev,
+                                         uint64_t* n_finite, void* stream_v) {
+  if (!h || (!device_image && n_pixels)) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    const MadStatistics s =
+        ImageMedianAndStdDevFromMad(*h, device_image, n_pixels, StreamOf(h, stream_v));
+    if (median) *median = s.median;
+    if (stddev) *stddev = s.stddev;
+    if (n_finite) *n_finite = s.n_finite;
+  });
+}
+
+rdl_status rdl_load_and_average(rdl_handle* h, const float* const* device_inputs,
+                                const double* weights, const uint32_t* output_index,
+                                uint64_t n_inputs, float* const* device_outputs,
+                                uint64_t n_outputs, uint64_t n_pixels, void* stream_v) {
+  if (!h || !device_outputs || (n_inputs && (!device_inputs || !weights || !output_index)))
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    ImageLoadAndAverage(*h, device_inputs, weights, output_index, n_inputs, device_outputs,
+                        n_outputs, n_pixels, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_auto_mask_from_model(rdl_handle* h, const float* const* device_models,
+                                    uint64_t n_models, uint8_t* device_mask, uint64_t n_pixels,
+                                    void* stream_v) {
+  if (!h || !device_mask || (n_models && !device_models)) return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    ImageMaskFromModel(*h, device_models, n_models, device_mask, n_pixels, StreamOf(h, stream_v));
   });
 }
 

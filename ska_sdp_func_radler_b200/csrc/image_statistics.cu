@@ -1,0 +1,352 @@
+// The steps of Radler::Perform either side of ExecuteMajorIteration, on the device (SURVEY 8(f),
+// rank 1), so that a caller holding the cube in device memory need not bring a plane back for them:
+//   radler.cc:162-169   integrated.MedianAndStdDevFromMAD()  -> ImageMedianAndStdDevFromMad
+//   image_set.cc:105-140 ImageSet::LoadAndAverage            -> ImageLoadAndAverage
+//   radler.cc:254-266   auto-mask from the model images      -> ImageMaskFromModel
+// MedianAndStdDevFromMAD is aocommon's (third-party, absent from the tree): restated as the
+// median over the finite pixels ((lower + upper middle) * 0.5 for an even count), then
+// 1.4826 x the same median of |pixel - median| -- oracle/ref_shim/aocommon/image.h holds the same
+// restatement; that part of the parity is UNPINNED. Order statistics have one right answer, so
+// the radix select below returns the very float std::nth_element leaves in place.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+#include "handle.h"
+#include "image_statistics.cuh"
+#include "iuwt.cuh"
+
+namespace rdl {
+namespace {
+
+// ---- exact selection: three histogram passes over the 32 key bits (11 + 11 + 10) -------------
+
+// h.iuwt_scalars words used here (the IUWT entry points use the same scratch; calls on one
+// handle are ordered): [2] key prefix found so far, [3] rank left inside it, [5] finite pixels;
+// the histogram sits at kIuwtHistWord (2048 unsigned).
+constexpr int kPrefixWord = 2, kRankWord = 3, kCountWord = 5;
+
+struct SelectPass {
+  int shift, bits, prefix_shift;  // bin = (key >> shift) & mask; prefix = key >> prefix_shift
+  int deviation;                  // 0: key orders the pixel itself; 1: |pixel - centre|
+  float centre;
+};
+
+// larger float <=> larger unsigned
+__device__ __forceinline__ unsigned OrderedBits(float v) {
+  const unsigned u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__device__ __forceinline__ void Count(float v, const SelectPass& pass, unsigned prefix, unsigned mask,
+                                      unsigned* bins) {
+  if ((__float_as_uint(v) & 0x7f800000u) == 0x7f800000u) return;  // std::isfinite
+  const unsigned key = pass.deviation ? __float_as_uint(fabsf(v - pass.centre)) : OrderedBits(v);
+  if (pass.prefix_shift < 32 && (key >> pass.prefix_shift) != prefix) return;
+  atomicAdd(&bins[(key >> pass.shift) & mask], 1u);
+}
+
+__global__ void __launch_bounds__(512)
+SelectHistogramKernel(const float* __restrict__ image, size_t n, SelectPass pass,
+                      const unsigned long long* __restrict__ scalars, unsigned* histogram) {
+  __shared__ unsigned bins[2048];
+  for (int i = threadIdx.x; i < 2048; i += blockDim.x) bins[i] = 0;
+  __syncthreads();
+  const unsigned prefix = unsigned(scalars[kPrefixWord]);
+  const unsigned mask = (1u << pass.bits) - 1u;
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  const size_t first = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if ((reinterpret_cast<uintptr_t>(image) & 15) == 0) {
+    const float4* image4 = reinterpret_cast<const float4*>(image);
+    for (size_t i = first; i < n / 4; i += stride) {
+      const float4 v = __ldg(image4 + i);
+      Count(v.x, pass, prefix, mask, bins);
+      Count(v.y, pass, prefix, mask, bins);
+      Count(v.z, pass, prefix, mask, bins);
+      Count(v.w, pass, prefix, mask, bins);
+    }
+    for (size_t i = n / 4 * 4 + first; i < n; i += stride) Count(image[i], pass, prefix, mask, bins);
+  } else {
+    for (size_t i = first; i < n; i += stride) Count(image[i], pass, prefix, mask, bins);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2048; i += blockDim.x)
+    if (bins[i]) atomicAdd(&histogram[i], bins[i]);
+}
+
+// One warp: finds the bin holding the wanted rank, appends it to the prefix, clears the
+// histogram. With upper_middle set (first pass of the first selection) the rank is count / 2 of
+// the pixels counted, and the count is kept for the host.
+__global__ void SelectNarrowKernel(unsigned long long* scalars, unsigned* histogram, int bits,
+                                   int upper_middle) {
+  __shared__ unsigned long long chunk_sum[32];
+  const int lane = threadIdx.x;
+  const int n_bins = 1 << bits, per = (n_bins + 31) / 32;
+  unsigned long long sum = 0;
+  for (int b = lane * per; b < min(n_bins, (lane + 1) * per); ++b) sum += histogram[b];
+  chunk_sum[lane] = sum;
+  __syncwarp();
+  if (lane == 0) {
+    unsigned long long rank = scalars[kRankWord];
+    if (upper_middle) {
+      unsigned long long total = 0;
+      for (int c = 0; c < 32; ++c) total += chunk_sum[c];
+      scalars[kCountWord] = total;
+      rank = total / 2;
+    }
+    int c = 0;
+    while (c < 31 && rank >= chunk_sum[c]) rank -= chunk_sum[c++];
+    int b = c * per;
+    while (b < n_bins - 1 && rank >= histogram[b]) rank -= histogram[b++];
+    scalars[kPrefixWord] = (scalars[kPrefixWord] << bits) | unsigned(b);
+    scalars[kRankWord] = rank;
+  }
+  __syncwarp();
+  for (int b = lane; b < 2048; b += 32) histogram[b] = 0;
+}
+
+struct Selected {
+  unsigned key;
+  uint64_t n_finite;
+};
+
+// The key of rank `rank` among the finite pixels (rank < 0: the upper middle, counted here).
+Selected Select(rdl_handle& h, const float* image, size_t n, int deviation, float centre,
+                long long rank, cudaStream_t stream) {
+  h.iuwt_scalars.Reserve(kIuwtScalarWords);
+  unsigned long long* scalars = h.iuwt_scalars.get();
+  unsigned* histogram = reinterpret_cast<unsigned*>(scalars + kIuwtHistWord);
+  RDL_CUDA(cudaMemsetAsync(scalars, 0, kIuwtScalarWords * sizeof(unsigned long long), stream));
+  if (rank >= 0) {
+    const unsigned long long r = static_cast<unsigned long long>(rank);
+    RDL_CUDA(cudaMemcpyAsync(scalars + kRankWord, &r, sizeof(r), cudaMemcpyHostToDevice, stream));
+  }
+  const SelectPass passes[3] = {{21, 11, 32, deviation, centre},
+                                {10, 11, 21, deviation, centre},
+                                {0, 10, 10, deviation, centre}};
+  const unsigned grid = unsigned(std::min<size_t>((n / 4 + 511) / 512 + 1, size_t(kSmCount) * 4));
+  for (int p = 0; p != 3; ++p) {
+    SelectHistogramKernel<<<grid, 512, 0, stream>>>(image, n, passes[p], scalars, histogram);
+    SelectNarrowKernel<<<1, 32, 0, stream>>>(scalars, histogram, passes[p].bits,
+                                             p == 0 && rank < 0);
+  }
+  RDL_CUDA(cudaGetLastError());
+  unsigned long long back[4] = {0, 0, 0, 0};  // words 2..5
+  RDL_CUDA(cudaMemcpyAsync(back, scalars + kPrefixWord, sizeof(back), cudaMemcpyDeviceToHost, stream));
+  RDL_CUDA(cudaStreamSynchronize(stream));
+  return {unsigned(back[0]), back[kCountWord - kPrefixWord]};
+}
+
+float FromBits(unsigned bits) {
+  float v;
+  static_assert(sizeof(v) == sizeof(bits), "float is 32 bits");
+  std::memcpy(&v, &bits, sizeof(v));
+  return v;
+}
+float FromOrderedBits(unsigned key) {
+  return FromBits((key & 0x80000000u) ? (key ^ 0x80000000u) : ~key);
+}
+
+// median of the finite pixels (deviation = 0) or of |pixel - centre| (deviation = 1)
+float Median(rdl_handle& h, const float* image, size_t n, int deviation, float centre,
+             uint64_t& n_finite, cudaStream_t stream) {
+  const Selected upper = Select(h, image, n, deviation, centre,
+                                n_finite ? static_cast<long long>(n_finite / 2) : -1, stream);
+  if (!n_finite) n_finite = upper.n_finite;
+  if (!n_finite) return 0.0f;
+  const float hi = deviation ? FromBits(upper.key) : FromOrderedBits(upper.key);
+  if (n_finite % 2 == 1) return hi;
+  const Selected lower = Select(h, image, n, deviation, centre,
+                                static_cast<long long>(n_finite / 2) - 1, stream);
+  const float lo = deviation ? FromBits(lower.key) : FromOrderedBits(lower.key);
+  return (lo + hi) * 0.5f;
+}
+
+}  // namespace
+
+MadStatistics ImageMedianAndStdDevFromMad(rdl_handle& h, const float* image, size_t n,
+                                          cudaStream_t stream) {
+  if (n >= (size_t(1) << 32)) throw std::invalid_argument("MedianAndStdDevFromMAD: plane too large");
+  MadStatistics result;
+  if (n == 0) return result;
+  uint64_t n_finite = 0;
+  result.median = Median(h, image, n, 0, 0.0f, n_finite, stream);
+  result.n_finite = n_finite;
+  if (!n_finite) return result;
+  result.stddev = 1.4826f * Median(h, image, n, 1, result.median, n_finite, stream);
+  return result;
+}
+
+// ---- LoadAndAverage ---------------------------------------------------------------------------
+
+namespace {
+
+template <int VEC> struct VecOf;
+template <> struct VecOf<1> { using type = float; };
+template <> struct VecOf<4> { using type = float4; };
+
+bool Aligned(const void* p, size_t a) { return reinterpret_cast<uintptr_t>(p) % a == 0; }
+
+constexpr int kAverageTerms = 16;  // input planes one launch folds into an output plane
+
+struct AverageParams {
+  const float* in[kAverageTerms];
+  float weight[kAverageTerms];
+  int n_terms;
+  int first, last;  // first: start from zero instead of the output's pixels; last: scale
+  float scale;
+  float* out;
+};
+
+// image = 0; image = fma(input, weight, image) per input in order (Image::AddWithFactor);
+// image *= 1 / sum of weights (image_set.cc:105-140). One pass over the inputs of an output
+// plane instead of a read-modify-write of the output per input.
+template <int VEC>
+__global__ void __launch_bounds__(256) LoadAndAverageKernel(AverageParams p, size_t n) {
+  using V = typename VecOf<VEC>::type;
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float acc[VEC];
+    if (p.first) {
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) acc[k] = 0.0f;
+    } else {
+      const V a = reinterpret_cast<const V*>(p.out)[i];
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) acc[k] = reinterpret_cast<const float*>(&a)[k];
+    }
+#pragma unroll 4
+    for (int t = 0; t < p.n_terms; ++t) {
+      const V v = __ldg(reinterpret_cast<const V*>(p.in[t]) + i);
+      const float w = p.weight[t];
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) acc[k] = __fmaf_rn(reinterpret_cast<const float*>(&v)[k], w, acc[k]);
+    }
+    if (p.last) {
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) acc[k] = acc[k] * p.scale;
+    }
+    V o;
+#pragma unroll
+    for (int k = 0; k != VEC; ++k) reinterpret_cast<float*>(&o)[k] = acc[k];
+    reinterpret_cast<V*>(p.out)[i] = o;
+  }
+}
+
+constexpr int kMaskPlanes = 32;
+struct MaskParams {
+  const float* model[kMaskPlanes];
+  int n_models, first;
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256) MaskFromModelKernel(MaskParams p, uint8_t* mask, size_t n) {
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint8_t set[VEC];
+    if (p.first) {
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) set[k] = 0;
+    } else {
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) set[k] = mask[i * VEC + k];
+    }
+    for (int m = 0; m < p.n_models; ++m) {
+#pragma unroll
+      for (int k = 0; k != VEC; ++k) {
+        const float v = __ldg(p.model[m] + i * VEC + k);
+        // std::isfinite(v) && v != 0.0
+        if ((__float_as_uint(v) & 0x7f800000u) != 0x7f800000u && v != 0.0f) set[k] = 1;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k != VEC; ++k) mask[i * VEC + k] = set[k];
+  }
+}
+
+unsigned GridFor(size_t items) {
+  return unsigned(std::max<size_t>(1, std::min<size_t>((items + 255) / 256, size_t(kSmCount) * 8)));
+}
+
+}  // namespace
+
+void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double* weights,
+                         const uint32_t* output_index, size_t n_inputs, float* const* outputs,
+                         size_t n_outputs, size_t n_pixels, cudaStream_t stream) {
+  (void)h;
+  for (size_t i = 0; i != n_inputs; ++i) {
+    if (output_index[i] >= n_outputs) throw std::invalid_argument("LoadAndAverage: output index");
+    if (!inputs[i]) throw std::invalid_argument("LoadAndAverage: null input plane");
+  }
+  for (size_t o = 0; o != n_outputs; ++o) {
+    if (!outputs[o]) throw std::invalid_argument("LoadAndAverage: null output plane");
+    for (size_t i = 0; i != n_inputs; ++i)
+      if (inputs[i] == outputs[o]) throw std::invalid_argument("LoadAndAverage: planes alias");
+  }
+  if (n_pixels == 0) return;
+  for (size_t o = 0; o != n_outputs; ++o) {
+    // the inputs of this output with a weight, in the caller's order (image_set.cc:126-131)
+    std::vector<size_t> terms;
+    double sum = 0.0;
+    bool vec = n_pixels % 4 == 0 && Aligned(outputs[o], 16);
+    for (size_t i = 0; i != n_inputs; ++i) {
+      if (output_index[i] != o || weights[i] == 0.0) continue;
+      terms.push_back(i);
+      sum += weights[i];
+      vec = vec && Aligned(inputs[i], 16);
+    }
+    // with no weighted input the reference scales a zero image by 1 / 0: NaN, reproduced
+    const float scale = float(1.0 / sum);
+    size_t done = 0;
+    do {
+      AverageParams p;
+      p.n_terms = int(std::min<size_t>(kAverageTerms, terms.size() - done));
+      for (int t = 0; t != p.n_terms; ++t) {
+        p.in[t] = inputs[terms[done + t]];
+        p.weight[t] = float(weights[terms[done + t]]);
+      }
+      p.first = done == 0;
+      done += size_t(p.n_terms);
+      p.last = done == terms.size();
+      p.scale = scale;
+      p.out = outputs[o];
+      if (vec)
+        LoadAndAverageKernel<4><<<GridFor(n_pixels / 4), 256, 0, stream>>>(p, n_pixels / 4);
+      else
+        LoadAndAverageKernel<1><<<GridFor(n_pixels), 256, 0, stream>>>(p, n_pixels);
+    } while (done != terms.size());
+  }
+  RDL_CUDA(cudaGetLastError());
+}
+
+void ImageMaskFromModel(rdl_handle& h, const float* const* models, size_t n_models, uint8_t* mask,
+                        size_t n_pixels, cudaStream_t stream) {
+  (void)h;
+  for (size_t m = 0; m != n_models; ++m)
+    if (!models[m]) throw std::invalid_argument("auto-mask from model: null model plane");
+  if (n_pixels == 0) return;
+  if (n_models == 0) {
+    RDL_CUDA(cudaMemsetAsync(mask, 0, n_pixels, stream));
+    return;
+  }
+  for (size_t done = 0; done != n_models;) {
+    MaskParams p;
+    p.n_models = int(std::min<size_t>(kMaskPlanes, n_models - done));
+    bool vec = n_pixels % 4 == 0 && Aligned(mask, 4);
+    for (int m = 0; m != p.n_models; ++m) {
+      p.model[m] = models[done + m];
+      vec = vec && Aligned(p.model[m], 16);
+    }
+    p.first = done == 0;
+    done += size_t(p.n_models);
+    if (vec)
+      MaskFromModelKernel<4><<<GridFor(n_pixels / 4), 256, 0, stream>>>(p, mask, n_pixels / 4);
+    else
+      MaskFromModelKernel<1><<<GridFor(n_pixels), 256, 0, stream>>>(p, mask, n_pixels);
+  }
+  RDL_CUDA(cudaGetLastError());
+}
+
+}  // namespace rdl
