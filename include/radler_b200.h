@@ -483,6 +483,16 @@ rdl_status rdl_load_and_average(rdl_handle* h, const float* const* device_inputs
 rdl_status rdl_auto_mask_from_model(rdl_handle* h, const float* const* device_models,
                                     uint64_t n_models, uint8_t* device_mask, uint64_t n_pixels,
                                     void* stream);
+/* ImageSet::InterpolateAndStoreModel (image_set.cc:208-283) for one polarisation, the case of
+ * fewer deconvolution channels than original ones: per pixel, the polynomial fitter set with
+ * rdl_set_spectral_fitter (its channels = the n_models planes) is fitted to the model planes and
+ * evaluated at each of output_frequencies (all-zero spectra give zeros). Other fitting modes and
+ * more than 8 terms: RDL_ERR_UNSUPPORTED. With as many deconvolution channels as original ones
+ * the reference stores the planes as they are: no call needed. Synchronises the stream. */
+rdl_status rdl_interpolate_model(rdl_handle* h, const float* const* device_models,
+                                 uint64_t n_models, const double* output_frequencies,
+                                 uint64_t n_outputs, float* const* device_outputs,
+                                 uint64_t n_pixels, void* stream);
 
 uint64_t rdl_good_fft_size(uint64_t minimum_size);
 uint64_t rdl_convolution_size(double convolution_scale, uint64_t original_size, double padding);

@@ -673,6 +673,29 @@ def ref_load_and_average(inputs, weights, n_pol, n_deconvolution):
     return out
 
 
+def ref_interpolate_model(models, n_pol, fit_frequencies, fit_weights, n_terms,
+                          original_frequencies):
+    """ImageSet::InterpolateAndStoreModel of the reference's own image_set.cc through the
+    polynomial SpectralFitter stand-in: `models` (n_deconvolution * n_pol, h, w) ->
+    (n_original * n_pol, h, w)."""
+    a = _f32(models)
+    n_in, h, w = a.shape
+    n_dec = n_in // n_pol
+    ff = np.ascontiguousarray(fit_frequencies, np.float64)
+    fw = np.ascontiguousarray(fit_weights, np.float32)
+    of = np.ascontiguousarray(original_frequencies, np.float64)
+    out = np.zeros((len(of) * n_pol, h, w), np.float32)
+    in_ptrs = (C.c_void_p * n_in)(*[a[i].ctypes.data for i in range(n_in)])
+    out_ptrs = (C.c_void_p * len(out))(*[out[i].ctypes.data for i in range(len(out))])
+    f = ref_lib().refa_interpolate_model
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64,
+                  C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p]
+    if f(in_ptrs, n_dec, n_pol, ff.ctypes.data, fw.ctypes.data, n_terms, of.ctypes.data, len(of),
+         w, h, out_ptrs) != 0:
+        raise RuntimeError("refa_interpolate_model failed")
+    return out
+
+
 def ref_median_and_stddev_from_mad(image):
     """aocommon::Image::MedianAndStdDevFromMAD, the stand-in of oracle/ref_shim (aocommon is not
     in the reference tree: restated, unpinned) -> (median, stddev) as float32."""

@@ -410,19 +410,22 @@ void ThreadedSubtractImage(float* image, const Image& psf, size_t x, size_t y, f
 }
 
 // ---- spectral fitter ------------------------------------------------------------
-std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
-                                         const std::vector<float>& weights) {
+namespace {
+// xp: powers x_i^k (n x t); returns the term-solve operator T (t x n), empty when no channel
+// carries weight. t = min(n_terms, channels with weight).
+std::vector<double> SolveForTerms(size_t n_terms, const std::vector<double>& freqs,
+                                  const std::vector<float>& weights, std::vector<double>& xp,
+                                  size_t& t) {
   const size_t n = freqs.size();
-  std::vector<double> proj(n * n, 0.0);
   std::vector<size_t> used;
   for (size_t i = 0; i != n; ++i)
     if (weights[i] > 0.0f) used.push_back(i);
   const size_t m = used.size();
-  if (m == 0) return proj;
-  const size_t t = std::min(n_terms, m);
+  t = std::min(n_terms, m);
+  if (t == 0) return {};
   const double ref = freqs[n / 2];
   // powers x_i^k for all channels (also for zero-weight ones: they are evaluated)
-  std::vector<double> xp(n * t);
+  xp.assign(n * t, 0.0);
   for (size_t i = 0; i != n; ++i) {
     const double x = freqs[i] / ref - 1.0;
     double p = 1.0;
@@ -465,7 +468,33 @@ std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<doubl
       B[col * n + c] = s / d;
     }
   }
-  // B now holds the term-solve operator T (t x n); projection = X T
+  return B;
+}
+}  // namespace
+
+std::vector<double> PolynomialTermSolve(size_t n_terms, const std::vector<double>& freqs,
+                                        const std::vector<float>& weights, size_t& t_used) {
+  std::vector<double> xp;
+  return SolveForTerms(n_terms, freqs, weights, xp, t_used);
+}
+
+double EvaluatePolynomial(const float* terms, size_t n_terms, double x) {
+  double p = 1.0, s = 0.0;
+  for (size_t k = 0; k != n_terms; ++k) {
+    s = s + double(terms[k]) * p;
+    p = p * x;
+  }
+  return s;
+}
+
+std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
+                                         const std::vector<float>& weights) {
+  const size_t n = freqs.size();
+  std::vector<double> proj(n * n, 0.0), xp;
+  size_t t = 0;
+  const std::vector<double> B = SolveForTerms(n_terms, freqs, weights, xp, t);
+  if (t == 0) return proj;
+  // B holds the term-solve operator T (t x n); projection = X T
   for (size_t i = 0; i != n; ++i)
     for (size_t j = 0; j != n; ++j) {
       double s = 0.0;

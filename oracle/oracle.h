@@ -92,6 +92,12 @@ class SpectralFitter {
 // with partial pivoting, fixed operation order.
 std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
                                          const std::vector<float>& weights);
+// The t_used x n operator of the same fit that maps channel values to polynomial terms, and the
+// evaluation sum_k terms[k] x^k by repeated multiplication (SpectralFitter::Fit / Evaluate as
+// ImageSet::InterpolateAndStoreModel uses them, image_set.cc:236-283).
+std::vector<double> PolynomialTermSolve(size_t n_terms, const std::vector<double>& freqs,
+                                        const std::vector<float>& weights, size_t& t_used);
+double EvaluatePolynomial(const float* terms, size_t n_terms, double x);
 
 // ---------------------------------------------------------------------------
 // ImageSet (image_set.{h,cc}) — only what the algorithms use.

@@ -473,6 +473,55 @@ int refa_load_and_average(const float* const* inputs, const double* weights, uin
   });
 }
 
+// ImageSet::InterpolateAndStoreModel (image_set.cc:208-283): models[deconvolution channel *
+// n_pol + pol] -> outputs[original channel * n_pol + pol] through a polynomial fitter over the
+// deconvolution frequencies / weights (the schaapcommon stand-in of ref_shim).
+int refa_interpolate_model(const float* const* models, uint64_t n_deconvolution, uint64_t n_pol,
+                           const double* fit_frequencies, const float* fit_weights,
+                           uint64_t n_terms, const double* original_frequencies,
+                           uint64_t n_original, uint64_t width, uint64_t height,
+                           float* const* outputs) {
+  return Guard(nullptr, [&] {
+    class StoreAccessor final : public aocommon::ImageAccessor {
+     public:
+      StoreAccessor(float* data, size_t w, size_t h) : data_(data), w_(w), h_(h) {}
+      size_t Width() const override { return w_; }
+      size_t Height() const override { return h_; }
+      void Load(float*) const override { throw std::runtime_error("write-only accessor"); }
+      void Store(const float* data) override { std::memcpy(data_, data, w_ * h_ * sizeof(float)); }
+
+     private:
+      float* data_;
+      size_t w_, h_;
+    };
+    static const aocommon::PolarizationEnum kPols[4] = {
+        aocommon::PolarizationEnum::StokesI, aocommon::PolarizationEnum::StokesQ,
+        aocommon::PolarizationEnum::StokesU, aocommon::PolarizationEnum::StokesV};
+    WorkTable table(std::vector<PsfOffset>{}, n_original, n_deconvolution);
+    for (size_t ch = 0; ch != n_original; ++ch) {
+      for (size_t p = 0; p != n_pol; ++p) {
+        auto e = std::make_unique<WorkTableEntry>();
+        e->band_start_frequency = e->band_end_frequency = original_frequencies[ch];
+        e->polarization = kPols[p % 4];
+        e->original_channel_index = ch;
+        e->image_weight = 1.0;
+        e->model_accessor = std::make_unique<StoreAccessor>(outputs[ch * n_pol + p], width, height);
+        e->residual_accessor = std::make_unique<UnusedAccessor>();
+        if (p == 0) e->psf_accessors.emplace_back(std::make_unique<UnusedAccessor>());
+        table.AddEntry(std::move(e));
+      }
+    }
+    ImageSet set(table, false, {}, width, height);
+    for (size_t i = 0; i != set.Size(); ++i)
+      std::memcpy(set.Data(i), models[i], width * height * sizeof(float));
+    const schaapcommon::fitters::SpectralFitter fitter(
+        schaapcommon::fitters::SpectralFittingMode::kPolynomial, n_terms,
+        std::vector<double>(fit_frequencies, fit_frequencies + n_deconvolution),
+        std::vector<float>(fit_weights, fit_weights + n_deconvolution));
+    set.InterpolateAndStoreModel(fitter);
+  });
+}
+
 // integrated.MedianAndStdDevFromMAD() (radler.cc:165-166): the aocommon stand-in of ref_shim
 void refa_median_and_stddev_from_mad(const float* image, uint64_t n, float* median, float* stddev) {
   aocommon::Image img(n, 1);

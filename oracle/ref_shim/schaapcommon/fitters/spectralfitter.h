@@ -67,12 +67,7 @@ class SpectralFitter {
     if (mode_ == SpectralFittingMode::kNoFitting)
       throw std::runtime_error("Evaluate() needs a fitting mode");
     const double x = frequency / ReferenceFrequency() - 1.0;
-    double p = 1.0, s = 0.0;
-    for (size_t k = 0; k != terms.size(); ++k) {
-      s = s + double(terms[k]) * p;
-      p = p * x;
-    }
-    return NumT(s);
+    return NumT(oracle::EvaluatePolynomial(terms.data(), terms.size(), x));
   }
   void Evaluate(NumT* values, const std::vector<NumT>& terms) const {
     for (size_t i = 0; i != frequencies_.size(); ++i) values[i] = Evaluate(terms, frequencies_[i]);
@@ -89,60 +84,11 @@ class SpectralFitter {
   size_t t_used_ = 0;
 };
 
-// Weighted normal equations solved column by column for the unit vectors: the t x n operator
-// that maps channel values to polynomial terms.
+// The t x n operator that maps channel values to polynomial terms: the oracle leaf's, compiled
+// without contraction (this header is compiled with the reference's flags, whose contractions
+// would move the last bit of the operator and with it values that sit on float rounding ties).
 inline void SpectralFitter::BuildTermSolve() {
-  const size_t n = frequencies_.size();
-  std::vector<size_t> used;
-  for (size_t i = 0; i != n; ++i)
-    if (weights_[i] > 0.0f) used.push_back(i);
-  const size_t t = std::min(n_terms_, used.size());
-  t_used_ = t;
-  term_solve_.assign(t * n, 0.0);
-  if (t == 0) return;
-  const double ref = ReferenceFrequency();
-  std::vector<double> xp(n * t);
-  for (size_t i = 0; i != n; ++i) {
-    const double x = frequencies_[i] / ref - 1.0;
-    double p = 1.0;
-    for (size_t k = 0; k != t; ++k) {
-      xp[i * t + k] = p;
-      p = p * x;
-    }
-  }
-  std::vector<double> N(t * t, 0.0), B(t * n, 0.0);
-  for (size_t a = 0; a != t; ++a) {
-    for (size_t b = 0; b != t; ++b) {
-      double s = 0.0;
-      for (size_t u : used) s = s + double(weights_[u]) * xp[u * t + a] * xp[u * t + b];
-      N[a * t + b] = s;
-    }
-    for (size_t u : used) B[a * n + u] = double(weights_[u]) * xp[u * t + a];
-  }
-  for (size_t col = 0; col != t; ++col) {
-    size_t piv = col;
-    for (size_t r = col + 1; r != t; ++r)
-      if (std::fabs(N[r * t + col]) > std::fabs(N[piv * t + col])) piv = r;
-    if (piv != col) {
-      for (size_t c = 0; c != t; ++c) std::swap(N[col * t + c], N[piv * t + c]);
-      for (size_t c = 0; c != n; ++c) std::swap(B[col * n + c], B[piv * n + c]);
-    }
-    const double d = N[col * t + col];
-    for (size_t r = col + 1; r != t; ++r) {
-      const double f = N[r * t + col] / d;
-      for (size_t c = col; c != t; ++c) N[r * t + c] -= f * N[col * t + c];
-      for (size_t c = 0; c != n; ++c) B[r * n + c] -= f * B[col * n + c];
-    }
-  }
-  for (size_t col = t; col-- > 0;) {
-    const double d = N[col * t + col];
-    for (size_t c = 0; c != n; ++c) {
-      double s = B[col * n + c];
-      for (size_t k = col + 1; k != t; ++k) s -= N[col * t + k] * B[k * n + c];
-      B[col * n + c] = s / d;
-    }
-  }
-  term_solve_ = B;
+  term_solve_ = oracle::PolynomialTermSolve(n_terms_, frequencies_, weights_, t_used_);
 }
 
 }  // namespace schaapcommon::fitters

@@ -97,6 +97,7 @@ EXPORTED_SYMBOLS = [
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs", "rdl_rms_sliding_minimum", "rdl_rms_make_factor_image", "rdl_rms_make",
     "rdl_median_and_stddev_from_mad", "rdl_load_and_average", "rdl_auto_mask_from_model",
+    "rdl_interpolate_model",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
     "rdl_parallel_facet_count", "rdl_parallel_facet_get",
     "rdl_parallel_timing",
@@ -741,6 +742,20 @@ class DeconvolutionAlgorithm:
         f = lib().rdl_auto_mask_from_model
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
         self._check(f(self._h, ptrs, n, mask.data_ptr(), mask.numel(), stream))
+
+    def interpolate_model(self, models, output_frequencies, outputs, stream=None):
+        """ImageSet::InterpolateAndStoreModel (image_set.cc:208-283) for one polarisation: the
+        polynomial fitter of set_spectral_fitter fitted per pixel to `models` (device planes, one
+        per deconvolution channel) and evaluated at `output_frequencies` into `outputs`."""
+        n, n_out = len(models), len(outputs)
+        m_ptrs = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in models])
+        o_ptrs = (C.c_void_p * max(n_out, 1))(*[t.data_ptr() for t in outputs])
+        freqs = (C.c_double * max(n_out, 1))(*[float(f) for f in output_frequencies])
+        f = lib().rdl_interpolate_model
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
+                      C.c_uint64, C.c_void_p]
+        self._check(f(self._h, m_ptrs, n, freqs, n_out, o_ptrs,
+                      models[0].numel() if n else 0, stream))
 
     def iuwt_mad(self, image, stream=None):
         """IuwtDeconvolutionAlgorithm::Mad (iuwt_deconvolution_algorithm.cc:104-110)."""

@@ -1078,6 +1078,19 @@ rdl_status rdl_auto_mask_from_model(rdl_handle* h, const float* const* device_mo
   });
 }
 
+rdl_status rdl_interpolate_model(rdl_handle* h, const float* const* device_models,
+                                 uint64_t n_models, const double* output_frequencies,
+                                 uint64_t n_outputs, float* const* device_outputs,
+                                 uint64_t n_pixels, void* stream_v) {
+  if (!h || !device_models || (n_outputs && (!output_frequencies || !device_outputs)))
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    ImageInterpolateModel(*h, device_models, n_models, output_frequencies, n_outputs,
+                          device_outputs, n_pixels, StreamOf(h, stream_v));
+  });
+}
+
 rdl_status rdl_iuwt_mad(rdl_handle* h, const float* device_image, uint64_t n, float* mad,
                         void* stream_v) {
   if (!h || !device_image || !mad) return RDL_ERR_INVALID_ARGUMENT;

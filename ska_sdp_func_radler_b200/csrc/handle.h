@@ -97,6 +97,10 @@ bool IsSimpleSpec(const IntegSpec& spec, size_t n_images);
 // Polynomial projection matrix (spectral fit restated).
 std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
                                          const std::vector<float>& weights);
+// The t_used x n operator of the same fit that maps channel values to polynomial terms
+// (projection = powers x this); t_used = min(n_terms, channels with weight).
+std::vector<double> PolynomialTermSolve(size_t n_terms, const std::vector<double>& freqs,
+                                        const std::vector<float>& weights, size_t& t_used);
 
 struct Settings {  // deconvolution_algorithm.h:189-202
   float threshold = 0.0f;
@@ -163,6 +167,7 @@ struct rdl_handle {
   std::vector<float> fit_weights;
   std::vector<double> projection_host;
   rdl::DeviceBuffer<double> projection;
+  rdl::DeviceBuffer<double> interpolation;  // InterpolateAndStoreModel: term solve + powers
 
   // auto-mask mode (multiscale)
   bool track_per_scale_masks = false, use_per_scale_masks = false;

@@ -151,17 +151,21 @@ bool IsSimpleSpec(const IntegSpec& s, size_t n_images) {
 // number of channels with weight > 0. Fixed operation order (normal equations,
 // Gaussian elimination with partial pivoting) so the CPU checker and this library
 // agree to the bit.
-std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
-                                         const std::vector<float>& weights) {
+namespace {
+// pw = n x t powers of x_i; returns the t x n operator (X^T W X)^-1 X^T W that maps channel
+// values to polynomial terms (t = 0: no channel carries weight).
+std::vector<double> SolveTerms(size_t n_terms, const std::vector<double>& freqs,
+                               const std::vector<float>& weights, std::vector<double>& pw,
+                               size_t& t_used) {
   const size_t n = freqs.size();
-  std::vector<double> proj(n * n, 0.0);
   std::vector<size_t> used;
   for (size_t i = 0; i != n; ++i)
     if (weights[i] > 0.0f) used.push_back(i);
-  if (used.empty()) return proj;
-  const size_t t = n_terms < used.size() ? n_terms : used.size();
+  t_used = n_terms < used.size() ? n_terms : used.size();
+  const size_t t = t_used;
+  if (t == 0) return {};
   const double ref = freqs[n / 2];
-  std::vector<double> pw(n * t);
+  pw.assign(n * t, 0.0);
   for (size_t i = 0; i != n; ++i) {
     const double x = freqs[i] / ref - 1.0;
     double p = 1.0;
@@ -202,6 +206,23 @@ std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<doubl
       rhs[col * n + c] = s / d;
     }
   }
+  return rhs;
+}
+}  // namespace
+
+std::vector<double> PolynomialTermSolve(size_t n_terms, const std::vector<double>& freqs,
+                                        const std::vector<float>& weights, size_t& t_used) {
+  std::vector<double> pw;
+  return SolveTerms(n_terms, freqs, weights, pw, t_used);
+}
+
+std::vector<double> PolynomialProjection(size_t n_terms, const std::vector<double>& freqs,
+                                         const std::vector<float>& weights) {
+  const size_t n = freqs.size();
+  std::vector<double> proj(n * n, 0.0), pw;
+  size_t t = 0;
+  const std::vector<double> rhs = SolveTerms(n_terms, freqs, weights, pw, t);
+  if (t == 0) return proj;
   for (size_t i = 0; i != n; ++i)
     for (size_t j = 0; j != n; ++j) {
       double s = 0.0;

@@ -349,4 +349,115 @@ void ImageMaskFromModel(rdl_handle& h, const float* const* models, size_t n_mode
   RDL_CUDA(cudaGetLastError());
 }
 
+// ---- InterpolateAndStoreModel -------------------------------------------------------------------
+
+namespace {
+
+constexpr int kMaxFitTerms = 8;        // polynomial terms held in registers per pixel
+constexpr int kInterpolateOutputs = 32;  // output planes per launch
+
+struct InterpolateParams {
+  const float* model[kMaxImages];
+  float* out[kInterpolateOutputs];
+  const double* solve;   // t_used x n_models: channel values -> polynomial terms
+  const double* powers;  // n_out x n_terms: (nu_out / nu_ref - 1)^k
+  int n_models, t_used, n_terms, n_out;
+};
+
+// Per pixel (image_set.cc:236-283): the spectrum over the deconvolution channels -> polynomial
+// terms (fitter.Fit; all-zero spectra give zero terms) -> fitter.Evaluate at every output
+// frequency. Same operation order as the polynomial fitter of the clean loops: fma over the
+// channels in double, terms rounded to float, then s = s + term * power in double.
+__global__ void __launch_bounds__(256) InterpolateModelKernel(InterpolateParams p, size_t n) {
+  __shared__ double s_solve[kMaxFitTerms * kMaxImages];
+  __shared__ double s_powers[kInterpolateOutputs * kMaxFitTerms];
+  for (int i = threadIdx.x; i < p.t_used * p.n_models; i += blockDim.x) s_solve[i] = p.solve[i];
+  for (int i = threadIdx.x; i < p.n_out * p.n_terms; i += blockDim.x) s_powers[i] = p.powers[i];
+  __syncthreads();
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    double term[kMaxFitTerms];
+#pragma unroll
+    for (int k = 0; k != kMaxFitTerms; ++k) term[k] = 0.0;
+    bool is_zero = true;
+    for (int j = 0; j < p.n_models; ++j) {
+      const float v = __ldg(p.model[j] + i);
+      is_zero = is_zero && v == 0.0f;
+      const double dv = double(v);
+#pragma unroll
+      for (int k = 0; k != kMaxFitTerms; ++k)
+        if (k < p.t_used) term[k] = fma(s_solve[k * p.n_models + j], dv, term[k]);
+    }
+    if (is_zero) {
+      for (int o = 0; o < p.n_out; ++o) p.out[o][i] = 0.0f;
+      continue;
+    }
+    double rounded[kMaxFitTerms];
+#pragma unroll
+    for (int k = 0; k != kMaxFitTerms; ++k) rounded[k] = k < p.t_used ? double(float(term[k])) : 0.0;
+    for (int o = 0; o < p.n_out; ++o) {
+      double sum = 0.0;
+#pragma unroll
+      for (int k = 0; k != kMaxFitTerms; ++k)
+        if (k < p.n_terms) sum = sum + rounded[k] * s_powers[o * p.n_terms + k];
+      p.out[o][i] = float(sum);
+    }
+  }
+}
+
+}  // namespace
+
+void ImageInterpolateModel(rdl_handle& h, const float* const* models, size_t n_models,
+                           const double* output_frequencies, size_t n_outputs,
+                           float* const* outputs, size_t n_pixels, cudaStream_t stream) {
+  if (h.fit_mode != RDL_FIT_POLYNOMIAL)
+    throw std::domain_error("interpolating the model needs the polynomial spectral fitter "
+                            "(rdl_set_spectral_fitter)");
+  if (n_models != h.fit_freqs.size())
+    throw std::invalid_argument("interpolate model: one model plane per fitter channel");
+  if (h.fit_terms > size_t(kMaxFitTerms))
+    throw std::domain_error("interpolate model: at most 8 polynomial terms");
+  for (size_t j = 0; j != n_models; ++j)
+    if (!models[j]) throw std::invalid_argument("interpolate model: null model plane");
+  for (size_t o = 0; o != n_outputs; ++o) {
+    if (!outputs[o]) throw std::invalid_argument("interpolate model: null output plane");
+    for (size_t j = 0; j != n_models; ++j)
+      if (outputs[o] == models[j]) throw std::invalid_argument("interpolate model: planes alias");
+  }
+  if (n_pixels == 0 || n_outputs == 0) return;
+  size_t t_used = 0;
+  const size_t n_terms = h.fit_terms;
+  std::vector<double> host = PolynomialTermSolve(n_terms, h.fit_freqs, h.fit_weights, t_used);
+  const size_t solve_size = host.size();  // t_used x n_models
+  // SpectralFitter::Evaluate: powers of nu / nu_ref - 1 by repeated multiplication
+  const double reference = h.fit_freqs[h.fit_freqs.size() / 2];
+  for (size_t o = 0; o != n_outputs; ++o) {
+    const double x = output_frequencies[o] / reference - 1.0;
+    double power = 1.0;
+    for (size_t k = 0; k != n_terms; ++k) {
+      host.push_back(power);
+      power = power * x;
+    }
+  }
+  h.interpolation.Reserve(std::max<size_t>(host.size(), 1));
+  RDL_CUDA(cudaMemcpyAsync(h.interpolation.get(), host.data(), host.size() * sizeof(double),
+                           cudaMemcpyHostToDevice, stream));
+  for (size_t done = 0; done != n_outputs;) {
+    InterpolateParams p;
+    for (size_t j = 0; j != n_models; ++j) p.model[j] = models[j];
+    p.n_out = int(std::min<size_t>(kInterpolateOutputs, n_outputs - done));
+    for (int o = 0; o != p.n_out; ++o) p.out[o] = outputs[done + o];
+    p.solve = h.interpolation.get();
+    p.powers = h.interpolation.get() + solve_size + done * n_terms;
+    p.n_models = int(n_models);
+    p.t_used = int(t_used);
+    p.n_terms = int(n_terms);
+    done += size_t(p.n_out);
+    InterpolateModelKernel<<<GridFor(n_pixels), 256, 0, stream>>>(p, n_pixels);
+  }
+  RDL_CUDA(cudaGetLastError());
+  // the pageable staging vector must outlive the copy
+  RDL_CUDA(cudaStreamSynchronize(stream));
+}
+
 }  // namespace rdl

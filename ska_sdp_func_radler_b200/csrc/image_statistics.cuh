@@ -34,5 +34,13 @@ void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double
 void ImageMaskFromModel(rdl_handle& h, const float* const* models, size_t n_models, uint8_t* mask,
                         size_t n_pixels, cudaStream_t stream);
 
+// ImageSet::InterpolateAndStoreModel (image_set.cc:208-283) for one polarisation when there are
+// fewer deconvolution channels than original ones: per pixel, fit the handle's polynomial
+// spectral fitter to the deconvolution-channel model planes and evaluate it at every output
+// frequency. `models` / `outputs` are HOST arrays of device pointers.
+void ImageInterpolateModel(rdl_handle& h, const float* const* models, size_t n_models,
+                           const double* output_frequencies, size_t n_outputs,
+                           float* const* outputs, size_t n_pixels, cudaStream_t stream);
+
 }  // namespace rdl
 #endif

@@ -76,3 +76,36 @@ def noise_images():
     cases["wide_range"] = (rng.standard_normal((64, 64)) * 10.0 ** rng.uniform(-30, 30, (64, 64))
                            ).astype(np.float32)
     return cases
+
+
+def interpolate_case(n_dec, n_orig, h, w, seed):
+    """Model planes of a few components per deconvolution channel, zero elsewhere; frequencies
+    of the deconvolution channels (band centres of groups of original channels) and weights."""
+    rng = np.random.default_rng(seed)
+    orig = 1.2e8 + 2.0e6 * np.arange(n_orig) + rng.uniform(-2e5, 2e5, n_orig)
+    groups = [[ch for ch in range(n_orig) if ch * n_dec // n_orig == d] for d in range(n_dec)]
+    fit_freqs = np.array([orig[g].mean() for g in groups])
+    fit_weights = rng.uniform(0.5, 2.0, n_dec).astype(np.float32)
+    models = np.zeros((n_dec, h, w), np.float32)
+    ys, xs = rng.integers(0, h, 40), rng.integers(0, w, 40)
+    amp = rng.standard_normal(40)
+    for d in range(n_dec):
+        models[d, ys, xs] = (amp * (fit_freqs[d] / fit_freqs[0]) ** -0.7).astype(np.float32)
+    models[0, 0, 0] = 0.5  # a component in one channel only
+    models[-1, 1, 1] = -0.0
+    return models, fit_freqs, fit_weights, orig
+
+
+def interpolate_numpy(models, fit_freqs, fit_weights, n_terms, out_freqs):
+    """Weighted polynomial least squares in (nu / nu_ref - 1), nu_ref = the middle fit channel,
+    evaluated at out_freqs: float64 throughout (tolerance check)."""
+    used = fit_weights > 0
+    t = min(n_terms, int(used.sum()))
+    ref = fit_freqs[len(fit_freqs) // 2]
+    x = fit_freqs / ref - 1.0
+    a = np.vander(x, t, increasing=True)
+    sw = np.sqrt(np.where(used, fit_weights, 0.0).astype(np.float64))
+    solve = np.linalg.pinv(a * sw[:, None]) * sw[None, :]  # t x n
+    terms = np.tensordot(solve, models.astype(np.float64), axes=(1, 0))
+    xo = out_freqs / ref - 1.0
+    return np.tensordot(np.vander(xo, t, increasing=True), terms, axes=(1, 0))

@@ -120,3 +120,125 @@ def test_auto_mask_from_model(rdl, torch_cuda, n_models, h, w):
     assert np.array_equal(mask.cpu().numpy(), want.astype(np.uint8))
     alg.auto_mask_from_model([], mask)
     assert int(mask.sum()) == 0
+
+
+@pytest.mark.parametrize("n_dec,n_orig,n_terms,h,w", [(4, 16, 2, 48, 64), (3, 7, 3, 33, 35),
+                                                      (2, 8, 4, 20, 24), (8, 40, 1, 16, 16),
+                                                      (5, 70, 8, 12, 20)])
+def test_interpolate_model_bit_exact(rdl, oracle, torch_cuda, n_dec, n_orig, n_terms, h, w):
+    """InterpolateAndStoreModel of the reference's own image_set.cc through the polynomial
+    fitter the reference sources are compiled against (schaapcommon's is not in the tree:
+    restated, unpinned) -- terms clamped to the channels (n_terms 4 on 2 channels), more outputs
+    than one launch takes (40, 70), a zero-weight fit channel."""
+    from perform_steps_cases import interpolate_case
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    models, ff, fw, orig = interpolate_case(n_dec, n_orig, h, w, seed=n_dec * n_orig)
+    if n_dec == 5:
+        fw[2] = 0.0
+    want = oracle.ref_interpolate_model(models, 1, ff, fw, n_terms, orig)
+    alg = rdl.GenericClean()
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, n_terms, ff, fw)
+    d_models = [torch.from_numpy(m).cuda() for m in models]
+    d_out = [torch.full((h, w), 3.0, device="cuda") for _ in range(n_orig)]
+    alg.interpolate_model(d_models, orig, d_out)
+    got = np.stack([t.cpu().numpy() for t in d_out])
+    assert np.count_nonzero(want) > 30 * n_orig
+    assert np.array_equal(got, want)  # zeros of either sign are zeros
+
+
+def test_interpolate_model_needs_the_polynomial_fitter(rdl, torch_cuda):
+    torch = torch_cuda
+    alg = rdl.GenericClean()
+    m = [torch.zeros((8, 8), device="cuda") for _ in range(2)]
+    o = [torch.zeros((8, 8), device="cuda") for _ in range(3)]
+    with pytest.raises(rdl.RadlerError):
+        alg.interpolate_model(m, [1e8, 1.1e8, 1.2e8], o)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, [1e8, 1.2e8], None)
+    with pytest.raises(rdl.RadlerError):
+        alg.interpolate_model(m + m, [1e8, 1.1e8, 1.2e8], o)
+    with pytest.raises(rdl.RadlerError):
+        alg.interpolate_model(m, [1e8, 1.1e8], [m[0], o[1]])
+    alg.interpolate_model(m, [1e8, 1.1e8, 1.2e8], o)
+
+
+def test_one_major_iteration_of_perform_on_the_device(rdl, oracle, torch_cuda):
+    """The sequence Radler::Perform runs (radler.cc:150-273, image_set.cc): LoadAndAverage of 8
+    original channels into 2 deconvolution channels, GetLinearIntegrated + MedianAndStdDevFromMAD,
+    the threshold from the noise, GenericClean::ExecuteMajorIteration with a 2-term polynomial
+    fit, InterpolateAndStoreModel back to the 8 channels -- every step on device planes, one copy
+    back at the end, against the same sequence through the reference's own sources / the
+    oracle."""
+    from helpers import hogbom_case
+    from perform_steps_cases import output_index_of
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, n_orig, n_dec = 256, 8, 2
+    res, psfs, w_orig, f_orig = hogbom_case(n, n_orig, seed=12)
+    w_orig = w_orig.astype(np.float64)
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    groups = [[i for i, o in enumerate(index) if o == d] for d in range(n_dec)]
+    w_dec = np.array([w_orig[g].sum() for g in groups], np.float32)
+    f_dec = np.array([(f_orig[g] * w_orig[g]).sum() / w_orig[g].sum() for g in groups])
+    kw = dict(max_iterations=300, minor_loop_gain=0.1, major_loop_gain=0.8, clean_border_ratio=0.0)
+
+    # host: the reference's own image_set.cc around the oracle's minor loop
+    r_res = oracle.ref_load_and_average(res, w_orig, 1, n_dec)
+    r_psf = oracle.ref_load_and_average(psfs, w_orig, 1, n_dec)
+    ocube = oracle.Cube(n, n, n_dec, 1, w_dec)
+    _, r_std = oracle.ref_median_and_stddev_from_mad(oracle.integrate(ocube, r_res))
+    os_ = oracle.Settings(threshold=float(5.0 * r_std), **kw)
+    os_.spectral_mode, os_.n_terms, os_.frequencies, os_.fit_weights = 1, 2, f_dec, w_dec
+    r_model = np.zeros_like(r_res)
+    o = oracle.GenericClean(use_sub_minor_optimization=False).execute(ocube, os_, r_res, r_model,
+                                                                      r_psf)
+    assert 20 < o.iteration_number < 300  # stopped by the noise threshold
+    r_out = oracle.ref_interpolate_model(r_model, 1, f_dec, w_dec, 2, f_orig)
+
+    # device
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    d_orig = [torch.from_numpy(p).cuda() for p in res]
+    d_psf_orig = [torch.from_numpy(p).cuda() for p in psfs]
+    d_res = torch.zeros((n_dec, n, n), device="cuda")
+    d_psf = torch.zeros((n_dec, n, n), device="cuda")
+    d_model = torch.zeros((n_dec, n, n), device="cuda")
+    alg.load_and_average(d_orig, w_orig, index, list(d_res))
+    alg.load_and_average(d_psf_orig, w_orig, index, list(d_psf))
+    cube = rdl.Cube(n, n, n_dec, 1, w_dec)
+    integrated = torch.zeros((n, n), device="cuda")
+    alg.integrate(cube, d_res, integrated)
+    _, g_std, _ = alg.median_and_stddev_from_mad(integrated)
+    assert np.float32(g_std) == r_std
+    alg.apply(threshold=float(5.0 * np.float32(g_std)), **kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, f_dec, w_dec)
+    g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+    assert g.iteration_number == o.iteration_number
+    d_out = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+    alg.interpolate_model(list(d_model), f_orig, d_out)
+    assert np.array_equal(d_res.cpu().numpy(), r_res)
+    assert np.array_equal(d_model.cpu().numpy(), r_model)
+    assert np.array_equal(np.stack([t.cpu().numpy() for t in d_out]), r_out)
+
+
+def test_interpolate_model_on_float_rounding_ties(rdl, oracle, torch_cuda):
+    """Evenly spaced channels with unit weights give a term-solve operator of round numbers
+    (0.1, 0.2, ...): a tenth of all fitted terms then sit on a float rounding tie that the last bit
+    of the operator decides. Both sides build it with the same uncontracted operations."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n_dec, n_orig, n = 4, 16, 96
+    rng = np.random.default_rng(1)
+    orig = 1.2e8 + 2.0e6 * np.arange(n_orig)
+    fit = orig.reshape(n_dec, -1).mean(axis=1)
+    models = (rng.standard_normal((n_dec, n, n)) + 3.0).astype(np.float32)
+    for n_terms in (2, 3):
+        want = oracle.ref_interpolate_model(models, 1, fit, np.ones(n_dec, np.float32), n_terms, orig)
+        alg = rdl.GenericClean()
+        alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, n_terms, fit, None)
+        d_out = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+        alg.interpolate_model([torch.from_numpy(m).cuda() for m in models], orig, d_out)
+        got = np.stack([t.cpu().numpy() for t in d_out])
+        assert np.array_equal(got, want), n_terms

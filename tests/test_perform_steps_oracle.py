@@ -35,3 +35,16 @@ def test_median_and_stddev_from_mad(name):
     m, s = oracle.ref_median_and_stddev_from_mad(a)
     wm, ws = mad_numpy(a)
     assert m == wm and s == ws
+
+
+@needs_ref
+@pytest.mark.parametrize("n_dec,n_orig,n_terms", [(4, 16, 2), (3, 7, 3), (2, 8, 4), (8, 24, 1)])
+def test_interpolate_model(n_dec, n_orig, n_terms):
+    from perform_steps_cases import interpolate_case, interpolate_numpy
+    models, ff, fw, orig = interpolate_case(n_dec, n_orig, 24, 30, seed=n_dec + n_orig)
+    got = oracle.ref_interpolate_model(models, 1, ff, fw, n_terms, orig)
+    want = interpolate_numpy(models, ff, fw, n_terms, orig)
+    assert got.shape == want.shape
+    assert np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
+    empty = ~models.any(axis=0)
+    assert np.all(got[:, empty] == 0.0)

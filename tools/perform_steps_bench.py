@@ -71,6 +71,29 @@ def main():
                       "device_ms": round(ms, 3),
                       "GB/s": round((n_dec * plane.nbytes + n * n) / ms / 1e6, 1)}), flush=True)
 
+    # InterpolateAndStoreModel: n_dec model planes (a few thousand components) -> n_orig planes
+    orig = 1.2e8 + 2.0e6 * np.arange(n_orig)
+    fit = orig.reshape(n_dec, -1).mean(axis=1)
+    host_models = np.zeros((n_dec, n, n), np.float32)
+    ys, xs = rng.integers(0, n, 5000), rng.integers(0, n, 5000)
+    for d_ in range(n_dec):
+        host_models[d_, ys, xs] = (rng.standard_normal(5000) + 3.0).astype(np.float32)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, fit, None)
+    for m, hm in zip(models, host_models):
+        m.copy_(torch.from_numpy(hm))
+    outs = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+    ms = device_ms(lambda: alg.interpolate_model(models, orig, outs))
+    line = {"step": "InterpolateAndStoreModel", "frame": n, "deconvolution": n_dec,
+            "original": n_orig, "terms": 2, "device_ms": round(ms, 3),
+            "GB/s": round((n_dec + n_orig) * plane.nbytes / ms / 1e6, 1)}
+    if oracle.ref_lib() is not None:
+        t = time.perf_counter()
+        want = oracle.ref_interpolate_model(host_models, 1, fit, np.ones(n_dec, np.float32), 2, orig)
+        line["host_ms"] = round((time.perf_counter() - t) * 1e3, 1)
+        got = np.stack([t_.cpu().numpy() for t_ in outs])
+        line["identical"] = bool(np.array_equal(got, want))
+    print(json.dumps(line), flush=True)
+
 
 if __name__ == "__main__":
     main()
