@@ -478,6 +478,15 @@ rdl_status rdl_load_and_average(rdl_handle* h, const float* const* device_inputs
                                 const double* weights, const uint32_t* output_index,
                                 uint64_t n_inputs, float* const* device_outputs,
                                 uint64_t n_outputs, uint64_t n_pixels, void* stream);
+/* ImageSet::LoadAndAveragePsfs (image_set.cc:142-205) after the loads, one PSF per original
+ * channel: the same grouping (output_index = deconvolution channel), but the reference keeps the
+ * weights double there -- psf = float(double(psf) + double(input) * weight), then
+ * psf = float(double(psf) / sum of weights); inputs of weight 0 are read (x 0), an output without
+ * weight is scaled by 0. */
+rdl_status rdl_load_and_average_psfs(rdl_handle* h, const float* const* device_inputs,
+                                     const double* weights, const uint32_t* output_index,
+                                     uint64_t n_inputs, float* const* device_outputs,
+                                     uint64_t n_outputs, uint64_t n_pixels, void* stream);
 /* The auto-mask derived from the model planes when the second auto-masking phase starts
  * (radler.cc:254-266): mask = 1 where any model plane is finite and non-zero, else 0. */
 rdl_status rdl_auto_mask_from_model(rdl_handle* h, const float* const* device_models,

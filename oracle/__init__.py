@@ -673,6 +673,23 @@ def ref_load_and_average(inputs, weights, n_pol, n_deconvolution):
     return out
 
 
+def ref_load_and_average_psfs(psfs, weights, n_deconvolution):
+    """ImageSet::LoadAndAveragePsfs of the reference's own image_set.cc: (n_original, h, w), one
+    weight per original channel -> (n_deconvolution, h, w)."""
+    a = _f32(psfs)
+    n, h, w = a.shape
+    wts = np.ascontiguousarray(weights, np.float64)
+    out = np.zeros((min(n_deconvolution, n) if n_deconvolution else n, h, w), np.float32)
+    in_ptrs = (C.c_void_p * n)(*[a[i].ctypes.data for i in range(n)])
+    out_ptrs = (C.c_void_p * len(out))(*[out[i].ctypes.data for i in range(len(out))])
+    f = ref_lib().refa_load_and_average_psfs
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
+                  C.c_void_p]
+    if f(in_ptrs, wts.ctypes.data, n, n_deconvolution, w, h, out_ptrs) != 0:
+        raise RuntimeError("refa_load_and_average_psfs failed")
+    return out
+
+
 def ref_interpolate_model(models, n_pol, fit_frequencies, fit_weights, n_terms,
                           original_frequencies):
     """ImageSet::InterpolateAndStoreModel of the reference's own image_set.cc through the
@@ -694,6 +711,34 @@ def ref_interpolate_model(models, n_pol, fit_frequencies, fit_weights, n_terms,
          w, h, out_ptrs) != 0:
         raise RuntimeError("refa_interpolate_model failed")
     return out
+
+
+def ref_radler_perform(residuals, models, psfs, frequencies, weights, n_deconvolution, *,
+                       auto_threshold_sigma, minor_loop_gain, major_loop_gain,
+                       minor_iteration_count, fit_terms):
+    """radler::Radler::Perform of the reference's own radler.cc (one major iteration of
+    GenericClean without the sub-minor loop, one polarisation). `residuals` / `models`
+    (n_original, h, w) are overwritten the way wsclean's load-and-store accessors are.
+    -> (another_iteration_required, iteration_number)."""
+    for a in (residuals, models, psfs):
+        assert a.dtype == np.float32 and a.flags.c_contiguous
+    n, h, w = residuals.shape
+    fr = np.ascontiguousarray(frequencies, np.float64)
+    wt = np.ascontiguousarray(weights, np.float64)
+    tables = [(C.c_void_p * n)(*[a[i].ctypes.data for i in range(n)])
+              for a in (residuals, models, psfs)]
+    another, iterations = C.c_int32(), C.c_uint64()
+    f = ref_lib().refa_radler_perform
+    f.argtypes = [C.c_uint64] * 4 + [C.c_void_p] * 5 + [C.c_double] * 3 + [C.c_uint64] * 2 + \
+        [C.c_void_p] * 2
+    if f(w, h, n, n_deconvolution, fr.ctypes.data, wt.ctypes.data, tables[0], tables[1],
+         tables[2], float(auto_threshold_sigma), float(minor_loop_gain), float(major_loop_gain),
+         int(minor_iteration_count), int(fit_terms), C.byref(another), C.byref(iterations)) != 0:
+        err = ref_lib().refa_last_error
+        err.restype = C.c_char_p
+        err.argtypes = [C.c_void_p]
+        raise RuntimeError("Radler::Perform: " + err(None).decode())
+    return bool(another.value), int(iterations.value)
 
 
 def ref_median_and_stddev_from_mad(image):

@@ -26,6 +26,7 @@
 #include "algorithms/parallel_deconvolution.h"
 #undef private
 #include "image_set.h"
+#include "radler.h"
 #include "settings.h"
 #include "work_table.h"
 #ifdef RDL_WITH_ADAPTER
@@ -519,6 +520,92 @@ int refa_interpolate_model(const float* const* models, uint64_t n_deconvolution,
         std::vector<double>(fit_frequencies, fit_frequencies + n_deconvolution),
         std::vector<float>(fit_weights, fit_weights + n_deconvolution));
     set.InterpolateAndStoreModel(fitter);
+  });
+}
+
+// ImageSet::LoadAndAveragePsfs (image_set.cc:142-205): one PSF per original channel ->
+// outputs[deconvolution channel].
+int refa_load_and_average_psfs(const float* const* inputs, const double* weights,
+                               uint64_t n_original, uint64_t n_deconvolution, uint64_t width,
+                               uint64_t height, float* const* outputs) {
+  return Guard(nullptr, [&] {
+    WorkTable table(std::vector<PsfOffset>{}, n_original, n_deconvolution);
+    for (size_t ch = 0; ch != n_original; ++ch) {
+      auto e = std::make_unique<WorkTableEntry>();
+      e->band_start_frequency = e->band_end_frequency = 1.0e8 + 1.0e6 * ch;
+      e->polarization = aocommon::PolarizationEnum::StokesI;
+      e->original_channel_index = ch;
+      e->image_weight = weights[ch];
+      e->model_accessor = std::make_unique<UnusedAccessor>();
+      e->residual_accessor = std::make_unique<UnusedAccessor>();
+      e->psf_accessors.emplace_back(std::make_unique<MemoryAccessor>(inputs[ch], width, height));
+      table.AddEntry(std::move(e));
+    }
+    const ImageSet set(table, false, {}, width, height);
+    const std::vector<std::vector<aocommon::Image>> psfs = set.LoadAndAveragePsfs();
+    for (size_t i = 0; i != psfs[0].size(); ++i)
+      std::memcpy(outputs[i], psfs[0][i].Data(), width * height * sizeof(float));
+  });
+}
+
+// Radler::Perform itself (radler.cc:130-316), one major iteration of GenericClean without the
+// sub-minor loop: n_original channels (one polarisation) averaged to n_deconvolution channels,
+// the threshold from the MAD noise estimate (auto_threshold_sigma), a polynomial spectral fit,
+// residuals assigned and the model interpolated back to the original channels. residuals /
+// models are read and overwritten through load-and-store accessors, like wsclean's.
+int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
+                        uint64_t n_deconvolution, const double* frequencies,
+                        const double* weights, float* const* residuals, float* const* models,
+                        const float* const* psfs, double auto_threshold_sigma,
+                        double minor_loop_gain, double major_loop_gain,
+                        uint64_t minor_iteration_count, uint64_t fit_terms,
+                        int32_t* another_iteration_required, uint64_t* iteration_number) {
+  return Guard(nullptr, [&] {
+    class BufferAccessor final : public aocommon::ImageAccessor {
+     public:
+      BufferAccessor(float* data, size_t w, size_t h) : data_(data), w_(w), h_(h) {}
+      size_t Width() const override { return w_; }
+      size_t Height() const override { return h_; }
+      void Load(float* data) const override { std::memcpy(data, data_, w_ * h_ * sizeof(float)); }
+      void Store(const float* data) override { std::memcpy(data_, data, w_ * h_ * sizeof(float)); }
+
+     private:
+      float* data_;
+      size_t w_, h_;
+    };
+    Settings s;
+    s.trimmed_image_width = width;
+    s.trimmed_image_height = height;
+    s.channels_out = n_original;
+    s.algorithm_type = AlgorithmType::kGenericClean;
+    s.generic.use_sub_minor_optimization = false;
+    s.auto_threshold_sigma = auto_threshold_sigma;
+    s.minor_loop_gain = minor_loop_gain;
+    s.major_loop_gain = major_loop_gain;
+    s.minor_iteration_count = minor_iteration_count;
+    s.border_ratio = 0.0;
+    if (fit_terms) {
+      s.spectral_fitting.mode = schaapcommon::fitters::SpectralFittingMode::kPolynomial;
+      s.spectral_fitting.terms = fit_terms;
+    }
+    auto table = std::make_unique<WorkTable>(std::vector<PsfOffset>{}, n_original, n_deconvolution);
+    for (size_t ch = 0; ch != n_original; ++ch) {
+      auto e = std::make_unique<WorkTableEntry>();
+      e->band_start_frequency = e->band_end_frequency = frequencies[ch];
+      e->polarization = aocommon::PolarizationEnum::StokesI;
+      e->original_channel_index = ch;
+      e->image_weight = weights[ch];
+      e->model_accessor = std::make_unique<BufferAccessor>(models[ch], width, height);
+      e->residual_accessor = std::make_unique<BufferAccessor>(residuals[ch], width, height);
+      e->psf_accessors.emplace_back(
+          std::make_unique<BufferAccessor>(const_cast<float*>(psfs[ch]), width, height));
+      table->AddEntry(std::move(e));
+    }
+    Radler radler(s, std::move(table), 0.0);
+    bool another = false;
+    radler.Perform(another, 1);
+    *another_iteration_required = another ? 1 : 0;
+    *iteration_number = radler.IterationNumber();
   });
 }
 

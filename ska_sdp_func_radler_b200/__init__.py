@@ -96,7 +96,7 @@ EXPORTED_SYMBOLS = [
     "rdl_padded_convolution", "rdl_multiscale_transform", "rdl_iuwt_smooth", "rdl_iuwt_decompose", "rdl_iuwt_decompose_static", "rdl_iuwt_decompose_aliased", "rdl_iuwt_recompose",
     "rdl_iuwt_select_structures", "rdl_iuwt_floodfill", "rdl_iuwt_floodfill_2d", "rdl_iuwt_mad",
     "rdl_iuwt_max_abs", "rdl_rms_sliding_minimum", "rdl_rms_make_factor_image", "rdl_rms_make",
-    "rdl_median_and_stddev_from_mad", "rdl_load_and_average", "rdl_auto_mask_from_model",
+    "rdl_median_and_stddev_from_mad", "rdl_load_and_average", "rdl_load_and_average_psfs", "rdl_auto_mask_from_model",
     "rdl_interpolate_model",
     "rdl_parallel_execute_major_iteration", "rdl_parallel_execute_major_iteration_dd",
     "rdl_parallel_facet_count", "rdl_parallel_facet_get",
@@ -720,15 +720,16 @@ class DeconvolutionAlgorithm:
                       C.byref(m), C.byref(s), C.byref(n), stream))
         return m.value, s.value, n.value
 
-    def load_and_average(self, inputs, weights, output_index, outputs, stream=None):
+    def load_and_average(self, inputs, weights, output_index, outputs, stream=None, psfs=False):
         """ImageSet::LoadAndAverage (image_set.cc:105-140) with the planes already on the device:
-        `inputs` / `outputs` are sequences of equally sized device planes."""
+        `inputs` / `outputs` are sequences of equally sized device planes. psfs=True:
+        ImageSet::LoadAndAveragePsfs (:142-205), whose products stay double."""
         n_in, n_out = len(inputs), len(outputs)
         in_ptrs = (C.c_void_p * max(n_in, 1))(*[t.data_ptr() for t in inputs])
         out_ptrs = (C.c_void_p * max(n_out, 1))(*[t.data_ptr() for t in outputs])
         w = (C.c_double * max(n_in, 1))(*[float(v) for v in weights])
         idx = (C.c_uint32 * max(n_in, 1))(*[int(v) for v in output_index])
-        f = lib().rdl_load_and_average
+        f = lib().rdl_load_and_average_psfs if psfs else lib().rdl_load_and_average
         f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                       C.c_uint64, C.c_uint64, C.c_void_p]
         n_pixels = outputs[0].numel() if n_out else 0

@@ -1064,7 +1064,20 @@ rdl_status rdl_load_and_average(rdl_handle* h, const float* const* device_inputs
   return Guard(h, [&] {
     RDL_CUDA(cudaSetDevice(h->device));
     ImageLoadAndAverage(*h, device_inputs, weights, output_index, n_inputs, device_outputs,
-                        n_outputs, n_pixels, StreamOf(h, stream_v));
+                        n_outputs, n_pixels, false, StreamOf(h, stream_v));
+  });
+}
+
+rdl_status rdl_load_and_average_psfs(rdl_handle* h, const float* const* device_inputs,
+                                     const double* weights, const uint32_t* output_index,
+                                     uint64_t n_inputs, float* const* device_outputs,
+                                     uint64_t n_outputs, uint64_t n_pixels, void* stream_v) {
+  if (!h || !device_outputs || (n_inputs && (!device_inputs || !weights || !output_index)))
+    return RDL_ERR_INVALID_ARGUMENT;
+  return Guard(h, [&] {
+    RDL_CUDA(cudaSetDevice(h->device));
+    ImageLoadAndAverage(*h, device_inputs, weights, output_index, n_inputs, device_outputs,
+                        n_outputs, n_pixels, true, StreamOf(h, stream_v));
   });
 }
 

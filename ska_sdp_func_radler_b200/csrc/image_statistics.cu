@@ -194,16 +194,21 @@ constexpr int kAverageTerms = 16;  // input planes one launch folds into an outp
 struct AverageParams {
   const float* in[kAverageTerms];
   float weight[kAverageTerms];
+  double weight_d[kAverageTerms];  // the PSF rule multiplies in double
   int n_terms;
   int first, last;  // first: start from zero instead of the output's pixels; last: scale
   float scale;
+  double scale_d;
   float* out;
 };
 
 // image = 0; image = fma(input, weight, image) per input in order (Image::AddWithFactor);
 // image *= 1 / sum of weights (image_set.cc:105-140). One pass over the inputs of an output
 // plane instead of a read-modify-write of the output per input.
-template <int VEC>
+// PSF_RULE: ImageSet::LoadAndAveragePsfs (image_set.cc:142-205) instead, whose weights stay
+// double: psf = float(double(psf) + double(input) * weight), contracted by the reference's build
+// to one double fma, and psf = float(double(psf) * (1 / sum of weights)).
+template <int VEC, bool PSF_RULE>
 __global__ void __launch_bounds__(256) LoadAndAverageKernel(AverageParams p, size_t n) {
   using V = typename VecOf<VEC>::type;
   const size_t stride = size_t(gridDim.x) * blockDim.x;
@@ -220,13 +225,22 @@ __global__ void __launch_bounds__(256) LoadAndAverageKernel(AverageParams p, siz
 #pragma unroll 4
     for (int t = 0; t < p.n_terms; ++t) {
       const V v = __ldg(reinterpret_cast<const V*>(p.in[t]) + i);
-      const float w = p.weight[t];
+      if (PSF_RULE) {
+        const double w = p.weight_d[t];
 #pragma unroll
-      for (int k = 0; k != VEC; ++k) acc[k] = __fmaf_rn(reinterpret_cast<const float*>(&v)[k], w, acc[k]);
+        for (int k = 0; k != VEC; ++k)
+          acc[k] = float(fma(double(reinterpret_cast<const float*>(&v)[k]), w, double(acc[k])));
+      } else {
+        const float w = p.weight[t];
+#pragma unroll
+        for (int k = 0; k != VEC; ++k)
+          acc[k] = __fmaf_rn(reinterpret_cast<const float*>(&v)[k], w, acc[k]);
+      }
     }
     if (p.last) {
 #pragma unroll
-      for (int k = 0; k != VEC; ++k) acc[k] = acc[k] * p.scale;
+      for (int k = 0; k != VEC; ++k)
+        acc[k] = PSF_RULE ? float(double(acc[k]) * p.scale_d) : acc[k] * p.scale;
     }
     V o;
 #pragma unroll
@@ -274,7 +288,7 @@ unsigned GridFor(size_t items) {
 
 void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double* weights,
                          const uint32_t* output_index, size_t n_inputs, float* const* outputs,
-                         size_t n_outputs, size_t n_pixels, cudaStream_t stream) {
+                         size_t n_outputs, size_t n_pixels, bool psf_rule, cudaStream_t stream) {
   (void)h;
   for (size_t i = 0; i != n_inputs; ++i) {
     if (output_index[i] >= n_outputs) throw std::invalid_argument("LoadAndAverage: output index");
@@ -292,13 +306,16 @@ void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double
     double sum = 0.0;
     bool vec = n_pixels % 4 == 0 && Aligned(outputs[o], 16);
     for (size_t i = 0; i != n_inputs; ++i) {
-      if (output_index[i] != o || weights[i] == 0.0) continue;
+      // LoadAndAverage leaves inputs without weight out; LoadAndAveragePsfs adds them x 0
+      if (output_index[i] != o || (!psf_rule && weights[i] == 0.0)) continue;
       terms.push_back(i);
       sum += weights[i];
       vec = vec && Aligned(inputs[i], 16);
     }
-    // with no weighted input the reference scales a zero image by 1 / 0: NaN, reproduced
+    // with no weighted input LoadAndAverage scales a zero image by 1 / 0: NaN, reproduced;
+    // LoadAndAveragePsfs scales by 0 (image_set.cc:196-198)
     const float scale = float(1.0 / sum);
+    const double scale_d = sum == 0.0 ? 0.0 : 1.0 / sum;
     size_t done = 0;
     do {
       AverageParams p;
@@ -306,16 +323,23 @@ void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double
       for (int t = 0; t != p.n_terms; ++t) {
         p.in[t] = inputs[terms[done + t]];
         p.weight[t] = float(weights[terms[done + t]]);
+        p.weight_d[t] = weights[terms[done + t]];
       }
       p.first = done == 0;
       done += size_t(p.n_terms);
       p.last = done == terms.size();
       p.scale = scale;
+      p.scale_d = scale_d;
       p.out = outputs[o];
-      if (vec)
-        LoadAndAverageKernel<4><<<GridFor(n_pixels / 4), 256, 0, stream>>>(p, n_pixels / 4);
+      const unsigned grid = GridFor(vec ? n_pixels / 4 : n_pixels);
+      if (vec && psf_rule)
+        LoadAndAverageKernel<4, true><<<grid, 256, 0, stream>>>(p, n_pixels / 4);
+      else if (vec)
+        LoadAndAverageKernel<4, false><<<grid, 256, 0, stream>>>(p, n_pixels / 4);
+      else if (psf_rule)
+        LoadAndAverageKernel<1, true><<<grid, 256, 0, stream>>>(p, n_pixels);
       else
-        LoadAndAverageKernel<1><<<GridFor(n_pixels), 256, 0, stream>>>(p, n_pixels);
+        LoadAndAverageKernel<1, false><<<grid, 256, 0, stream>>>(p, n_pixels);
     } while (done != terms.size());
   }
   RDL_CUDA(cudaGetLastError());

@@ -24,9 +24,11 @@ MadStatistics ImageMedianAndStdDevFromMad(rdl_handle& h, const float* image, siz
 // memory: output[output_index[i]] accumulates input[i] x weight[i] in the order given (inputs of
 // weight zero are left out, as the reference does), then every output is scaled by
 // 1 / (sum of its weights). `inputs` / `outputs` are HOST arrays of device pointers.
+// psf_rule: ImageSet::LoadAndAveragePsfs (image_set.cc:142-205) instead -- the same grouping
+// with the products and the final scale in double, zero-weight inputs included.
 void ImageLoadAndAverage(rdl_handle& h, const float* const* inputs, const double* weights,
                          const uint32_t* output_index, size_t n_inputs, float* const* outputs,
-                         size_t n_outputs, size_t n_pixels, cudaStream_t stream);
+                         size_t n_outputs, size_t n_pixels, bool psf_rule, cudaStream_t stream);
 
 // The auto-mask Radler::Perform derives from the model images when the second auto-masking phase
 // starts (radler.cc:254-266): a pixel is set where any model plane is finite and non-zero.

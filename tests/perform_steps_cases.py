@@ -109,3 +109,21 @@ def interpolate_numpy(models, fit_freqs, fit_weights, n_terms, out_freqs):
     terms = np.tensordot(solve, models.astype(np.float64), axes=(1, 0))
     xo = out_freqs / ref - 1.0
     return np.tensordot(np.vander(xo, t, increasing=True), terms, axes=(1, 0))
+
+
+def deconvolution_channels(frequencies, weights, n_deconvolution):
+    """ImageSet::CalculateDeconvolutionFrequencies (image_set.cc:464-497): per deconvolution
+    channel the weighted mean frequency (double) and the summed weight (accumulated in float)."""
+    n = len(frequencies)
+    n_dec = min(n, n_deconvolution) if n_deconvolution else n
+    freqs, sums = np.zeros(n_dec), np.zeros(n_dec, np.float32)
+    plain, counts = np.zeros(n_dec), np.zeros(n_dec, int)
+    for i in range(n):
+        d = i * n_dec // n
+        freqs[d] += frequencies[i] * weights[i]
+        sums[d] = np.float32(np.float64(sums[d]) + weights[i])
+        plain[d] += frequencies[i]
+        counts[d] += 1
+    for d in range(n_dec):
+        freqs[d] = freqs[d] / np.float64(sums[d]) if sums[d] > 0 else plain[d] / counts[d]
+    return freqs, sums

@@ -242,3 +242,85 @@ def test_interpolate_model_on_float_rounding_ties(rdl, oracle, torch_cuda):
         alg.interpolate_model([torch.from_numpy(m).cuda() for m in models], orig, d_out)
         got = np.stack([t.cpu().numpy() for t in d_out])
         assert np.array_equal(got, want), n_terms
+
+
+@pytest.mark.parametrize("n_original,n_deconvolution,h,w", [(8, 3, 33, 47), (5, 5, 64, 64),
+                                                            (40, 2, 32, 40), (6, 0, 17, 19)])
+def test_load_and_average_psfs_bit_exact(rdl, oracle, torch_cuda, n_original, n_deconvolution, h, w):
+    """ImageSet::LoadAndAveragePsfs (image_set.cc:142-205): double products, zero-weight
+    channels included, against the reference's own source."""
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(n_original)
+    psfs = rng.standard_normal((n_original, h, w)).astype(np.float32)
+    weights = rng.uniform(0.2, 3.0, n_original)
+    weights[n_original // 2] = 0.0
+    if n_deconvolution == n_original:
+        weights[0] = 0.0  # a deconvolution channel without weight: scaled by 0
+    index, n_dec = output_index_of(n_original, 1, n_deconvolution)
+    want = oracle.ref_load_and_average_psfs(psfs, weights, n_deconvolution)
+    alg = rdl.GenericClean()
+    d_out = [torch.full((h, w), 5.0, device="cuda") for _ in range(n_dec)]
+    alg.load_and_average([torch.from_numpy(p).cuda() for p in psfs], weights, index, d_out,
+                         psfs=True)
+    got = np.stack([t.cpu().numpy() for t in d_out])
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("n_orig,n_dec,terms", [(8, 2, 2), (6, 6, 2), (9, 3, 3)])
+def test_radler_perform_major_iteration(rdl, oracle, torch_cuda, n_orig, n_dec, terms):
+    """radler::Radler::Perform of the reference's OWN radler.cc (oracle/_ref), one major
+    iteration: LoadAndAverage of residual and model, MedianAndStdDevFromMAD of the integrated
+    residual, threshold = 5 sigma, LoadAndAveragePsfs, GenericClean::ExecuteMajorIteration with a
+    polynomial fit, AssignAndStoreResidual, InterpolateAndStoreModel -- against the same steps
+    on device planes through the C ABI. Stored residuals and models bit for bit."""
+    from helpers import hogbom_case
+    from perform_steps_cases import deconvolution_channels
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n = 256
+    res, psfs, w_orig, f_orig = hogbom_case(n, n_orig, seed=20 + n_orig)
+    w_orig = w_orig.astype(np.float64)
+    kw = dict(minor_loop_gain=0.1, major_loop_gain=0.95)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    r_model[:, 5, 7] = 0.25  # a component of an earlier major iteration
+    start_model = r_model.copy()
+    another, iterations = oracle.ref_radler_perform(
+        r_res, r_model, psfs, f_orig, w_orig, n_dec, auto_threshold_sigma=5.0,
+        minor_iteration_count=400, fit_terms=terms, **kw)
+    assert 30 < iterations <= 400
+
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    f_dec, w_dec = deconvolution_channels(f_orig, w_orig, n_dec)
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    upload = lambda planes: [torch.from_numpy(p).cuda() for p in planes]
+    d_res = torch.zeros((n_dec, n, n), device="cuda")
+    d_model = torch.zeros((n_dec, n, n), device="cuda")
+    d_psf = torch.zeros((n_dec, n, n), device="cuda")
+    alg.load_and_average(upload(res), w_orig, index, list(d_res))
+    alg.load_and_average(upload(start_model), w_orig, index, list(d_model))
+    alg.load_and_average(upload(psfs), w_orig, index, list(d_psf), psfs=True)
+    cube = rdl.Cube(n, n, n_dec, 1, w_dec)
+    integrated = torch.zeros((n, n), device="cuda")
+    alg.integrate(cube, d_res, integrated)
+    _, stddev, _ = alg.median_and_stddev_from_mad(integrated)
+    # radler.cc:233-237, then DeconvolutionAlgorithm::SetThreshold(float)
+    alg.apply(threshold=max(float(np.float32(stddev)) * 5.0, 0.0), max_iterations=400,
+              clean_border_ratio=0.0, **kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, terms, f_dec, w_dec)
+    g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+    assert g.iteration_number == iterations
+    assert g.another_iteration_required == another
+    g_res = d_res.cpu().numpy()
+    for ch, d in enumerate(index):  # AssignAndStoreResidual
+        assert np.array_equal(g_res[d], r_res[ch]), ch
+    if n_dec == n_orig:  # stored as they are (image_set.cc:210-215)
+        g_model = d_model.cpu().numpy()
+    else:
+        d_out = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+        alg.interpolate_model(list(d_model), f_orig, d_out)
+        g_model = np.stack([t.cpu().numpy() for t in d_out])
+    assert np.count_nonzero(r_model) > 4 * n_orig  # several sources, every channel
+    assert np.array_equal(g_model, r_model)

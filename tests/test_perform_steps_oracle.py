@@ -48,3 +48,53 @@ def test_interpolate_model(n_dec, n_orig, n_terms):
     assert np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
     empty = ~models.any(axis=0)
     assert np.all(got[:, empty] == 0.0)
+
+
+@needs_ref
+def test_load_and_average_psfs():
+    rng = np.random.default_rng(0)
+    psfs = rng.standard_normal((8, 32, 40)).astype(np.float32)
+    w = rng.uniform(0.5, 2, 8)
+    w[3] = 0.0
+    got = oracle.ref_load_and_average_psfs(psfs, w, 3)
+    index, n_dec = output_index_of(8, 1, 3)
+    want, sums = np.zeros((n_dec, 32, 40), np.float32), np.zeros(n_dec)
+    for i, d in enumerate(index):  # image_set.cc:186-190: the product and the sum in double
+        want[d] = (want[d].astype(np.float64) + psfs[i].astype(np.float64) * w[i]).astype(np.float32)
+        sums[d] += w[i]
+    for d in range(n_dec):
+        want[d] = (want[d].astype(np.float64) * (1.0 / sums[d])).astype(np.float32)
+    assert np.mean(got != want) < 1e-4  # numpy cannot fuse the multiply-add: rare last-bit cases
+    assert np.allclose(got, want, rtol=2e-7, atol=0)
+
+
+@needs_ref
+def test_radler_perform_is_the_sum_of_its_steps():
+    """radler::Radler::Perform (the reference's own radler.cc) against the same major iteration
+    assembled from the pieces the device tests use as checkers: LoadAndAverage(+Psfs),
+    MedianAndStdDevFromMAD, the restated GenericClean, InterpolateAndStoreModel."""
+    from helpers import hogbom_case
+    from perform_steps_cases import deconvolution_channels
+    n, n_orig, n_dec = 128, 8, 2
+    res, psfs, w_orig, f_orig = hogbom_case(n, n_orig, seed=12)
+    w_orig = w_orig.astype(np.float64)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    another, iterations = oracle.ref_radler_perform(
+        r_res, r_model, psfs, f_orig, w_orig, n_dec, auto_threshold_sigma=5.0,
+        minor_loop_gain=0.1, major_loop_gain=0.9, minor_iteration_count=300, fit_terms=2)
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    f_dec, w_dec = deconvolution_channels(f_orig, w_orig, n_dec)
+    p_res = oracle.ref_load_and_average(res, w_orig, 1, n_dec)
+    p_psf = oracle.ref_load_and_average_psfs(psfs, w_orig, n_dec)
+    cube = oracle.Cube(n, n, n_dec, 1, w_dec)
+    _, std = oracle.ref_median_and_stddev_from_mad(oracle.integrate(cube, p_res))
+    s = oracle.Settings(threshold=float(np.float32(float(std) * 5.0)), max_iterations=300,
+                        minor_loop_gain=0.1, major_loop_gain=0.9, clean_border_ratio=0.0)
+    s.spectral_mode, s.n_terms, s.frequencies, s.fit_weights = 1, 2, f_dec, w_dec
+    p_model = np.zeros_like(p_res)
+    o = oracle.GenericClean(use_sub_minor_optimization=False).execute(cube, s, p_res, p_model, p_psf)
+    assert (o.another_iteration_required, o.iteration_number) == (another, iterations)
+    assert iterations > 10
+    assert np.array_equal(oracle.ref_interpolate_model(p_model, 1, f_dec, w_dec, 2, f_orig), r_model)
+    for ch, d in enumerate(index):
+        assert np.array_equal(p_res[d], r_res[ch])
