@@ -134,9 +134,11 @@ rdl_status rdl_set_clean_border_ratio(rdl_handle* h, float v);            /* Set
 rdl_status rdl_set_divergence_limit(rdl_handle* h, float v);              /* SetDivergenceLimit */
 rdl_status rdl_set_iteration_number(rdl_handle* h, uint64_t n);           /* SetIterationNumber */
 /* SetCleanMask: non-owning const bool* in the reference; here the mask (width*height
- * bytes, host memory) is copied to the device at the call. NULL clears it. */
+ * bytes, host OR device memory -- e.g. what rdl_auto_mask_from_model wrote) is copied at the
+ * call, with a blocking copy that orders after work on the handle's own stream. NULL clears it. */
 rdl_status rdl_set_clean_mask(rdl_handle* h, const uint8_t* mask, uint64_t width, uint64_t height);
-/* SetRmsFactorImage (moved-in aocommon::Image); NULL clears it. Host memory. */
+/* SetRmsFactorImage (moved-in aocommon::Image); NULL clears it. Host or device memory (e.g. the
+ * plane rdl_rms_make_factor_image converted), copied at the call. */
 rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t width, uint64_t height);
 /* SetSpectralFitter(unique_ptr<SpectralFitter>, n_polarizations)
  * (deconvolution_algorithm.h:137-142; fitter built in radler.cc:318-331). */

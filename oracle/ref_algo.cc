@@ -552,13 +552,16 @@ int refa_load_and_average_psfs(const float* const* inputs, const double* weights
 // sub-minor loop: n_original channels (one polarisation) averaged to n_deconvolution channels,
 // the threshold from the MAD noise estimate (auto_threshold_sigma), a polynomial spectral fit,
 // residuals assigned and the model interpolated back to the original channels. residuals /
-// models are read and overwritten through load-and-store accessors, like wsclean's.
+// models are read and overwritten through load-and-store accessors, like wsclean's. With
+// auto_mask_sigma > 0 and several major iterations the two-phase auto-masking runs (:171-185,
+// :221-227, :252-268).
 int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
                         uint64_t n_deconvolution, const double* frequencies,
                         const double* weights, float* const* residuals, float* const* models,
                         const float* const* psfs, double auto_threshold_sigma,
                         double minor_loop_gain, double major_loop_gain,
                         uint64_t minor_iteration_count, uint64_t fit_terms,
+                        double auto_mask_sigma, uint64_t n_major_iterations,
                         int32_t* another_iteration_required, uint64_t* iteration_number) {
   return Guard(nullptr, [&] {
     class BufferAccessor final : public aocommon::ImageAccessor {
@@ -580,6 +583,7 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
     s.algorithm_type = AlgorithmType::kGenericClean;
     s.generic.use_sub_minor_optimization = false;
     s.auto_threshold_sigma = auto_threshold_sigma;
+    if (auto_mask_sigma > 0.0) s.auto_mask_sigma = auto_mask_sigma;
     s.minor_loop_gain = minor_loop_gain;
     s.major_loop_gain = major_loop_gain;
     s.minor_iteration_count = minor_iteration_count;
@@ -602,10 +606,14 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
       table->AddEntry(std::move(e));
     }
     Radler radler(s, std::move(table), 0.0);
-    bool another = false;
-    radler.Perform(another, 1);
-    *another_iteration_required = another ? 1 : 0;
-    *iteration_number = radler.IterationNumber();
+    // successive major iterations on the stored residuals (no re-imaging in between); the
+    // flag and the iteration count after each one
+    for (uint64_t major = 0; major != n_major_iterations; ++major) {
+      bool another = false;
+      radler.Perform(another, major + 1);
+      another_iteration_required[major] = another ? 1 : 0;
+      iteration_number[major] = radler.IterationNumber();
+    }
   });
 }
 

@@ -359,12 +359,20 @@ class DeconvolutionAlgorithm:
         if mask is None:
             self._check(lib().rdl_set_clean_mask(self._h, None, 0, 0))
             return
+        if hasattr(mask, "data_ptr"):  # a uint8 device plane, e.g. from auto_mask_from_model
+            self._check(lib().rdl_set_clean_mask(self._h, mask.data_ptr(), mask.shape[1],
+                                                 mask.shape[0]))
+            return
         m = np.ascontiguousarray(mask, np.uint8)
         self._check(lib().rdl_set_clean_mask(self._h, m.ctypes.data, m.shape[1], m.shape[0]))
 
     def set_rms_factor_image(self, image):
         if image is None:
             self._check(lib().rdl_set_rms_factor_image(self._h, None, 0, 0))
+            return
+        if hasattr(image, "data_ptr"):  # a float32 device plane, e.g. from rms_make_factor_image
+            self._check(lib().rdl_set_rms_factor_image(self._h, image.data_ptr(), image.shape[1],
+                                                       image.shape[0]))
             return
         a = np.ascontiguousarray(image, np.float32)
         self._check(lib().rdl_set_rms_factor_image(self._h, a.ctypes.data, a.shape[1], a.shape[0]))

@@ -127,6 +127,16 @@ void UnpinAll(rdl_handle* h) {
   h->pinned.clear();
 }
 
+// Device (or managed) memory? Host pointers CUDA does not know about are host memory.
+bool IsDevicePointer(const void* p) {
+  cudaPointerAttributes attributes{};
+  if (cudaPointerGetAttributes(&attributes, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return attributes.type == cudaMemoryTypeDevice || attributes.type == cudaMemoryTypeManaged;
+}
+
 cudaStream_t StreamOf(rdl_handle* h, void* stream) {
   return stream ? static_cast<cudaStream_t>(stream) : h->own_stream;
 }
@@ -294,9 +304,15 @@ rdl_status rdl_set_clean_mask(rdl_handle* h, const uint8_t* mask, uint64_t width
       h->mask_w = h->mask_h = 0;
       return;
     }
-    h->mask_host.assign(mask, mask + width * height);
     h->mask.Resize(width * height);
-    RDL_CUDA(cudaMemcpy(h->mask.get(), mask, width * height, cudaMemcpyHostToDevice));
+    if (IsDevicePointer(mask)) {  // e.g. the output of rdl_auto_mask_from_model
+      h->mask_host.resize(width * height);
+      RDL_CUDA(cudaMemcpy(h->mask_host.data(), mask, width * height, cudaMemcpyDeviceToHost));
+      RDL_CUDA(cudaMemcpy(h->mask.get(), mask, width * height, cudaMemcpyDeviceToDevice));
+    } else {
+      h->mask_host.assign(mask, mask + width * height);
+      RDL_CUDA(cudaMemcpy(h->mask.get(), mask, width * height, cudaMemcpyHostToDevice));
+    }
     h->mask_w = width;
     h->mask_h = height;
   });
@@ -314,10 +330,18 @@ rdl_status rdl_set_rms_factor_image(rdl_handle* h, const float* image, uint64_t 
       h->rms_w = h->rms_h = 0;
       return;
     }
-    h->rms_host.assign(image, image + width * height);
     h->rms.Resize(width * height);
-    RDL_CUDA(cudaMemcpy(h->rms.get(), image, width * height * sizeof(float),
-                        cudaMemcpyHostToDevice));
+    if (IsDevicePointer(image)) {  // e.g. the output of rdl_rms_make_factor_image
+      h->rms_host.resize(width * height);
+      RDL_CUDA(cudaMemcpy(h->rms_host.data(), image, width * height * sizeof(float),
+                          cudaMemcpyDeviceToHost));
+      RDL_CUDA(cudaMemcpy(h->rms.get(), image, width * height * sizeof(float),
+                          cudaMemcpyDeviceToDevice));
+    } else {
+      h->rms_host.assign(image, image + width * height);
+      RDL_CUDA(cudaMemcpy(h->rms.get(), image, width * height * sizeof(float),
+                          cudaMemcpyHostToDevice));
+    }
     h->rms_w = width;
     h->rms_h = height;
   });

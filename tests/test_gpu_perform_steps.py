@@ -324,3 +324,91 @@ def test_radler_perform_major_iteration(rdl, oracle, torch_cuda, n_orig, n_dec, 
         g_model = np.stack([t.cpu().numpy() for t in d_out])
     assert np.count_nonzero(r_model) > 4 * n_orig  # several sources, every channel
     assert np.array_equal(g_model, r_model)
+
+
+def test_radler_perform_two_phase_auto_mask(rdl, oracle, torch_cuda):
+    """Two major iterations of radler::Radler::Perform (the reference's own radler.cc) with
+    auto-masking: the first cleans to auto_mask_sigma, the second doubles the minor-loop gain
+    (:171-177), cleans to auto_threshold_sigma (:233-237) under the mask derived from the
+    averaged model planes (:252-268). The device side keeps everything in device memory: the
+    mask goes from rdl_auto_mask_from_model straight into rdl_set_clean_mask."""
+    from helpers import hogbom_case
+    from perform_steps_cases import deconvolution_channels
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, n_orig, n_dec, terms = 256, 8, 2, 2
+    res, psfs, w_orig, f_orig = hogbom_case(n, n_orig, seed=28)
+    w_orig = w_orig.astype(np.float64)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    per_major = oracle.ref_radler_perform(
+        r_res, r_model, psfs, f_orig, w_orig, n_dec, auto_threshold_sigma=3.0,
+        minor_loop_gain=0.1, major_loop_gain=1.0, minor_iteration_count=2000, fit_terms=terms,
+        auto_mask_sigma=8.0, n_major_iterations=2)
+    assert per_major[0][0] and per_major[0][1] > 50 and per_major[1][1] > per_major[0][1] + 50
+
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    f_dec, w_dec = deconvolution_channels(f_orig, w_orig, n_dec)
+    alg = rdl.GenericClean(use_sub_minor_optimization=False)
+    alg.apply(max_iterations=2000, major_loop_gain=1.0, clean_border_ratio=0.0)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, terms, f_dec, w_dec)
+    cube = rdl.Cube(n, n, n_dec, 1, w_dec)
+    # the caller's planes of the original channels, kept on the device across major iterations
+    s_res = [torch.from_numpy(p).cuda() for p in res]
+    s_model = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+    s_psf = [torch.from_numpy(p).cuda() for p in psfs]
+    d_res = torch.zeros((n_dec, n, n), device="cuda")
+    d_model = torch.zeros((n_dec, n, n), device="cuda")
+    d_psf = torch.zeros((n_dec, n, n), device="cuda")
+    integrated = torch.zeros((n, n), device="cuda")
+    mask = torch.zeros((n, n), dtype=torch.uint8, device="cuda")
+    finished = False
+    for major in range(2):
+        alg.load_and_average(s_res, w_orig, index, list(d_res))
+        alg.load_and_average(s_model, w_orig, index, list(d_model))
+        alg.integrate(cube, d_res, integrated)
+        _, stddev, _ = alg.median_and_stddev_from_mad(integrated)
+        stddev = float(np.float32(stddev))
+        if finished:
+            alg.apply(minor_loop_gain=min(1.0, 0.1 * 2.0), threshold=max(stddev * 3.0, 0.0))
+            alg.auto_mask_from_model(list(d_model), mask)
+            alg.set_clean_mask(mask)
+        else:
+            alg.apply(minor_loop_gain=0.1, threshold=max(stddev * 8.0, 0.0))
+        alg.load_and_average(s_psf, w_orig, index, list(d_psf), psfs=True)
+        g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+        another = g.another_iteration_required
+        if not another and not finished:
+            finished, another = True, True
+        assert (another, g.iteration_number) == per_major[major], major
+        for ch, d in enumerate(index):  # AssignAndStoreResidual
+            s_res[ch].copy_(d_res[d])
+        alg.interpolate_model(list(d_model), f_orig, s_model)
+    assert finished and 0 < int(mask.sum()) < 100
+    assert np.array_equal(np.stack([t.cpu().numpy() for t in s_res]), r_res)
+    assert np.array_equal(np.stack([t.cpu().numpy() for t in s_model]), r_model)
+
+
+def test_rms_factor_image_from_a_device_plane(rdl, torch_cuda):
+    """rdl_set_rms_factor_image / rdl_set_clean_mask take device planes as well: same peaks as
+    with the host copies."""
+    from helpers import hogbom_case
+    torch = torch_cuda
+    n = 128
+    res, psfs, _, _ = hogbom_case(n, 1, seed=3)
+    rng = np.random.default_rng(3)
+    factor = rng.uniform(0.5, 1.0, (n, n)).astype(np.float32)
+    mask = (rng.uniform(size=(n, n)) > 0.3).astype(np.uint8)
+    traces = []
+    for device in (False, True):
+        alg = rdl.GenericClean(use_sub_minor_optimization=False)
+        alg.apply(max_iterations=60, clean_border_ratio=0.0, trace_capacity=1 << 10)
+        alg.set_rms_factor_image(torch.from_numpy(factor).cuda() if device else factor)
+        alg.set_clean_mask(torch.from_numpy(mask).cuda() if device else mask)
+        d_res, d_model = torch.from_numpy(res.copy()).cuda(), torch.zeros((1, n, n), device="cuda")
+        alg.execute_major_iteration(rdl.Cube(n, n, 1, 1, None), d_res, d_model,
+                                    torch.from_numpy(psfs).cuda())
+        traces.append(alg.trace())
+    assert len(traces[0]) == 60
+    for k in ("x", "y", "value"):
+        assert np.array_equal(traces[0][k], traces[1][k])
