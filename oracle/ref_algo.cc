@@ -548,8 +548,8 @@ int refa_load_and_average_psfs(const float* const* inputs, const double* weights
   });
 }
 
-// Radler::Perform itself (radler.cc:130-316), one major iteration of GenericClean without the
-// sub-minor loop: n_original channels (one polarisation) averaged to n_deconvolution channels,
+// Radler::Perform itself (radler.cc:130-316), major iterations of GenericClean with or without
+// the sub-minor loop: n_original channels (one polarisation) averaged to n_deconvolution channels,
 // the threshold from the MAD noise estimate (auto_threshold_sigma), a polynomial spectral fit,
 // residuals assigned and the model interpolated back to the original channels. residuals /
 // models are read and overwritten through load-and-store accessors, like wsclean's. With
@@ -562,7 +562,8 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
                         double minor_loop_gain, double major_loop_gain,
                         uint64_t minor_iteration_count, uint64_t fit_terms,
                         double auto_mask_sigma, uint64_t n_major_iterations,
-                        int32_t* another_iteration_required, uint64_t* iteration_number) {
+                        int32_t use_sub_minor_optimization, int32_t* another_iteration_required,
+                        uint64_t* iteration_number) {
   return Guard(nullptr, [&] {
     class BufferAccessor final : public aocommon::ImageAccessor {
      public:
@@ -581,7 +582,7 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
     s.trimmed_image_height = height;
     s.channels_out = n_original;
     s.algorithm_type = AlgorithmType::kGenericClean;
-    s.generic.use_sub_minor_optimization = false;
+    s.generic.use_sub_minor_optimization = use_sub_minor_optimization != 0;
     s.auto_threshold_sigma = auto_threshold_sigma;
     if (auto_mask_sigma > 0.0) s.auto_mask_sigma = auto_mask_sigma;
     s.minor_loop_gain = minor_loop_gain;

@@ -412,3 +412,48 @@ def test_rms_factor_image_from_a_device_plane(rdl, torch_cuda):
     assert len(traces[0]) == 60
     for k in ("x", "y", "value"):
         assert np.array_equal(traces[0][k], traces[1][k])
+
+
+def test_radler_perform_with_the_sub_minor_loop(rdl, oracle, torch_cuda):
+    """The same major iteration through the reference's DEFAULT GenericClean (sub-minor loop,
+    CorrectResidualDirty through FFT convolutions): components and model bit for bit, the stored
+    residuals within 1e-5 of the peak (FFT round-off, as in the path-A tests)."""
+    from helpers import hogbom_case
+    from perform_steps_cases import deconvolution_channels
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, n_orig, n_dec, terms = 256, 8, 2, 2
+    res, psfs, w_orig, f_orig = hogbom_case(n, n_orig, seed=28)
+    w_orig = w_orig.astype(np.float64)
+    kw = dict(minor_loop_gain=0.1, major_loop_gain=0.9)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    another, iterations = oracle.ref_radler_perform(
+        r_res, r_model, psfs, f_orig, w_orig, n_dec, auto_threshold_sigma=5.0,
+        minor_iteration_count=2000, fit_terms=terms, use_sub_minor_optimization=True, **kw)
+    assert iterations > 50
+
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    f_dec, w_dec = deconvolution_channels(f_orig, w_orig, n_dec)
+    alg = rdl.GenericClean(use_sub_minor_optimization=True)
+    upload = lambda planes: [torch.from_numpy(p).cuda() for p in planes]
+    d_res = torch.zeros((n_dec, n, n), device="cuda")
+    d_model = torch.zeros((n_dec, n, n), device="cuda")
+    d_psf = torch.zeros((n_dec, n, n), device="cuda")
+    alg.load_and_average(upload(res), w_orig, index, list(d_res))
+    alg.load_and_average(upload(psfs), w_orig, index, list(d_psf), psfs=True)
+    cube = rdl.Cube(n, n, n_dec, 1, w_dec)
+    integrated = torch.zeros((n, n), device="cuda")
+    alg.integrate(cube, d_res, integrated)
+    _, stddev, _ = alg.median_and_stddev_from_mad(integrated)
+    alg.apply(threshold=max(float(np.float32(stddev)) * 5.0, 0.0), max_iterations=2000,
+              clean_border_ratio=0.0, **kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, terms, f_dec, w_dec)
+    g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+    assert (g.another_iteration_required, g.iteration_number) == (another, iterations)
+    d_out = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+    alg.interpolate_model(list(d_model), f_orig, d_out)
+    assert np.array_equal(np.stack([t.cpu().numpy() for t in d_out]), r_model)
+    g_res, peak = d_res.cpu().numpy(), np.abs(res).max()
+    for ch, d in enumerate(index):
+        assert np.abs(g_res[d] - r_res[ch]).max() <= 1e-5 * peak, ch
