@@ -716,7 +716,8 @@ def ref_interpolate_model(models, n_pol, fit_frequencies, fit_weights, n_terms,
 def ref_radler_perform(residuals, models, psfs, frequencies, weights, n_deconvolution, *,
                        auto_threshold_sigma, minor_loop_gain, major_loop_gain,
                        minor_iteration_count, fit_terms, auto_mask_sigma=0.0,
-                       n_major_iterations=1, use_sub_minor_optimization=False):
+                       n_major_iterations=1, use_sub_minor_optimization=False,
+                       multiscale=False, beam_size=0.0, pixel_scale=1.0):
     """radler::Radler::Perform of the reference's own radler.cc (major iterations of
     GenericClean, one polarisation). `residuals` / `models`
     (n_original, h, w) are overwritten the way wsclean's load-and-store accessors are.
@@ -733,11 +734,13 @@ def ref_radler_perform(residuals, models, psfs, frequencies, weights, n_deconvol
     iterations = (C.c_uint64 * n_major_iterations)()
     f = ref_lib().refa_radler_perform
     f.argtypes = [C.c_uint64] * 4 + [C.c_void_p] * 5 + [C.c_double] * 3 + [C.c_uint64] * 2 + \
-        [C.c_double, C.c_uint64, C.c_int32] + [C.c_void_p] * 2
+        [C.c_double, C.c_uint64, C.c_int32, C.c_int32, C.c_double, C.c_double] + \
+        [C.c_void_p] * 2
     if f(w, h, n, n_deconvolution, fr.ctypes.data, wt.ctypes.data, tables[0], tables[1],
          tables[2], float(auto_threshold_sigma), float(minor_loop_gain), float(major_loop_gain),
          int(minor_iteration_count), int(fit_terms), float(auto_mask_sigma),
-         int(n_major_iterations), int(use_sub_minor_optimization), another, iterations) != 0:
+         int(n_major_iterations), int(use_sub_minor_optimization), int(multiscale),
+         float(beam_size), float(pixel_scale), another, iterations) != 0:
         err = ref_lib().refa_last_error
         err.restype = C.c_char_p
         err.argtypes = [C.c_void_p]

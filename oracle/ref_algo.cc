@@ -562,8 +562,9 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
                         double minor_loop_gain, double major_loop_gain,
                         uint64_t minor_iteration_count, uint64_t fit_terms,
                         double auto_mask_sigma, uint64_t n_major_iterations,
-                        int32_t use_sub_minor_optimization, int32_t* another_iteration_required,
-                        uint64_t* iteration_number) {
+                        int32_t use_sub_minor_optimization, int32_t multiscale,
+                        double beam_size, double pixel_scale,
+                        int32_t* another_iteration_required, uint64_t* iteration_number) {
   return Guard(nullptr, [&] {
     class BufferAccessor final : public aocommon::ImageAccessor {
      public:
@@ -581,7 +582,8 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
     s.trimmed_image_width = width;
     s.trimmed_image_height = height;
     s.channels_out = n_original;
-    s.algorithm_type = AlgorithmType::kGenericClean;
+    s.algorithm_type = multiscale ? AlgorithmType::kMultiscale : AlgorithmType::kGenericClean;
+    s.pixel_scale.x = s.pixel_scale.y = pixel_scale;
     s.generic.use_sub_minor_optimization = use_sub_minor_optimization != 0;
     s.auto_threshold_sigma = auto_threshold_sigma;
     if (auto_mask_sigma > 0.0) s.auto_mask_sigma = auto_mask_sigma;
@@ -606,7 +608,7 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
           std::make_unique<BufferAccessor>(const_cast<float*>(psfs[ch]), width, height));
       table->AddEntry(std::move(e));
     }
-    Radler radler(s, std::move(table), 0.0);
+    Radler radler(s, std::move(table), beam_size);
     // successive major iterations on the stored residuals (no re-imaging in between); the
     // flag and the iteration count after each one
     for (uint64_t major = 0; major != n_major_iterations; ++major) {

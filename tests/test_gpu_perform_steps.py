@@ -457,3 +457,50 @@ def test_radler_perform_with_the_sub_minor_loop(rdl, oracle, torch_cuda):
     g_res, peak = d_res.cpu().numpy(), np.abs(res).max()
     for ch, d in enumerate(index):
         assert np.abs(g_res[d] - r_res[ch]).max() <= 1e-5 * peak, ch
+
+
+def test_radler_perform_multiscale(rdl, oracle, torch_cuda):
+    """One major iteration of radler::Radler::Perform with AlgorithmType::kMultiscale (4
+    original channels averaged to 2, polynomial fit) against the device steps around
+    MultiScaleAlgorithm: same component count and stop reason, stored residuals and interpolated
+    models within 1e-4 of their peak (the scale convolutions are FFTs on both sides)."""
+    from helpers import multiscale_case
+    from perform_steps_cases import deconvolution_channels
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n, n_orig, n_dec, terms, beam = 256, 4, 2, 2, 6.0
+    res, psfs, w_orig, f_orig = multiscale_case(n, n_orig, seed=5)
+    w_orig = w_orig.astype(np.float64)
+    kw = dict(minor_loop_gain=0.1, major_loop_gain=0.8)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    another, iterations = oracle.ref_radler_perform(
+        r_res, r_model, psfs, f_orig, w_orig, n_dec, auto_threshold_sigma=5.0,
+        minor_iteration_count=500, fit_terms=terms, multiscale=True, beam_size=beam, **kw)
+    assert iterations > 40
+
+    index, _ = output_index_of(n_orig, 1, n_dec)
+    f_dec, w_dec = deconvolution_channels(f_orig, w_orig, n_dec)
+    alg = rdl.MultiScaleAlgorithm(beam, 1.0)
+    upload = lambda planes: [torch.from_numpy(p).cuda() for p in planes]
+    d_res = torch.zeros((n_dec, n, n), device="cuda")
+    d_model = torch.zeros((n_dec, n, n), device="cuda")
+    d_psf = torch.zeros((n_dec, n, n), device="cuda")
+    alg.load_and_average(upload(res), w_orig, index, list(d_res))
+    alg.load_and_average(upload(psfs), w_orig, index, list(d_psf), psfs=True)
+    cube = rdl.Cube(n, n, n_dec, 1, w_dec)
+    integrated = torch.zeros((n, n), device="cuda")
+    alg.integrate(cube, d_res, integrated)
+    _, stddev, _ = alg.median_and_stddev_from_mad(integrated)
+    alg.apply(threshold=max(float(np.float32(stddev)) * 5.0, 0.0), max_iterations=500,
+              clean_border_ratio=0.0, **kw)
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, terms, f_dec, w_dec)
+    g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+    assert (g.another_iteration_required, g.iteration_number) == (another, iterations)
+    d_out = [torch.zeros((n, n), device="cuda") for _ in range(n_orig)]
+    alg.interpolate_model(list(d_model), f_orig, d_out)
+    g_model = np.stack([t.cpu().numpy() for t in d_out])
+    assert np.abs(g_model - r_model).max() <= 1e-4 * np.abs(r_model).max()
+    g_res, peak = d_res.cpu().numpy(), np.abs(res).max()
+    for ch, d in enumerate(index):
+        assert np.abs(g_res[d] - r_res[ch]).max() <= 1e-4 * peak, ch
