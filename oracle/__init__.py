@@ -717,7 +717,7 @@ def ref_radler_perform(residuals, models, psfs, frequencies, weights, n_deconvol
                        auto_threshold_sigma, minor_loop_gain, major_loop_gain,
                        minor_iteration_count, fit_terms, auto_mask_sigma=0.0,
                        n_major_iterations=1, use_sub_minor_optimization=False,
-                       multiscale=False, beam_size=0.0, pixel_scale=1.0):
+                       multiscale=False, beam_size=0.0, pixel_scale=1.0, iuwt=False):
     """radler::Radler::Perform of the reference's own radler.cc (major iterations of
     GenericClean, one polarisation). `residuals` / `models`
     (n_original, h, w) are overwritten the way wsclean's load-and-store accessors are.
@@ -739,7 +739,8 @@ def ref_radler_perform(residuals, models, psfs, frequencies, weights, n_deconvol
     if f(w, h, n, n_deconvolution, fr.ctypes.data, wt.ctypes.data, tables[0], tables[1],
          tables[2], float(auto_threshold_sigma), float(minor_loop_gain), float(major_loop_gain),
          int(minor_iteration_count), int(fit_terms), float(auto_mask_sigma),
-         int(n_major_iterations), int(use_sub_minor_optimization), int(multiscale),
+         int(n_major_iterations), int(use_sub_minor_optimization),
+         2 if iuwt else int(multiscale),
          float(beam_size), float(pixel_scale), another, iterations) != 0:
         err = ref_lib().refa_last_error
         err.restype = C.c_char_p

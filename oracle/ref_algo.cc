@@ -562,7 +562,7 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
                         double minor_loop_gain, double major_loop_gain,
                         uint64_t minor_iteration_count, uint64_t fit_terms,
                         double auto_mask_sigma, uint64_t n_major_iterations,
-                        int32_t use_sub_minor_optimization, int32_t multiscale,
+                        int32_t use_sub_minor_optimization, int32_t algorithm,
                         double beam_size, double pixel_scale,
                         int32_t* another_iteration_required, uint64_t* iteration_number) {
   return Guard(nullptr, [&] {
@@ -582,7 +582,9 @@ int refa_radler_perform(uint64_t width, uint64_t height, uint64_t n_original,
     s.trimmed_image_width = width;
     s.trimmed_image_height = height;
     s.channels_out = n_original;
-    s.algorithm_type = multiscale ? AlgorithmType::kMultiscale : AlgorithmType::kGenericClean;
+    s.algorithm_type = algorithm == 1   ? AlgorithmType::kMultiscale
+                       : algorithm == 2 ? AlgorithmType::kIuwt
+                                        : AlgorithmType::kGenericClean;
     s.pixel_scale.x = s.pixel_scale.y = pixel_scale;
     s.generic.use_sub_minor_optimization = use_sub_minor_optimization != 0;
     s.auto_threshold_sigma = auto_threshold_sigma;

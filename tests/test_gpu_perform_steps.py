@@ -504,3 +504,39 @@ def test_radler_perform_multiscale(rdl, oracle, torch_cuda):
     g_res, peak = d_res.cpu().numpy(), np.abs(res).max()
     for ch, d in enumerate(index):
         assert np.abs(g_res[d] - r_res[ch]).max() <= 1e-4 * peak, ch
+
+
+def test_radler_perform_iuwt(rdl, oracle, torch_cuda):
+    """One major iteration of radler::Radler::Perform with AlgorithmType::kIuwt on one channel:
+    same iteration count and flag, images within 1e-5 of the peak (tests/
+    test_gpu_iuwt_deconvolution.py says why not bit for bit)."""
+    from helpers import multiscale_case
+    torch = torch_cuda
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    n = 256
+    res, psfs, _, freqs = multiscale_case(n, 1, seed=3)
+    kw = dict(minor_loop_gain=0.1, major_loop_gain=0.8)
+    r_res, r_model = res.copy(), np.zeros_like(res)
+    another, iterations = oracle.ref_radler_perform(
+        r_res, r_model, psfs, freqs, np.ones(1), 1, auto_threshold_sigma=3.0,
+        minor_iteration_count=12, fit_terms=0, iuwt=True, **kw)
+    assert iterations > 3 and np.abs(r_model).max() > 0
+
+    alg = rdl.DeconvolutionAlgorithm(rdl.IUWT)
+    d_res = torch.zeros((1, n, n), device="cuda")
+    d_psf = torch.zeros((1, n, n), device="cuda")
+    d_model = torch.zeros((1, n, n), device="cuda")
+    alg.load_and_average([torch.from_numpy(res[0]).cuda()], [1.0], [0], list(d_res))
+    alg.load_and_average([torch.from_numpy(psfs[0]).cuda()], [1.0], [0], list(d_psf), psfs=True)
+    cube = rdl.Cube(n, n, 1, 1, None)
+    integrated = torch.zeros((n, n), device="cuda")
+    alg.integrate(cube, d_res, integrated)
+    _, stddev, _ = alg.median_and_stddev_from_mad(integrated)
+    alg.apply(threshold=max(float(np.float32(stddev)) * 3.0, 0.0), max_iterations=12,
+              clean_border_ratio=0.0, **kw)
+    g = alg.execute_major_iteration(cube, d_res, d_model, d_psf)
+    assert (g.another_iteration_required, g.iteration_number) == (another, iterations)
+    peak = np.abs(res).max()
+    assert np.abs(d_res.cpu().numpy() - r_res).max() <= 1e-5 * peak
+    assert np.abs(d_model.cpu().numpy() - r_model).max() <= 1e-5 * peak
