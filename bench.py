@@ -634,10 +634,59 @@ def run_ours(args):
                     "speedup_device": best * 1e3 / (ms_total / 2),
                     "speedup_e2e": best * 1e3 / ms["e2e"]["ms_per_step"]}
             line["multiscale"] = ms
+            try:
+                line["perform_steps"] = perform_steps(rdl, ms_alg, ms_cube, ms_res0, ms_f, ms_w)
+            except Exception as e:  # informational: never costs the line
+                line["perform_steps"] = {"error": str(e)}
             del ms_res0, ms_psfs, ms_alg
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def perform_steps(rdl, alg, cube, planes, freqs, weights, n_dec=4):
+    """What Radler::Perform does either side of ExecuteMajorIteration (SURVEY 8(f) rank 1), on the
+    device-resident cube: the planes taken as original channels averaged to n_dec deconvolution
+    channels, the MAD noise estimate of the integrated cube, the auto-mask from the model, the
+    model interpolated back. Milliseconds per step (CUDA events on torch's stream, which the
+    handle's own blocking stream orders with; the MAD and the interpolation synchronise)."""
+    import torch
+    c, n, _ = planes.shape
+    dev = planes.device
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    index = [ch * n_dec // c for ch in range(c)]
+    w64 = [float(w) for w in (weights if weights is not None else [1.0] * c)]
+    averaged = torch.zeros((n_dec, n, n), device=dev)
+    integrated = torch.zeros((n, n), device=dev)
+    mask = torch.zeros((n, n), dtype=torch.uint8, device=dev)
+    out = {"frame": n, "original_channels": c, "deconvolution_channels": n_dec}
+    out["load_and_average_ms"] = timed(lambda: alg.load_and_average(list(planes), w64, index,
+                                                                    list(averaged)))
+    out["integrate_ms"] = timed(lambda: alg.integrate(cube, planes, integrated))
+    out["median_and_stddev_from_mad_ms"] = timed(lambda: alg.median_and_stddev_from_mad(integrated))
+    out["stddev"] = alg.median_and_stddev_from_mad(integrated)[1]
+    out["auto_mask_from_model_ms"] = timed(lambda: alg.auto_mask_from_model(list(averaged), mask))
+    fit = [sum(freqs[ch] for ch in range(c) if index[ch] == d) / index.count(d)
+           for d in range(n_dec)]
+    alg.set_spectral_fitter(rdl.FIT_POLYNOMIAL, 2, fit, None)
+    outputs = [torch.empty((n, n), device=dev) for _ in range(c)]
+    out["interpolate_model_ms"] = timed(lambda: alg.interpolate_model(list(averaged), list(freqs),
+                                                                      outputs))
+    out["note"] = ("device planes only; parity of each step and of the whole sequence against "
+                   "radler::Radler::Perform of the reference's own sources: "
+                   "tests/test_gpu_perform_steps.py")
+    return out
 
 
 # --------------------------------------------------------------------------------------
