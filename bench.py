@@ -89,7 +89,7 @@ class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,power.limit,clocks.mem")
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
@@ -115,18 +115,28 @@ class ClockSampler:
         self.proc.terminate()
         self.thread.join(timeout=2)
         sm, mx, reasons = [], None, set()
+        power, limit, mem = [], None, []
         for r in self.rows:
             try:
                 sm.append(float(r[0]))
                 mx = float(r[1])
             except (ValueError, IndexError):
                 continue
+            try:  # what a power-capped box looks like: draw at the limit, SM clock below max
+                power.append(float(r[2]))
+                limit = float(r[7])
+                mem.append(float(r[8]))
+            except (ValueError, IndexError):
+                pass
             for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
                                 "sw_power_cap"], r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm),
+                "sm_min_mhz": float(min(sm)) if sm else None,
+                "power_w": float(np.median(power)) if power else None, "power_limit_w": limit,
+                "mem_mhz": float(np.median(mem)) if mem else None}
 
 
 def profile_traffic(name, kernels=None):
