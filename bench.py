@@ -748,6 +748,9 @@ def fft_roofline(rdl, n_pad, dev):
             "avg_launch_us": per_conv_s * 1e6 / 5.0, "us_per_convolution": per_conv_s * 1e6}
 
 
+STEP_MS = []  # this rank's time of each timed step of the last run_multiscale_device
+
+
 def run_multiscale_device(rdl, alg, cube, res0, psfs, steps, warmup, barrier, stream):
     """Device-resident timing of `steps` major iterations; returns (ms_total, last result,
     minor iterations, launches)."""
@@ -771,8 +774,10 @@ def run_multiscale_device(rdl, alg, cube, res0, psfs, steps, warmup, barrier, st
     barrier()
     l0 = alg.kernel_launch_count
     total, minor, r = 0.0, 0, None
+    STEP_MS.clear()
     for _ in range(steps):
         ms, r = one()
+        STEP_MS.append(ms)
         total += ms
         minor += alg.minor_iteration_count
     barrier()
@@ -845,6 +850,7 @@ def run_ours_multiscale(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t[0]) / args.steps
+    step_ms = list(STEP_MS)
 
     # ---- e2e: the same call with pinned HOST buffers --------------------------------------
     h_res = torch.empty((c, n, n), dtype=torch.float32).pin_memory()
@@ -875,7 +881,8 @@ def run_ours_multiscale(args):
             "metric": "multiscale major-iteration time (MultiScaleAlgorithm::ExecuteMajorIteration)",
             "value": ms_per_step, "unit": "ms per major iteration",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
+            "ms_per_step": ms_per_step, "step_ms_rank0": step_ms, "higher_is_better": False,
+            "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"multiscale {n}^2 x {c} channels joined, 5 scales, polynomial "
                                    f"fit 2 terms, mgain 0.8, max {iters} components per major "
