@@ -22,11 +22,19 @@ namespace rdl {
 namespace {
 
 // ---- exact selection: three histogram passes over the 32 key bits (11 + 11 + 10) -------------
+// A median needs the upper middle element and, for an even count, the lower middle one: both
+// ranks are narrowed together. They share one histogram until they fall into different bins
+// (adjacent order statistics rarely do before the last pass); from then on a pixel is counted in
+// the histogram of whichever prefix it matches.
 
 // h.iuwt_scalars words used here (the IUWT entry points use the same scratch; calls on one
-// handle are ordered): [2] key prefix found so far, [3] rank left inside it, [5] finite pixels;
-// the histogram sits at kIuwtHistWord (2048 unsigned).
-constexpr int kPrefixWord = 2, kRankWord = 3, kCountWord = 5;
+// handle are ordered): [2] / [6] key prefix found so far for the lower / upper rank, [3] / [7]
+// rank left inside it, [5] finite pixels; the two histograms (2048 unsigned each) sit at
+// kIuwtHistWord and behind it.
+constexpr int kPrefixLo = 2, kRankLo = 3, kPrefixHi = 6, kRankHi = 7;
+constexpr int kCountWord = 5;
+constexpr int kHistogramBins = 2048;
+constexpr int kSelectWords = kIuwtHistWord + 2 * kHistogramBins / 2;
 
 struct SelectPass {
   int shift, bits, prefix_shift;  // bin = (key >> shift) & mask; prefix = key >> prefix_shift
@@ -40,21 +48,30 @@ __device__ __forceinline__ unsigned OrderedBits(float v) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-__device__ __forceinline__ void Count(float v, const SelectPass& pass, unsigned prefix, unsigned mask,
-                                      unsigned* bins) {
+__device__ __forceinline__ void Count(float v, const SelectPass& pass, unsigned prefix_lo,
+                                      unsigned prefix_hi, unsigned mask, unsigned* bins) {
   if ((__float_as_uint(v) & 0x7f800000u) == 0x7f800000u) return;  // std::isfinite
   const unsigned key = pass.deviation ? __float_as_uint(fabsf(v - pass.centre)) : OrderedBits(v);
-  if (pass.prefix_shift < 32 && (key >> pass.prefix_shift) != prefix) return;
-  atomicAdd(&bins[(key >> pass.shift) & mask], 1u);
+  const unsigned bin = (key >> pass.shift) & mask;
+  if (pass.prefix_shift >= 32) {
+    atomicAdd(&bins[bin], 1u);
+    return;
+  }
+  const unsigned prefix = key >> pass.prefix_shift;
+  if (prefix == prefix_lo)
+    atomicAdd(&bins[bin], 1u);
+  else if (prefix == prefix_hi)
+    atomicAdd(&bins[kHistogramBins + bin], 1u);
 }
 
 __global__ void __launch_bounds__(512)
 SelectHistogramKernel(const float* __restrict__ image, size_t n, SelectPass pass,
                       const unsigned long long* __restrict__ scalars, unsigned* histogram) {
-  __shared__ unsigned bins[2048];
-  for (int i = threadIdx.x; i < 2048; i += blockDim.x) bins[i] = 0;
+  __shared__ unsigned bins[2 * kHistogramBins];
+  for (int i = threadIdx.x; i < 2 * kHistogramBins; i += blockDim.x) bins[i] = 0;
   __syncthreads();
-  const unsigned prefix = unsigned(scalars[kPrefixWord]);
+  const unsigned prefix_lo = unsigned(scalars[kPrefixLo]);
+  const unsigned prefix_hi = unsigned(scalars[kPrefixHi]);
   const unsigned mask = (1u << pass.bits) - 1u;
   const size_t stride = size_t(gridDim.x) * blockDim.x;
   const size_t first = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -62,66 +79,73 @@ SelectHistogramKernel(const float* __restrict__ image, size_t n, SelectPass pass
     const float4* image4 = reinterpret_cast<const float4*>(image);
     for (size_t i = first; i < n / 4; i += stride) {
       const float4 v = __ldg(image4 + i);
-      Count(v.x, pass, prefix, mask, bins);
-      Count(v.y, pass, prefix, mask, bins);
-      Count(v.z, pass, prefix, mask, bins);
-      Count(v.w, pass, prefix, mask, bins);
+      Count(v.x, pass, prefix_lo, prefix_hi, mask, bins);
+      Count(v.y, pass, prefix_lo, prefix_hi, mask, bins);
+      Count(v.z, pass, prefix_lo, prefix_hi, mask, bins);
+      Count(v.w, pass, prefix_lo, prefix_hi, mask, bins);
     }
-    for (size_t i = n / 4 * 4 + first; i < n; i += stride) Count(image[i], pass, prefix, mask, bins);
+    for (size_t i = n / 4 * 4 + first; i < n; i += stride)
+      Count(image[i], pass, prefix_lo, prefix_hi, mask, bins);
   } else {
-    for (size_t i = first; i < n; i += stride) Count(image[i], pass, prefix, mask, bins);
+    for (size_t i = first; i < n; i += stride) Count(image[i], pass, prefix_lo, prefix_hi, mask, bins);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 2048; i += blockDim.x)
+  for (int i = threadIdx.x; i < 2 * kHistogramBins; i += blockDim.x)
     if (bins[i]) atomicAdd(&histogram[i], bins[i]);
 }
 
-// One warp: finds the bin holding the wanted rank, appends it to the prefix, clears the
-// histogram. With upper_middle set (first pass of the first selection) the rank is count / 2 of
-// the pixels counted, and the count is kept for the host.
-__global__ void SelectNarrowKernel(unsigned long long* scalars, unsigned* histogram, int bits,
-                                   int upper_middle) {
-  __shared__ unsigned long long chunk_sum[32];
-  const int lane = threadIdx.x;
+// Two warps, one per rank: each finds the bin holding its rank (in the shared histogram while
+// the prefixes are equal), appends it to its prefix; then both histograms are cleared. With
+// middle_ranks set (first pass of the first selection) the ranks are (count - 1) / 2 and
+// count / 2 of the pixels counted, and the count is kept for the host.
+__global__ void __launch_bounds__(64)
+SelectNarrowKernel(unsigned long long* scalars, unsigned* histogram, int bits, int middle_ranks) {
+  __shared__ unsigned long long chunk_sum[2][32];
+  const int which = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const unsigned long long prefix_lo = scalars[kPrefixLo], prefix_hi = scalars[kPrefixHi];
+  const unsigned* bins = histogram + ((which == 1 && prefix_hi != prefix_lo) ? kHistogramBins : 0);
   const int n_bins = 1 << bits, per = (n_bins + 31) / 32;
   unsigned long long sum = 0;
-  for (int b = lane * per; b < min(n_bins, (lane + 1) * per); ++b) sum += histogram[b];
-  chunk_sum[lane] = sum;
-  __syncwarp();
+  for (int b = lane * per; b < min(n_bins, (lane + 1) * per); ++b) sum += bins[b];
+  chunk_sum[which][lane] = sum;
+  __syncthreads();
   if (lane == 0) {
-    unsigned long long rank = scalars[kRankWord];
-    if (upper_middle) {
+    unsigned long long rank = scalars[which ? kRankHi : kRankLo];
+    if (middle_ranks) {
       unsigned long long total = 0;
-      for (int c = 0; c < 32; ++c) total += chunk_sum[c];
-      scalars[kCountWord] = total;
-      rank = total / 2;
+      for (int c = 0; c < 32; ++c) total += chunk_sum[which][c];
+      if (which == 0) scalars[kCountWord] = total;
+      rank = which == 0 ? (total ? (total - 1) / 2 : 0) : total / 2;
     }
     int c = 0;
-    while (c < 31 && rank >= chunk_sum[c]) rank -= chunk_sum[c++];
+    while (c < 31 && rank >= chunk_sum[which][c]) rank -= chunk_sum[which][c++];
     int b = c * per;
-    while (b < n_bins - 1 && rank >= histogram[b]) rank -= histogram[b++];
-    scalars[kPrefixWord] = (scalars[kPrefixWord] << bits) | unsigned(b);
-    scalars[kRankWord] = rank;
+    while (b < n_bins - 1 && rank >= bins[b]) rank -= bins[b++];
+    scalars[which ? kPrefixHi : kPrefixLo] = ((which ? prefix_hi : prefix_lo) << bits) | unsigned(b);
+    scalars[which ? kRankHi : kRankLo] = rank;
   }
-  __syncwarp();
-  for (int b = lane; b < 2048; b += 32) histogram[b] = 0;
+  __syncthreads();
+  for (int b = threadIdx.x; b < 2 * kHistogramBins; b += 64) histogram[b] = 0;
 }
 
 struct Selected {
-  unsigned key;
+  unsigned key_lo, key_hi;  // of ranks (count - 1) / 2 and count / 2
   uint64_t n_finite;
 };
 
-// The key of rank `rank` among the finite pixels (rank < 0: the upper middle, counted here).
-Selected Select(rdl_handle& h, const float* image, size_t n, int deviation, float centre,
-                long long rank, cudaStream_t stream) {
-  h.iuwt_scalars.Reserve(kIuwtScalarWords);
+// The keys of the two middle ranks among the finite pixels; n_finite = 0: counted here.
+Selected SelectMiddle(rdl_handle& h, const float* image, size_t n, int deviation, float centre,
+                      uint64_t n_finite, cudaStream_t stream) {
+  h.iuwt_scalars.Reserve(kSelectWords);
   unsigned long long* scalars = h.iuwt_scalars.get();
   unsigned* histogram = reinterpret_cast<unsigned*>(scalars + kIuwtHistWord);
-  RDL_CUDA(cudaMemsetAsync(scalars, 0, kIuwtScalarWords * sizeof(unsigned long long), stream));
-  if (rank >= 0) {
-    const unsigned long long r = static_cast<unsigned long long>(rank);
-    RDL_CUDA(cudaMemcpyAsync(scalars + kRankWord, &r, sizeof(r), cudaMemcpyHostToDevice, stream));
+  RDL_CUDA(cudaMemsetAsync(scalars, 0, kSelectWords * sizeof(unsigned long long), stream));
+  if (n_finite) {
+    unsigned long long init[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    init[kRankLo] = (n_finite - 1) / 2;
+    init[kRankHi] = n_finite / 2;
+    init[kCountWord] = n_finite;
+    RDL_CUDA(cudaMemcpyAsync(scalars, init, sizeof(init), cudaMemcpyHostToDevice, stream));
   }
   const SelectPass passes[3] = {{21, 11, 32, deviation, centre},
                                 {10, 11, 21, deviation, centre},
@@ -129,14 +153,14 @@ Selected Select(rdl_handle& h, const float* image, size_t n, int deviation, floa
   const unsigned grid = unsigned(std::min<size_t>((n / 4 + 511) / 512 + 1, size_t(kSmCount) * 4));
   for (int p = 0; p != 3; ++p) {
     SelectHistogramKernel<<<grid, 512, 0, stream>>>(image, n, passes[p], scalars, histogram);
-    SelectNarrowKernel<<<1, 32, 0, stream>>>(scalars, histogram, passes[p].bits,
-                                             p == 0 && rank < 0);
+    SelectNarrowKernel<<<1, 64, 0, stream>>>(scalars, histogram, passes[p].bits,
+                                             p == 0 && !n_finite);
   }
   RDL_CUDA(cudaGetLastError());
-  unsigned long long back[4] = {0, 0, 0, 0};  // words 2..5
-  RDL_CUDA(cudaMemcpyAsync(back, scalars + kPrefixWord, sizeof(back), cudaMemcpyDeviceToHost, stream));
+  unsigned long long back[8];
+  RDL_CUDA(cudaMemcpyAsync(back, scalars, sizeof(back), cudaMemcpyDeviceToHost, stream));
   RDL_CUDA(cudaStreamSynchronize(stream));
-  return {unsigned(back[0]), back[kCountWord - kPrefixWord]};
+  return {unsigned(back[kPrefixLo]), unsigned(back[kPrefixHi]), back[kCountWord]};
 }
 
 float FromBits(unsigned bits) {
@@ -152,15 +176,12 @@ float FromOrderedBits(unsigned key) {
 // median of the finite pixels (deviation = 0) or of |pixel - centre| (deviation = 1)
 float Median(rdl_handle& h, const float* image, size_t n, int deviation, float centre,
              uint64_t& n_finite, cudaStream_t stream) {
-  const Selected upper = Select(h, image, n, deviation, centre,
-                                n_finite ? static_cast<long long>(n_finite / 2) : -1, stream);
-  if (!n_finite) n_finite = upper.n_finite;
+  const Selected s = SelectMiddle(h, image, n, deviation, centre, n_finite, stream);
+  n_finite = s.n_finite;
   if (!n_finite) return 0.0f;
-  const float hi = deviation ? FromBits(upper.key) : FromOrderedBits(upper.key);
+  const float hi = deviation ? FromBits(s.key_hi) : FromOrderedBits(s.key_hi);
   if (n_finite % 2 == 1) return hi;
-  const Selected lower = Select(h, image, n, deviation, centre,
-                                static_cast<long long>(n_finite / 2) - 1, stream);
-  const float lo = deviation ? FromBits(lower.key) : FromOrderedBits(lower.key);
+  const float lo = deviation ? FromBits(s.key_lo) : FromOrderedBits(s.key_lo);
   return (lo + hi) * 0.5f;
 }
 
