@@ -129,7 +129,7 @@ def test_k5_facets_8x8_reduced_frame(rdl, oracle, torch_cuda, sub_minor):
     # pixel further left or right, and that pixel belongs to the neighbouring facet, whose version
     # of it (its own components' sidelobes subtracted) differs. Seen here: ONE pixel of 2^20,
     # 1.7e-3 of the peak, same models; each facet alone agrees three ways (oracle, reference
-    # sources, device) within 2e-7 (tools/k5_debug2.py). Allow a few such pixels, everything else
+    # sources, device) within 2e-7 (tests/tools/k5_debug2.py). Allow a few such pixels, everything else
     # within 1e-5.
     diff = np.abs(g_res - r_res)
     flipped = int(np.count_nonzero(diff > 1e-5 * peak))

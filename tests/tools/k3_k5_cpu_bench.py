@@ -2,13 +2,13 @@
 BASELINE configs 3 and 5, on bounded versions of the configs, wall clock:
   K3  IuwtDeconvolution::ExecuteMajorIteration, 2048^2 x 1
   K5  ParallelDeconvolution 8 x 8 facets, Hogbom per facet (divider search included), 4096^2 x 1
-python tools/k3_k5_cpu_bench.py [k3_size] [k5_size]"""
+python tests/tools/k3_k5_cpu_bench.py [k3_size] [k5_size]"""
 import json
 import os
 import sys
 import time
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import torch
 

@@ -1,7 +1,7 @@
 """Times csrc/image_statistics.cu (Radler::Perform's steps around the major iteration) on the
 device against the reference's host code for the same step (oracle/_ref: image_set.cc compiled
 against the aocommon stand-in), one JSON line per step.
-    python tools/perform_steps_bench.py [size] [n_original] [n_deconvolution]"""
+    python tests/tools/perform_steps_bench.py [size] [n_original] [n_deconvolution]"""
 import json
 import os
 import sys
@@ -10,7 +10,7 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import oracle  # noqa: E402  (the CPU arm only)
 import ska_sdp_func_radler_b200 as rdl  # noqa: E402
 
