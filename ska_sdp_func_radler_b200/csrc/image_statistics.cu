@@ -2,7 +2,9 @@
 // rank 1), so that a caller holding the cube in device memory need not bring a plane back for them:
 //   radler.cc:162-169   integrated.MedianAndStdDevFromMAD()  -> ImageMedianAndStdDevFromMad
 //   image_set.cc:105-140 ImageSet::LoadAndAverage            -> ImageLoadAndAverage
+//   image_set.cc:142-205 ImageSet::LoadAndAveragePsfs        -> ImageLoadAndAverage (psf_rule)
 //   radler.cc:254-266   auto-mask from the model images      -> ImageMaskFromModel
+//   image_set.cc:208-283 ImageSet::InterpolateAndStoreModel  -> ImageInterpolateModel
 // MedianAndStdDevFromMAD is aocommon's (third-party, absent from the tree): restated as the
 // median over the finite pixels ((lower + upper middle) * 0.5 for an even count), then
 // 1.4826 x the same median of |pixel - median| -- oracle/ref_shim/aocommon/image.h holds the same
